@@ -1,0 +1,125 @@
+/*
+ * rmb_b200.h -- C ABI of the B200-native batched policy-rollout engine for RoboManipBaselines' ACT hot path.
+ *
+ * The reference (RoboManipBaselines @ 219a5496) is pure Python and has no FFI; each entry point below replaces the
+ * Python function named next to it (paths relative to the reference root). A maintainer binds this library with
+ * ctypes. Conventions:
+ *   - every function returns 0 on success, <0 on error; rmb_last_error() gives the message
+ *   - all `d_*` pointers are DEVICE pointers owned by the caller (e.g. torch tensors); `stream` is a cudaStream_t
+ *   - all work is enqueued on `stream`; no hidden synchronisation except in rmb_act_engine_create/finalize
+ *   - one engine per GPU, not thread-safe per handle; sm_100a only, there is no CPU fallback
+ */
+#ifndef RMB_B200_H_
+#define RMB_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct rmb_act_engine rmb_act_engine_t;
+
+/* model_meta_info["policy"]["args"] of policy/act/TrainAct.py:45-57 + dims that DETRVAE keeps as class attributes
+ * (third_party/act/detr/models/detr_vae.py:37-46) -- carried per engine instance here. */
+typedef struct rmb_act_config {
+  int32_t max_batch;        /* episodes per forward (workspace is sized for this) */
+  int32_t num_cams;         /* len(camera_names) */
+  int32_t img_h, img_w;     /* camera resolution, multiples of 32 (480 x 640 in MujocoUR5eCable) */
+  int32_t state_dim;        /* DETRVAE.STATE_DIM */
+  int32_t action_dim;       /* DETRVAE.ACTION_DIM */
+  int32_t hidden_dim;       /* 512 (only value supported) */
+  int32_t dim_feedforward;  /* multiple of 64 (3200) */
+  int32_t nheads;           /* 8 (head dim must be 64) */
+  int32_t enc_layers;       /* 4 */
+  int32_t dec_layers;       /* 7 -- only layer 0 is live at inference (detr_vae.py:142 takes hs[0]) */
+  int32_t chunk_size;       /* num_queries (100) */
+  int32_t device;           /* CUDA device ordinal */
+} rmb_act_config_t;
+
+/* Last error message of the library (per process). */
+const char* rmb_last_error(void);
+/* Library version string and a cheap "is this a B200" probe (returns 0 if device `dev` is sm_100). */
+const char* rmb_version(void);
+int rmb_check_device(int dev);
+
+/* ---- engine lifetime: replaces ACTPolicy.__init__ (third_party/act/policy.py:10-16) + RolloutBase.load_ckpt
+ *      (robo_manip_baselines/common/base/RolloutBase.py:376-385) */
+int rmb_act_engine_create(const rmb_act_config_t* cfg, rmb_act_engine_t** out);
+void rmb_act_engine_destroy(rmb_act_engine_t* e);
+/* Hand over one tensor of the reference checkpoint (`policy_*.ckpt` state dict, key e.g.
+ * "model.transformer.encoder.layers.0.linear1.weight"), fp32, host memory, `numel` elements. Unused keys are accepted
+ * and ignored (the CVAE encoder, is_pad_head, decoder layers 1..6). */
+int rmb_act_load_tensor(rmb_act_engine_t* e, const char* name, const float* host_data, int64_t numel);
+/* Fold FrozenBatchNorm2d into the conv weights, precompute the input-independent tensors (sine position table,
+ * latent token, decoder query projection), upload bf16 weights. Must be called once after all tensors are loaded. */
+int rmb_act_finalize(rmb_act_engine_t* e);
+
+/* ---- ACTPolicy.__call__ inference branch (third_party/act/policy.py:18-38) -> DETRVAE.forward
+ *      (third_party/act/detr/models/detr_vae.py:89-150), for `batch` episodes at once.
+ * image_format 0: d_images = uint8  [batch, num_cams, H, W, 3]  (env layout; RolloutBase.get_images :479-490 fused)
+ * image_format 1: d_images = float32 [batch, num_cams, 3, H, W] in [0,1] (the nn.Module's input)
+ * d_qpos  float32 [batch, state_dim] (already normalised); d_a_hat float32 [batch, chunk_size, action_dim] (normalised). */
+int rmb_act_forward(rmb_act_engine_t* e, const void* d_images, int image_format, const float* d_qpos, float* d_a_hat,
+                    int batch, void* stream);
+/* Number of kernels rmb_act_forward launches for one call (for bench.py's gpu_launches). */
+int rmb_act_forward_num_launches(const rmb_act_engine_t* e);
+/* Algorithmic FLOPs of one forward for `batch` episodes (live graph only). */
+double rmb_act_forward_flops(const rmb_act_engine_t* e, int batch);
+/* Debug taps: copy an internal activation (fp32 view) of the last forward into d_out. which: 0 = backbone+input_proj
+ * tokens [batch, L, 512], 1 = encoder memory [batch, L, 512]. Returns number of floats, <0 on error. */
+int64_t rmb_act_debug_read(rmb_act_engine_t* e, int which, float* d_out, int batch, void* stream);
+
+/* ---- RolloutAct.infer_policy temporal ensembling + denormalize_data
+ *      (robo_manip_baselines/policy/act/RolloutAct.py:68-101; common/utils/DataUtils.py:26-40)
+ * d_ring  float32 [batch, C, C, Da]   slot (n mod C) holds the chunk of policy call n
+ * d_chunks float32 [batch, C, Da]     chunk predicted at this call (output of rmb_act_forward)
+ * d_step  int32 [batch]               per-episode 0-based policy-call counter, advanced by one
+ * d_reset uint8 [batch] or NULL       1 = episode restarts at this call (RolloutAct.reset_variables :62-66)
+ * d_wtab  float64 [C, C]              wtab[(m-1)*C + r] = exp(-0.01 r)/sum_{s<m} exp(-0.01 s) (numpy-made, see host code)
+ * norm_type 0 gaussian: out = d_p0*a + d_p1 (std, mean); 1 limits: out = d_p0*(a - out_min) + d_p1 (scale, min)
+ * outputs (each may be NULL): d_action float64 [batch, Da] denormalised, d_action_f32 same in fp32,
+ *                             d_action_norm float64 [batch, Da] ensembled but still normalised */
+int rmb_ensemble_step(float* d_ring, const float* d_chunks, int32_t* d_step, const uint8_t* d_reset,
+                      const double* d_wtab, int norm_type, const double* d_p0, const double* d_p1, double out_min,
+                      double* d_action, float* d_action_f32, double* d_action_norm, int batch, int C, int Da,
+                      void* stream);
+
+/* ---- normalize_data / denormalize_data (common/utils/DataUtils.py:9-40), fp64 like numpy.
+ * normalize: gaussian (type 0): y = (x - p0)/p1 (mean, std); limits (1): y = p1*(x - p0) + out_min (min, scale); y is fp32
+ *            (RolloutBase.get_state :474-475 casts to float32).
+ * denormalize: gaussian: y = p0*x + p1 (std, mean); limits: y = p0*(x - out_min) + p1 (scale, min); fp64. */
+int rmb_normalize(const double* d_x, int norm_type, const double* d_p0, const double* d_p1, double out_min, float* d_y,
+                  int64_t rows, int D, void* stream);
+int rmb_denormalize(const double* d_x, int norm_type, const double* d_p0, const double* d_p1, double out_min,
+                    double* d_y, int64_t rows, int D, void* stream);
+
+/* ---- RolloutBase.get_images (:479-490) + ImageNet normalise (third_party/act/policy.py:20-22) alone:
+ * uint8 [n_img, H, W, 3] -> bf16 [n_img, H, W + 8, 4] (4 zero pixels either side, 4th channel zero). */
+int rmb_preprocess_images_u8(const uint8_t* d_images, void* d_out_bf16, int n_img, int H, int W, void* stream);
+int rmb_preprocess_images_f32(const float* d_images_chw, void* d_out_bf16, int n_img, int H, int W, void* stream);
+
+/* ---- kernel-level entry points (used by the parity tests; same kernels the engine launches) */
+/* out[M,N] = A[M,K](bf16) * Wt[N,K]^T(bf16) + bias (+ residual) (ReLU); flags: bit0 relu, bit1 out fp32, bit2 residual fp32 */
+int rmb_gemm_bf16(const void* d_A, const void* d_Wt, const float* d_bias, const void* d_residual, void* d_out,
+                  int64_t M, int N, int K, int flags, void* stream);
+/* NHWC bf16 conv k in {1,3}, stride in {1,2}, pad k/2; Wt [Cout, k*k*Cin] tap-major; residual/out [B,OH,OW,Cout] bf16 */
+int rmb_conv2d_nhwc_bf16(const void* d_in, const void* d_Wt, const float* d_bias, const void* d_residual, void* d_out,
+                         int B, int H, int W, int Cin, int Cout, int ksize, int stride, int relu, void* stream);
+/* ResNet stem on the padded NHWC4 input: Wt [64, 7*32] (see gemm_plan.h), out [B, H/2, W/2, 64] bf16, ReLU */
+int rmb_conv1_stem_bf16(const void* d_in_padded, const void* d_Wt, const float* d_bias, void* d_out, int B, int H, int W,
+                        void* stream);
+int rmb_maxpool3x3s2_nhwc_bf16(const void* d_in, void* d_out, int B, int H, int W, int C, void* stream);
+/* softmax(Q K^T / 8) V for 64-wide heads. Q [B*Lq (or Lq if q_shared), ldq], K [B*Lk, ldk], V [B*Lk, ldv], bf16;
+ * head h reads columns col0 + 64h; out [B*Lq, ld_out] bf16 */
+int rmb_attention_bf16(const void* d_Q, int ldq, int q_col0, int q_shared, const void* d_K, int ldk, int k_col0,
+                       const void* d_V, int ldv, int v_col0, void* d_out, int ld_out, int B, int n_heads, int Lq, int Lk,
+                       void* stream);
+/* LayerNorm over 512 columns: x fp32 [rows,512]; outputs optional (NULL): y fp32, y bf16, bf16(y + pos[row % L]) */
+int rmb_layernorm512(const float* d_x, const float* d_gamma, const float* d_beta, const float* d_pos, int L,
+                     float* d_y_f32, void* d_y_bf16, void* d_ypos_bf16, int64_t rows, int do_norm, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RMB_B200_H_ */

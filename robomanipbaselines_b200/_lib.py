@@ -1,0 +1,100 @@
+"""ctypes binding of librmb_b200.so (the C ABI in include/rmb_b200.h).
+
+There is no CPU fallback: if the shared library is missing, loading raises, and every entry point that needs a GPU
+returns an error code that is turned into an exception here.
+"""
+import ctypes
+import os
+from ctypes import POINTER, c_char_p, c_double, c_float, c_int, c_int32, c_int64, c_uint8, c_void_p
+
+_PKG_DIR = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_PKG_DIR, "librmb_b200.so")
+
+
+class RmbError(RuntimeError):
+    pass
+
+
+class ActConfig(ctypes.Structure):
+    """Mirror of rmb_act_config_t."""
+
+    _fields_ = [
+        ("max_batch", c_int32), ("num_cams", c_int32), ("img_h", c_int32), ("img_w", c_int32),
+        ("state_dim", c_int32), ("action_dim", c_int32), ("hidden_dim", c_int32), ("dim_feedforward", c_int32),
+        ("nheads", c_int32), ("enc_layers", c_int32), ("dec_layers", c_int32), ("chunk_size", c_int32),
+        ("device", c_int32),
+    ]
+
+
+# name -> (restype, argtypes); must list every symbol include/rmb_b200.h declares (tests check this)
+SIGNATURES = {
+    "rmb_last_error": (c_char_p, []),
+    "rmb_version": (c_char_p, []),
+    "rmb_check_device": (c_int, [c_int]),
+    "rmb_act_engine_create": (c_int, [POINTER(ActConfig), POINTER(c_void_p)]),
+    "rmb_act_engine_destroy": (None, [c_void_p]),
+    "rmb_act_load_tensor": (c_int, [c_void_p, c_char_p, c_void_p, c_int64]),
+    "rmb_act_finalize": (c_int, [c_void_p]),
+    "rmb_act_forward": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int, c_void_p]),
+    "rmb_act_forward_num_launches": (c_int, [c_void_p]),
+    "rmb_act_forward_flops": (c_double, [c_void_p, c_int]),
+    "rmb_act_debug_read": (c_int64, [c_void_p, c_int, c_void_p, c_int, c_void_p]),
+    "rmb_ensemble_step": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p,
+                                  c_double, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
+    "rmb_normalize": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_double, c_void_p, c_int64, c_int, c_void_p]),
+    "rmb_denormalize": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_double, c_void_p, c_int64, c_int, c_void_p]),
+    "rmb_preprocess_images_u8": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
+    "rmb_preprocess_images_f32": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
+    "rmb_gemm_bf16": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int,
+                              c_void_p]),
+    "rmb_conv2d_nhwc_bf16": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int,
+                                     c_int, c_int, c_int, c_int, c_void_p]),
+    "rmb_conv1_stem_bf16": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
+    "rmb_maxpool3x3s2_nhwc_bf16": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
+    "rmb_attention_bf16": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_int, c_int, c_void_p, c_int, c_int,
+                                   c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p]),
+    "rmb_layernorm512": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p,
+                                 c_int64, c_int, c_void_p]),
+}
+
+_lib = None
+
+
+def load():
+    """dlopen librmb_b200.so and attach signatures. Raises RmbError when the library was not built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RmbError(
+            f"{LIB_PATH} not found: build it with `python -m robomanipbaselines_b200.build` "
+            "(there is no CPU fallback for the CUDA path)"
+        )
+    lib = ctypes.CDLL(LIB_PATH)
+    for name, (restype, argtypes) in SIGNATURES.items():
+        fn = getattr(lib, name)
+        fn.restype = restype
+        fn.argtypes = argtypes
+    _lib = lib
+    return lib
+
+
+def check(code, what=""):
+    """Turn a negative return code into an exception carrying rmb_last_error()."""
+    if code is not None and code < 0:
+        msg = load().rmb_last_error()
+        raise RmbError(f"{what} failed ({code}): {msg.decode() if msg else '?'}")
+    return code
+
+
+def ptr(t):
+    """Device/host pointer of a torch tensor (None -> NULL)."""
+    if t is None:
+        return None
+    return ctypes.c_void_p(t.data_ptr())
+
+
+def cur_stream():
+    import torch
+
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)

@@ -1,0 +1,746 @@
+// B200-native ACT inference engine + the C ABI declared in include/rmb_b200.h.
+// Replaces, for B episodes at once, the reference call chain
+//   RolloutAct.infer_policy (policy/act/RolloutAct.py:68-101) -> ACTPolicy.__call__ (third_party/act/policy.py:18-38)
+//   -> DETRVAE.forward inference branch (third_party/act/detr/models/detr_vae.py:89-150)
+//   -> Transformer.forward (third_party/act/detr/models/transformer.py:49-77).
+// Only the live graph is executed: decoder layers 1..6 and the CVAE encoder never influence a_hat (detr_vae.py:142
+// takes hs[0]); decoder layer 0's self-attention sees tgt = 0, so its output is the constant W_o b_v + b_o.
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdint.h>
+#include <string.h>
+
+#include <map>
+#include <memory>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "../../include/rmb_b200.h"
+#include "attention_tc.cuh"
+#include "elementwise.cuh"
+#include "gemm_plan.h"
+
+using namespace rmb;
+
+static thread_local std::string g_last_error;
+static int fail(const std::string& msg, int code = -1) { g_last_error = msg; return code; }
+#define RMB_CUDA(expr)                                                                             \
+  do {                                                                                             \
+    cudaError_t _e = (expr);                                                                       \
+    if (_e != cudaSuccess) return fail(std::string(#expr) + ": " + cudaGetErrorString(_e), -2);    \
+  } while (0)
+
+namespace {
+
+struct AttnPlan {
+  CUtensorMap tq, tk, tv;
+  AttnParams p;
+  int grid = 0;
+};
+
+bool plan_attention(AttnPlan* a, const void* Q, int ldq, int q_col0, bool q_shared, const void* K, int ldk, int k_col0,
+                    const void* V, int ldv, int v_col0, void* out, int ld_out, int B, int n_heads, int Lq, int Lk,
+                    std::string* err) {
+  const uint32_t box[3] = {64, 128, 1};
+  {
+    const uint64_t dims[3] = {(uint64_t)ldq, (uint64_t)Lq, (uint64_t)(q_shared ? 1 : B)};
+    const uint64_t str[2] = {(uint64_t)ldq * 2, (uint64_t)ldq * 2 * Lq};
+    if (!make_tmap_bf16(&a->tq, Q, 3, dims, str, box, 128, err)) return false;
+  }
+  {
+    const uint64_t dims[3] = {(uint64_t)ldk, (uint64_t)Lk, (uint64_t)B};
+    const uint64_t str[2] = {(uint64_t)ldk * 2, (uint64_t)ldk * 2 * Lk};
+    if (!make_tmap_bf16(&a->tk, K, 3, dims, str, box, 128, err)) return false;
+  }
+  {
+    const uint64_t dims[3] = {(uint64_t)ldv, (uint64_t)Lk, (uint64_t)B};
+    const uint64_t str[2] = {(uint64_t)ldv * 2, (uint64_t)ldv * 2 * Lk};
+    if (!make_tmap_bf16(&a->tv, V, 3, dims, str, box, 128, err)) return false;
+  }
+  AttnParams& p = a->p;
+  p.Lq = Lq; p.Lk = Lk; p.n_q_tiles = (Lq + 127) / 128; p.n_heads = n_heads;
+  p.q_col0 = q_col0; p.k_col0 = k_col0; p.v_col0 = v_col0; p.q_shared = q_shared ? 1 : 0;
+  p.scale_log2e = 0.125f * 1.4426950408889634f;
+  p.out = static_cast<__nv_bfloat16*>(out); p.ld_out = ld_out;
+  a->grid = B * n_heads * p.n_q_tiles;
+  return true;
+}
+
+cudaError_t launch_attention(const AttnPlan& a, cudaStream_t stream) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttnSmemBytes);
+    if (e != cudaSuccess) return e;
+    attr_set = true;
+  }
+  attention_tc_kernel<<<a.grid, kAttnThreads, kAttnSmemBytes, stream>>>(a.tq, a.tk, a.tv, a.p);
+  return cudaGetLastError();
+}
+
+int grid_for(long long work_items, int threads, int num_sms) {
+  long long blocks = (work_items + threads - 1) / threads;
+  const long long cap = static_cast<long long>(num_sms) * 16;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  return static_cast<int>(blocks);
+}
+
+}  // namespace
+
+// =====================================================================================================================
+struct rmb_act_engine {
+  rmb_act_config_t cfg;
+  int num_sms = 148;
+  bool finalized = false;
+  std::unordered_map<std::string, std::vector<float>> host_w;
+  std::vector<void*> allocs;
+
+  // derived
+  int Hf = 0, Wf = 0, L = 0, n_img_max = 0;
+
+  // ---- device weights
+  struct ConvW { __nv_bfloat16* w = nullptr; float* b = nullptr; int cin = 0, cout = 0, k = 0, stride = 1; };
+  ConvW stem;
+  ConvW blk[4][2][2];      // [layer][block][conv]
+  ConvW down[4];           // layer 1..3 (index = layer), layer 0 unused
+  ConvW input_proj;
+  struct EncW {
+    __nv_bfloat16 *w_qk, *w_v, *w_o, *w_1, *w_2;
+    float *b_qk, *b_v, *b_o, *b_1, *b_2, *g1, *be1, *g2, *be2;
+  };
+  std::vector<EncW> enc;
+  struct DecW {
+    __nv_bfloat16 *q_const;                 // [C, 512] projected queries (input independent)
+    __nv_bfloat16 *w_k, *w_v, *w_o, *w_1, *w_2;
+    float *b_k, *b_v, *b_o_fold, *b_1, *b_2, *g2, *be2, *g3, *be3, *gn, *ben;
+  } dec{};
+  float *w_head = nullptr, *b_head = nullptr, *w_state = nullptr, *b_state = nullptr, *latent_bias = nullptr;
+  float* pos = nullptr;    // [L, 512]
+
+  // ---- workspace (sized for max_batch)
+  __nv_bfloat16 *x0 = nullptr, *c1 = nullptr;
+  __nv_bfloat16* stage[4][3] = {};
+  float *tok_f32 = nullptr, *y_f32 = nullptr, *x1_f32 = nullptr;
+  __nv_bfloat16 *tok_b = nullptr, *tok_pb = nullptr, *qk = nullptr, *v = nullptr, *ao = nullptr, *x1_b = nullptr, *hh = nullptr;
+  __nv_bfloat16 *kd = nullptr, *vd = nullptr, *aod = nullptr, *t_b = nullptr, *hd = nullptr;
+  float *yd = nullptr, *t_f32 = nullptr, *yd2 = nullptr;
+
+  struct BatchPlans {
+    GemmPlan stem;
+    GemmPlan conv[4][2][2];
+    GemmPlan down[4];
+    GemmPlan input_proj;
+    struct Enc { GemmPlan qk, v, o, ff1, ff2; AttnPlan attn; };
+    std::vector<Enc> enc;
+    GemmPlan dk, dv, dout, dff1, dff2;
+    AttnPlan dattn;
+  };
+  std::map<int, std::unique_ptr<BatchPlans>> plans;
+
+  template <typename T>
+  T* dalloc(size_t n) {
+    void* p = nullptr;
+    if (cudaMalloc(&p, n * sizeof(T)) != cudaSuccess) return nullptr;
+    allocs.push_back(p);
+    return static_cast<T*>(p);
+  }
+};
+
+namespace {
+
+const std::vector<float>* find_w(rmb_act_engine* e, const std::string& name, size_t numel, std::string* err) {
+  auto it = e->host_w.find(name);
+  if (it == e->host_w.end()) { *err = "missing checkpoint tensor: " + name; return nullptr; }
+  if (it->second.size() != numel) {
+    *err = "checkpoint tensor " + name + " has " + std::to_string(it->second.size()) + " elements, expected " + std::to_string(numel);
+    return nullptr;
+  }
+  return &it->second;
+}
+
+bool upload_f32(rmb_act_engine* e, const std::vector<float>& h, float** d, std::string* err) {
+  *d = e->dalloc<float>(h.size());
+  if (!*d) { *err = "cudaMalloc failed (weights)"; return false; }
+  if (cudaMemcpy(*d, h.data(), h.size() * sizeof(float), cudaMemcpyHostToDevice) != cudaSuccess) { *err = "cudaMemcpy H2D failed"; return false; }
+  return true;
+}
+bool upload_bf16(rmb_act_engine* e, const std::vector<float>& h, __nv_bfloat16** d, std::string* err) {
+  std::vector<__nv_bfloat16> t(h.size());
+  for (size_t i = 0; i < h.size(); ++i) t[i] = __float2bfloat16_rn(h[i]);
+  *d = e->dalloc<__nv_bfloat16>(h.size());
+  if (!*d) { *err = "cudaMalloc failed (weights)"; return false; }
+  if (cudaMemcpy(*d, t.data(), t.size() * sizeof(__nv_bfloat16), cudaMemcpyHostToDevice) != cudaSuccess) { *err = "cudaMemcpy H2D failed"; return false; }
+  return true;
+}
+
+// FrozenBatchNorm2d (third_party/act/detr/models/backbone.py:21-57): y = x*scale + bias,
+// scale = w * rsqrt(rv + 1e-5), bias = b - rm*scale  -> folded into the conv that precedes it.
+bool bn_fold(rmb_act_engine* e, const std::string& bn, int c, std::vector<float>* scale, std::vector<float>* bias, std::string* err) {
+  const auto* w = find_w(e, bn + ".weight", c, err); if (!w) return false;
+  const auto* b = find_w(e, bn + ".bias", c, err); if (!b) return false;
+  const auto* rm = find_w(e, bn + ".running_mean", c, err); if (!rm) return false;
+  const auto* rv = find_w(e, bn + ".running_var", c, err); if (!rv) return false;
+  scale->resize(c); bias->resize(c);
+  for (int i = 0; i < c; ++i) {
+    const float s = (*w)[i] * (1.0f / sqrtf((*rv)[i] + 1e-5f));
+    (*scale)[i] = s;
+    (*bias)[i] = (*b)[i] - (*rm)[i] * s;
+  }
+  return true;
+}
+
+bool make_conv(rmb_act_engine* e, const std::string& conv, const std::string& bn, int cin, int cout, int k, int stride,
+               rmb_act_engine::ConvW* out, std::string* err) {
+  const auto* w = find_w(e, conv + ".weight", (size_t)cout * cin * k * k, err); if (!w) return false;
+  std::vector<float> scale, bias;
+  if (!bn_fold(e, bn, cout, &scale, &bias, err)) return false;
+  std::vector<float> r((size_t)cout * k * k * cin);
+  for (int co = 0; co < cout; ++co)
+    for (int ci = 0; ci < cin; ++ci)
+      for (int kh = 0; kh < k; ++kh)
+        for (int kw = 0; kw < k; ++kw)
+          r[(((size_t)co * k + kh) * k + kw) * cin + ci] = (*w)[(((size_t)co * cin + ci) * k + kh) * k + kw] * scale[co];
+  out->cin = cin; out->cout = cout; out->k = k; out->stride = stride;
+  return upload_bf16(e, r, &out->w, err) && upload_f32(e, bias, &out->b, err);
+}
+
+void layernorm_host(const std::vector<double>& x, const std::vector<float>& g, const std::vector<float>& b, std::vector<double>* y) {
+  const size_t n = x.size();
+  double mu = 0; for (double v : x) mu += v; mu /= n;
+  double var = 0; for (double v : x) var += (v - mu) * (v - mu); var /= n;
+  const double rstd = 1.0 / sqrt(var + 1e-5);
+  y->resize(n);
+  for (size_t i = 0; i < n; ++i) (*y)[i] = (x[i] - mu) * rstd * g[i] + b[i];
+}
+
+}  // namespace
+
+// =====================================================================================================================
+extern "C" {
+
+const char* rmb_last_error(void) { return g_last_error.c_str(); }
+const char* rmb_version(void) { return "rmb_b200 0.1 (sm_100a)"; }
+
+int rmb_check_device(int dev) {
+  cudaDeviceProp prop;
+  RMB_CUDA(cudaGetDeviceProperties(&prop, dev));
+  if (prop.major != 10) return fail(std::string("device is sm_") + std::to_string(prop.major * 10 + prop.minor) + ", this library is sm_100a only", -3);
+  return 0;
+}
+
+int rmb_act_engine_create(const rmb_act_config_t* cfg, rmb_act_engine_t** out) {
+  if (!cfg || !out) return fail("null argument");
+  if (cfg->hidden_dim != 512) return fail("hidden_dim must be 512");
+  if (cfg->nheads != 8) return fail("nheads must be 8 (head dim 64)");
+  if (cfg->dim_feedforward % 64 != 0) return fail("dim_feedforward must be a multiple of 64");
+  if (cfg->img_h % 32 != 0 || cfg->img_w % 32 != 0) return fail("image size must be a multiple of 32");
+  if (cfg->max_batch < 1 || cfg->num_cams < 1 || cfg->chunk_size < 1 || cfg->enc_layers < 1 || cfg->dec_layers < 1) return fail("bad config");
+  if (cfg->state_dim < 1 || cfg->action_dim < 1) return fail("bad state/action dim");
+  RMB_CUDA(cudaSetDevice(cfg->device));
+  if (int r = rmb_check_device(cfg->device)) return r;
+  auto* e = new rmb_act_engine();
+  e->cfg = *cfg;
+  cudaDeviceProp prop;
+  cudaGetDeviceProperties(&prop, cfg->device);
+  e->num_sms = prop.multiProcessorCount;
+  e->Hf = cfg->img_h / 32; e->Wf = cfg->img_w / 32;
+  e->L = 2 + e->Hf * e->Wf * cfg->num_cams;
+  e->n_img_max = cfg->max_batch * cfg->num_cams;
+  *out = e;
+  return 0;
+}
+
+void rmb_act_engine_destroy(rmb_act_engine_t* e) {
+  if (!e) return;
+  cudaSetDevice(e->cfg.device);
+  cudaDeviceSynchronize();
+  for (void* p : e->allocs) cudaFree(p);
+  delete e;
+}
+
+int rmb_act_load_tensor(rmb_act_engine_t* e, const char* name, const float* host_data, int64_t numel) {
+  if (!e || !name || (!host_data && numel > 0) || numel < 0) return fail("rmb_act_load_tensor: bad argument");
+  if (e->finalized) return fail("rmb_act_load_tensor: engine already finalized");
+  e->host_w[name] = std::vector<float>(host_data, host_data + numel);
+  return 0;
+}
+
+int rmb_act_finalize(rmb_act_engine_t* e) {
+  if (!e) return fail("null engine");
+  if (e->finalized) return fail("already finalized");
+  RMB_CUDA(cudaSetDevice(e->cfg.device));
+  std::string err;
+  const rmb_act_config_t& c = e->cfg;
+  const int D = 512, FF = c.dim_feedforward, C = c.chunk_size;
+  const std::string bb = "model.backbones.0.0.body.";
+
+  // ---- ResNet-18 trunk
+  {
+    // stem: [64,3,7,7] -> [64][kh][slot 0..7][4], slot j>=1 <-> kw = j-1, channel 3 and slot 0 are zero
+    const auto* w = find_w(e, bb + "conv1.weight", 64 * 3 * 49, &err); if (!w) return fail(err);
+    std::vector<float> scale, bias;
+    if (!bn_fold(e, bb + "bn1", 64, &scale, &bias, &err)) return fail(err);
+    std::vector<float> r(64 * 7 * 32, 0.f);
+    for (int co = 0; co < 64; ++co)
+      for (int ci = 0; ci < 3; ++ci)
+        for (int kh = 0; kh < 7; ++kh)
+          for (int kw = 0; kw < 7; ++kw)
+            r[((co * 7 + kh) * 8 + (kw + 1)) * 4 + ci] = (*w)[((co * 3 + ci) * 7 + kh) * 7 + kw] * scale[co];
+    e->stem.cin = 3; e->stem.cout = 64; e->stem.k = 7; e->stem.stride = 2;
+    if (!upload_bf16(e, r, &e->stem.w, &err) || !upload_f32(e, bias, &e->stem.b, &err)) return fail(err);
+  }
+  const int chans[4] = {64, 128, 256, 512};
+  for (int li = 0; li < 4; ++li)
+    for (int bi = 0; bi < 2; ++bi) {
+      const std::string p = bb + "layer" + std::to_string(li + 1) + "." + std::to_string(bi) + ".";
+      const int cin = (bi == 0 && li > 0) ? chans[li - 1] : chans[li];
+      const int stride = (bi == 0 && li > 0) ? 2 : 1;
+      if (!make_conv(e, p + "conv1", p + "bn1", cin, chans[li], 3, stride, &e->blk[li][bi][0], &err)) return fail(err);
+      if (!make_conv(e, p + "conv2", p + "bn2", chans[li], chans[li], 3, 1, &e->blk[li][bi][1], &err)) return fail(err);
+      if (bi == 0 && li > 0)
+        if (!make_conv(e, p + "downsample.0", p + "downsample.1", cin, chans[li], 1, 2, &e->down[li], &err)) return fail(err);
+    }
+  {
+    // input_proj: Conv2d 1x1 512 -> hidden with bias, no BN (detr_vae.py:67,135)
+    const auto* w = find_w(e, "model.input_proj.weight", (size_t)D * 512, &err); if (!w) return fail(err);
+    const auto* b = find_w(e, "model.input_proj.bias", D, &err); if (!b) return fail(err);
+    e->input_proj.cin = 512; e->input_proj.cout = D; e->input_proj.k = 1; e->input_proj.stride = 1;
+    if (!upload_bf16(e, *w, &e->input_proj.w, &err) || !upload_f32(e, *b, &e->input_proj.b, &err)) return fail(err);
+  }
+
+  // ---- encoder layers (transformer.py:143-197)
+  e->enc.resize(c.enc_layers);
+  for (int l = 0; l < c.enc_layers; ++l) {
+    const std::string p = "model.transformer.encoder.layers." + std::to_string(l) + ".";
+    const auto* wi = find_w(e, p + "self_attn.in_proj_weight", (size_t)3 * D * D, &err); if (!wi) return fail(err);
+    const auto* bi = find_w(e, p + "self_attn.in_proj_bias", 3 * D, &err); if (!bi) return fail(err);
+    const auto* wo = find_w(e, p + "self_attn.out_proj.weight", (size_t)D * D, &err); if (!wo) return fail(err);
+    const auto* bo = find_w(e, p + "self_attn.out_proj.bias", D, &err); if (!bo) return fail(err);
+    const auto* w1 = find_w(e, p + "linear1.weight", (size_t)FF * D, &err); if (!w1) return fail(err);
+    const auto* b1 = find_w(e, p + "linear1.bias", FF, &err); if (!b1) return fail(err);
+    const auto* w2 = find_w(e, p + "linear2.weight", (size_t)D * FF, &err); if (!w2) return fail(err);
+    const auto* b2 = find_w(e, p + "linear2.bias", D, &err); if (!b2) return fail(err);
+    const auto* g1 = find_w(e, p + "norm1.weight", D, &err); if (!g1) return fail(err);
+    const auto* be1 = find_w(e, p + "norm1.bias", D, &err); if (!be1) return fail(err);
+    const auto* g2 = find_w(e, p + "norm2.weight", D, &err); if (!g2) return fail(err);
+    const auto* be2 = find_w(e, p + "norm2.bias", D, &err); if (!be2) return fail(err);
+    rmb_act_engine::EncW& w = e->enc[l];
+    std::vector<float> wqk(wi->begin(), wi->begin() + (size_t)2 * D * D), wv(wi->begin() + (size_t)2 * D * D, wi->end());
+    std::vector<float> bqk(bi->begin(), bi->begin() + 2 * D), bv(bi->begin() + 2 * D, bi->end());
+    if (!upload_bf16(e, wqk, &w.w_qk, &err) || !upload_bf16(e, wv, &w.w_v, &err) || !upload_bf16(e, *wo, &w.w_o, &err) ||
+        !upload_bf16(e, *w1, &w.w_1, &err) || !upload_bf16(e, *w2, &w.w_2, &err) || !upload_f32(e, bqk, &w.b_qk, &err) ||
+        !upload_f32(e, bv, &w.b_v, &err) || !upload_f32(e, *bo, &w.b_o, &err) || !upload_f32(e, *b1, &w.b_1, &err) ||
+        !upload_f32(e, *b2, &w.b_2, &err) || !upload_f32(e, *g1, &w.g1, &err) || !upload_f32(e, *be1, &w.be1, &err) ||
+        !upload_f32(e, *g2, &w.g2, &err) || !upload_f32(e, *be2, &w.be2, &err))
+      return fail(err);
+  }
+
+  // ---- decoder layer 0 (transformer.py:229-250) with its input-independent parts folded
+  {
+    const std::string p = "model.transformer.decoder.layers.0.";
+    const auto* sa_b = find_w(e, p + "self_attn.in_proj_bias", 3 * D, &err); if (!sa_b) return fail(err);
+    const auto* sa_wo = find_w(e, p + "self_attn.out_proj.weight", (size_t)D * D, &err); if (!sa_wo) return fail(err);
+    const auto* sa_bo = find_w(e, p + "self_attn.out_proj.bias", D, &err); if (!sa_bo) return fail(err);
+    const auto* g1 = find_w(e, p + "norm1.weight", D, &err); if (!g1) return fail(err);
+    const auto* be1 = find_w(e, p + "norm1.bias", D, &err); if (!be1) return fail(err);
+    const auto* wi = find_w(e, p + "multihead_attn.in_proj_weight", (size_t)3 * D * D, &err); if (!wi) return fail(err);
+    const auto* bi = find_w(e, p + "multihead_attn.in_proj_bias", 3 * D, &err); if (!bi) return fail(err);
+    const auto* wo = find_w(e, p + "multihead_attn.out_proj.weight", (size_t)D * D, &err); if (!wo) return fail(err);
+    const auto* bo = find_w(e, p + "multihead_attn.out_proj.bias", D, &err); if (!bo) return fail(err);
+    const auto* w1 = find_w(e, p + "linear1.weight", (size_t)FF * D, &err); if (!w1) return fail(err);
+    const auto* b1 = find_w(e, p + "linear1.bias", FF, &err); if (!b1) return fail(err);
+    const auto* w2 = find_w(e, p + "linear2.weight", (size_t)D * FF, &err); if (!w2) return fail(err);
+    const auto* b2 = find_w(e, p + "linear2.bias", D, &err); if (!b2) return fail(err);
+    const auto* g2 = find_w(e, p + "norm2.weight", D, &err); if (!g2) return fail(err);
+    const auto* be2 = find_w(e, p + "norm2.bias", D, &err); if (!be2) return fail(err);
+    const auto* g3 = find_w(e, p + "norm3.weight", D, &err); if (!g3) return fail(err);
+    const auto* be3 = find_w(e, p + "norm3.bias", D, &err); if (!be3) return fail(err);
+    const auto* gn = find_w(e, "model.transformer.decoder.norm.weight", D, &err); if (!gn) return fail(err);
+    const auto* ben = find_w(e, "model.transformer.decoder.norm.bias", D, &err); if (!ben) return fail(err);
+    const auto* qe = find_w(e, "model.query_embed.weight", (size_t)C * D, &err); if (!qe) return fail(err);
+    // self-attention with value = tgt = 0: every value row is b_v, softmax rows sum to 1 -> sa = W_o b_v + b_o
+    std::vector<double> sa(D);
+    for (int i = 0; i < D; ++i) {
+      double acc = (*sa_bo)[i];
+      for (int k = 0; k < D; ++k) acc += (double)(*sa_wo)[(size_t)i * D + k] * (double)(*sa_b)[2 * D + k];
+      sa[i] = acc;
+    }
+    std::vector<double> tgt1;
+    layernorm_host(sa, *g1, *be1, &tgt1);                       // tgt after norm1: one vector for all queries/episodes
+    std::vector<float> qc((size_t)C * D);
+    for (int qi = 0; qi < C; ++qi)
+      for (int i = 0; i < D; ++i) {
+        double acc = (*bi)[i];
+        for (int k = 0; k < D; ++k) acc += (double)(*wi)[(size_t)i * D + k] * (tgt1[k] + (double)(*qe)[(size_t)qi * D + k]);
+        qc[(size_t)qi * D + i] = (float)acc;
+      }
+    std::vector<float> wk(wi->begin() + (size_t)D * D, wi->begin() + (size_t)2 * D * D), wv(wi->begin() + (size_t)2 * D * D, wi->end());
+    std::vector<float> bk(bi->begin() + D, bi->begin() + 2 * D), bv(bi->begin() + 2 * D, bi->end());
+    std::vector<float> bo_fold(D);
+    for (int i = 0; i < D; ++i) bo_fold[i] = (float)((double)(*bo)[i] + tgt1[i]);   // residual tgt1 folded into the bias
+    auto& d = e->dec;
+    if (!upload_bf16(e, qc, &d.q_const, &err) || !upload_bf16(e, wk, &d.w_k, &err) || !upload_bf16(e, wv, &d.w_v, &err) ||
+        !upload_bf16(e, *wo, &d.w_o, &err) || !upload_bf16(e, *w1, &d.w_1, &err) || !upload_bf16(e, *w2, &d.w_2, &err) ||
+        !upload_f32(e, bk, &d.b_k, &err) || !upload_f32(e, bv, &d.b_v, &err) || !upload_f32(e, bo_fold, &d.b_o_fold, &err) ||
+        !upload_f32(e, *b1, &d.b_1, &err) || !upload_f32(e, *b2, &d.b_2, &err) || !upload_f32(e, *g2, &d.g2, &err) ||
+        !upload_f32(e, *be2, &d.be2, &err) || !upload_f32(e, *g3, &d.g3, &err) || !upload_f32(e, *be3, &d.be3, &err) ||
+        !upload_f32(e, *gn, &d.gn, &err) || !upload_f32(e, *ben, &d.ben, &err))
+      return fail(err);
+  }
+  {
+    const auto* wh = find_w(e, "model.action_head.weight", (size_t)c.action_dim * D, &err); if (!wh) return fail(err);
+    const auto* bh = find_w(e, "model.action_head.bias", c.action_dim, &err); if (!bh) return fail(err);
+    const auto* ws = find_w(e, "model.input_proj_robot_state.weight", (size_t)D * c.state_dim, &err); if (!ws) return fail(err);
+    const auto* bs = find_w(e, "model.input_proj_robot_state.bias", D, &err); if (!bs) return fail(err);
+    const auto* lb = find_w(e, "model.latent_out_proj.bias", D, &err); if (!lb) return fail(err);
+    const auto* ap = find_w(e, "model.additional_pos_embed.weight", 2 * D, &err); if (!ap) return fail(err);
+    if (!upload_f32(e, *wh, &e->w_head, &err) || !upload_f32(e, *bh, &e->b_head, &err) || !upload_f32(e, *ws, &e->w_state, &err) ||
+        !upload_f32(e, *bs, &e->b_state, &err) || !upload_f32(e, *lb, &e->latent_bias, &err))
+      return fail(err);
+    // position table [L, 512]: rows 0,1 = additional_pos_embed; then PositionEmbeddingSine(256, normalize=True)
+    // (position_encoding.py:30-52) of a (Hf, Wf) map, identical for every camera, cameras folded along width
+    // (detr_vae.py:140-141): token 2 + h*(Wf*Ncam) + cam*Wf + w.
+    std::vector<float> pos((size_t)e->L * D);
+    for (int i = 0; i < 2 * D; ++i) pos[i] = (*ap)[i];
+    const float two_pi = 2.0f * 3.14159265358979323846f;
+    for (int h = 0; h < e->Hf; ++h)
+      for (int w = 0; w < e->Wf; ++w) {
+        const float y_embed = (float)(h + 1) / ((float)e->Hf + 1e-6f) * two_pi;
+        const float x_embed = (float)(w + 1) / ((float)e->Wf + 1e-6f) * two_pi;
+        float row[512];
+        for (int i = 0; i < 256; ++i) {
+          const float dim_t = powf(10000.0f, 2.0f * (float)(i / 2) / 256.0f);
+          const float ay = y_embed / dim_t, ax = x_embed / dim_t;
+          row[i] = (i % 2 == 0) ? sinf(ay) : cosf(ay);
+          row[256 + i] = (i % 2 == 0) ? sinf(ax) : cosf(ax);
+        }
+        for (int cam = 0; cam < c.num_cams; ++cam) {
+          const size_t t = 2 + (size_t)h * (e->Wf * c.num_cams) + (size_t)cam * e->Wf + w;
+          memcpy(&pos[t * D], row, sizeof(row));
+        }
+      }
+    if (!upload_f32(e, pos, &e->pos, &err)) return fail(err);
+  }
+
+  // ---- workspace
+  {
+    const size_t NI = e->n_img_max, H = c.img_h, W = c.img_w;
+    const size_t BL = (size_t)c.max_batch * e->L, BC = (size_t)c.max_batch * C;
+    bool ok = true;
+    ok &= (e->x0 = e->dalloc<__nv_bfloat16>(NI * H * (W + 8) * 4)) != nullptr;
+    ok &= (e->c1 = e->dalloc<__nv_bfloat16>(NI * (H / 2) * (W / 2) * 64)) != nullptr;
+    for (int li = 0; li < 4; ++li)
+      for (int k = 0; k < 3; ++k)
+        ok &= (e->stage[li][k] = e->dalloc<__nv_bfloat16>(NI * (H >> (2 + li)) * (W >> (2 + li)) * chans[li])) != nullptr;
+    ok &= (e->tok_f32 = e->dalloc<float>(BL * D)) != nullptr;
+    ok &= (e->y_f32 = e->dalloc<float>(BL * D)) != nullptr;
+    ok &= (e->x1_f32 = e->dalloc<float>(BL * D)) != nullptr;
+    ok &= (e->tok_b = e->dalloc<__nv_bfloat16>(BL * D)) != nullptr;
+    ok &= (e->tok_pb = e->dalloc<__nv_bfloat16>(BL * D)) != nullptr;
+    ok &= (e->qk = e->dalloc<__nv_bfloat16>(BL * 2 * D)) != nullptr;
+    ok &= (e->v = e->dalloc<__nv_bfloat16>(BL * D)) != nullptr;
+    ok &= (e->ao = e->dalloc<__nv_bfloat16>(BL * D)) != nullptr;
+    ok &= (e->x1_b = e->dalloc<__nv_bfloat16>(BL * D)) != nullptr;
+    ok &= (e->hh = e->dalloc<__nv_bfloat16>(BL * FF)) != nullptr;
+    ok &= (e->kd = e->dalloc<__nv_bfloat16>(BL * D)) != nullptr;
+    ok &= (e->vd = e->dalloc<__nv_bfloat16>(BL * D)) != nullptr;
+    ok &= (e->aod = e->dalloc<__nv_bfloat16>(BC * D)) != nullptr;
+    ok &= (e->t_b = e->dalloc<__nv_bfloat16>(BC * D)) != nullptr;
+    ok &= (e->hd = e->dalloc<__nv_bfloat16>(BC * FF)) != nullptr;
+    ok &= (e->yd = e->dalloc<float>(BC * D)) != nullptr;
+    ok &= (e->t_f32 = e->dalloc<float>(BC * D)) != nullptr;
+    ok &= (e->yd2 = e->dalloc<float>(BC * D)) != nullptr;
+    if (!ok) return fail("cudaMalloc failed (workspace)");
+  }
+  e->host_w.clear();
+  e->finalized = true;
+  RMB_CUDA(cudaDeviceSynchronize());
+  return 0;
+}
+
+static int build_plans(rmb_act_engine* e, int nb, rmb_act_engine::BatchPlans** out) {
+  auto it = e->plans.find(nb);
+  if (it != e->plans.end()) { *out = it->second.get(); return 0; }
+  std::unique_ptr<rmb_act_engine::BatchPlans> bp(new rmb_act_engine::BatchPlans());
+  std::string err;
+  const rmb_act_config_t& c = e->cfg;
+  const int NI = nb * c.num_cams, H = c.img_h, W = c.img_w, D = 512, FF = c.dim_feedforward, C = c.chunk_size, L = e->L;
+  const int chans[4] = {64, 128, 256, 512};
+  if (!plan_conv1(&bp->stem, e->x0, NI, H, W, e->stem.w, e->stem.b, e->c1, &err)) return fail(err);
+  // stage buffers: [0] = t (mid), [1] = y (block 0 out), [2] = d (downsample) then z (block 1 out)
+  for (int li = 0; li < 4; ++li) {
+    const int h = H >> (2 + li), w = W >> (2 + li);
+    const __nv_bfloat16* x_in = (li == 0) ? e->stage[0][2] /* maxpool output lives in stage[0][2] */ : e->stage[li - 1][2];
+    __nv_bfloat16 *t = e->stage[li][0], *y = e->stage[li][1], *z = e->stage[li][2];
+    const int hin = (li == 0) ? h : h * 2, win = (li == 0) ? w : w * 2;
+    const int cin = (li == 0) ? 64 : chans[li - 1];
+    const void* identity = x_in;
+    if (li > 0) {
+      if (!plan_conv(&bp->down[li], x_in, NI, hin, win, cin, 1, 2, e->down[li].w, chans[li], e->down[li].b, nullptr, false, z, chans[li], false, false, &err)) return fail(err);
+      identity = z;
+    }
+    if (!plan_conv(&bp->conv[li][0][0], x_in, NI, hin, win, cin, 3, (li == 0) ? 1 : 2, e->blk[li][0][0].w, chans[li], e->blk[li][0][0].b, nullptr, false, t, chans[li], false, true, &err)) return fail(err);
+    if (!plan_conv(&bp->conv[li][0][1], t, NI, h, w, chans[li], 3, 1, e->blk[li][0][1].w, chans[li], e->blk[li][0][1].b, identity, false, y, chans[li], false, true, &err)) return fail(err);
+    if (!plan_conv(&bp->conv[li][1][0], y, NI, h, w, chans[li], 3, 1, e->blk[li][1][0].w, chans[li], e->blk[li][1][0].b, nullptr, false, t, chans[li], false, true, &err)) return fail(err);
+    if (!plan_conv(&bp->conv[li][1][1], t, NI, h, w, chans[li], 3, 1, e->blk[li][1][1].w, chans[li], e->blk[li][1][1].b, y, false, z, chans[li], false, true, &err)) return fail(err);
+  }
+  // input_proj: 1x1 conv whose output rows are scattered straight into token order, fp32 residual stream
+  if (!plan_conv(&bp->input_proj, e->stage[3][2], NI, e->Hf, e->Wf, 512, 1, 1, e->input_proj.w, D, e->input_proj.b, nullptr, false, e->tok_f32, D, true, false, &err)) return fail(err);
+  bp->input_proj.p.remap_ncam = c.num_cams; bp->input_proj.p.remap_L = L; bp->input_proj.p.remap_off = 2;
+
+  const long long BL = (long long)nb * L, BC = (long long)nb * C;
+  bp->enc.resize(c.enc_layers);
+  for (int l = 0; l < c.enc_layers; ++l) {
+    auto& w = e->enc[l];
+    auto& pl = bp->enc[l];
+    if (!plan_linear(&pl.qk, e->tok_pb, BL, D, D, w.w_qk, 2 * D, w.b_qk, nullptr, 0, false, e->qk, 2 * D, false, false, &err)) return fail(err);
+    if (!plan_linear(&pl.v, e->tok_b, BL, D, D, w.w_v, D, w.b_v, nullptr, 0, false, e->v, D, false, false, &err)) return fail(err);
+    if (!plan_attention(&pl.attn, e->qk, 2 * D, 0, false, e->qk, 2 * D, D, e->v, D, 0, e->ao, D, nb, c.nheads, L, L, &err)) return fail(err);
+    if (!plan_linear(&pl.o, e->ao, BL, D, D, w.w_o, D, w.b_o, e->tok_f32, D, true, e->y_f32, D, true, false, &err)) return fail(err);
+    if (!plan_linear(&pl.ff1, e->x1_b, BL, D, D, w.w_1, FF, w.b_1, nullptr, 0, false, e->hh, FF, false, true, &err)) return fail(err);
+    if (!plan_linear(&pl.ff2, e->hh, BL, FF, FF, w.w_2, D, w.b_2, e->x1_f32, D, true, e->y_f32, D, true, false, &err)) return fail(err);
+  }
+  auto& d = e->dec;
+  if (!plan_linear(&bp->dk, e->tok_pb, BL, D, D, d.w_k, D, d.b_k, nullptr, 0, false, e->kd, D, false, false, &err)) return fail(err);
+  if (!plan_linear(&bp->dv, e->tok_b, BL, D, D, d.w_v, D, d.b_v, nullptr, 0, false, e->vd, D, false, false, &err)) return fail(err);
+  if (!plan_attention(&bp->dattn, d.q_const, D, 0, true, e->kd, D, 0, e->vd, D, 0, e->aod, D, nb, c.nheads, C, L, &err)) return fail(err);
+  if (!plan_linear(&bp->dout, e->aod, BC, D, D, d.w_o, D, d.b_o_fold, nullptr, 0, false, e->yd, D, true, false, &err)) return fail(err);
+  if (!plan_linear(&bp->dff1, e->t_b, BC, D, D, d.w_1, FF, d.b_1, nullptr, 0, false, e->hd, FF, false, true, &err)) return fail(err);
+  if (!plan_linear(&bp->dff2, e->hd, BC, FF, FF, d.w_2, D, d.b_2, e->t_f32, D, true, e->yd2, D, true, false, &err)) return fail(err);
+  *out = bp.get();
+  e->plans[nb] = std::move(bp);
+  return 0;
+}
+
+int rmb_act_forward_num_launches(const rmb_act_engine_t* e) {
+  if (!e) return -1;
+  // preprocess, stem, maxpool, 16 convs + 3 downsamples, input_proj, extra tokens, cast(+pos), 8 per encoder layer,
+  // decoder: K, V, attention, out, LN, FF1, FF2, head
+  return 3 + 19 + 3 + 8 * e->cfg.enc_layers + 8;
+}
+
+double rmb_act_forward_flops(const rmb_act_engine_t* e, int batch) {
+  if (!e) return -1.0;
+  const rmb_act_config_t& c = e->cfg;
+  const double NI = (double)batch * c.num_cams, H = c.img_h, W = c.img_w, D = 512, FF = c.dim_feedforward, L = e->L, C = c.chunk_size;
+  double f = 0;
+  f += 2.0 * NI * (H / 2) * (W / 2) * 64 * 147;                                       // stem
+  const double ch[4] = {64, 128, 256, 512};
+  for (int li = 0; li < 4; ++li) {
+    const double px = (H / (4 << li)) * (W / (4 << li));
+    const double cin = li == 0 ? 64 : ch[li - 1];
+    f += 2.0 * NI * px * ch[li] * 9 * cin + 3 * 2.0 * NI * px * ch[li] * 9 * ch[li];
+    if (li > 0) f += 2.0 * NI * px * ch[li] * cin;
+  }
+  f += 2.0 * NI * e->Hf * e->Wf * D * 512;                                            // input_proj
+  const double BL = (double)batch * L;
+  f += c.enc_layers * (2.0 * BL * D * (4 * D + 2 * FF) + 4.0 * batch * L * L * D);    // QKV+O, FFN, QK^T + PV
+  f += 2.0 * BL * D * 2 * D + 4.0 * batch * C * L * D + 2.0 * batch * C * D * (D + 2 * FF) + 2.0 * batch * C * D * c.action_dim;
+  return f;
+}
+
+int rmb_act_forward(rmb_act_engine_t* e, const void* d_images, int image_format, const float* d_qpos, float* d_a_hat,
+                    int batch, void* stream_) {
+  if (!e || !d_images || !d_qpos || !d_a_hat) return fail("rmb_act_forward: null argument");
+  if (!e->finalized) return fail("rmb_act_forward: weights not finalized");
+  if (batch < 1 || batch > e->cfg.max_batch) return fail("rmb_act_forward: batch out of range");
+  cudaStream_t s = static_cast<cudaStream_t>(stream_);
+  rmb_act_engine::BatchPlans* bp = nullptr;
+  if (int r = build_plans(e, batch, &bp)) return r;
+  const rmb_act_config_t& c = e->cfg;
+  const int NI = batch * c.num_cams, H = c.img_h, W = c.img_w, L = e->L, C = c.chunk_size;
+  const int sms = e->num_sms;
+  const float3 mean = make_float3(0.485f, 0.456f, 0.406f);
+  const float3 istd = make_float3(1.0f / 0.229f, 1.0f / 0.224f, 1.0f / 0.225f);
+  {
+    const long long items = (long long)NI * H * (W / 4 + 2);
+    if (image_format == 0)
+      preprocess_u8_kernel<<<grid_for(items, 256, sms), 256, 0, s>>>(static_cast<const uint8_t*>(d_images), e->x0, NI, H, W, mean, istd);
+    else if (image_format == 1)
+      preprocess_f32_kernel<<<grid_for(items, 256, sms), 256, 0, s>>>(static_cast<const float*>(d_images), e->x0, NI, H, W, mean, istd);
+    else
+      return fail("rmb_act_forward: image_format must be 0 (u8 HWC) or 1 (f32 CHW)");
+  }
+  RMB_CUDA(launch_gemm(bp->stem, sms, s));
+  {
+    const long long items = (long long)NI * (H / 4) * (W / 4) * 8;
+    maxpool3x3s2_kernel<<<grid_for(items, 256, sms), 256, 0, s>>>(e->c1, e->stage[0][2], NI, H / 2, W / 2, 64);
+  }
+  for (int li = 0; li < 4; ++li) {
+    if (li > 0) RMB_CUDA(launch_gemm(bp->down[li], sms, s));
+    RMB_CUDA(launch_gemm(bp->conv[li][0][0], sms, s));
+    RMB_CUDA(launch_gemm(bp->conv[li][0][1], sms, s));
+    RMB_CUDA(launch_gemm(bp->conv[li][1][0], sms, s));
+    RMB_CUDA(launch_gemm(bp->conv[li][1][1], sms, s));
+  }
+  RMB_CUDA(launch_gemm(bp->input_proj, sms, s));
+  act_extra_tokens_kernel<<<batch, 256, 0, s>>>(d_qpos, c.state_dim, e->latent_bias, e->w_state, e->b_state, e->tok_f32, L);
+  const long long BL = (long long)batch * L, BC = (long long)batch * C;
+  const int ln_grid = grid_for(BL * 32, 256, sms);
+  layernorm512_kernel<<<ln_grid, 256, 0, s>>>(e->tok_f32, nullptr, nullptr, e->pos, L, nullptr, e->tok_b, e->tok_pb, BL, 0, 1e-5f);
+  for (int l = 0; l < c.enc_layers; ++l) {
+    auto& w = e->enc[l];
+    auto& pl = bp->enc[l];
+    RMB_CUDA(launch_gemm(pl.qk, sms, s));
+    RMB_CUDA(launch_gemm(pl.v, sms, s));
+    RMB_CUDA(launch_attention(pl.attn, s));
+    RMB_CUDA(launch_gemm(pl.o, sms, s));                       // y = ao Wo^T + bo + x
+    layernorm512_kernel<<<ln_grid, 256, 0, s>>>(e->y_f32, w.g1, w.be1, nullptr, L, e->x1_f32, e->x1_b, nullptr, BL, 1, 1e-5f);
+    RMB_CUDA(launch_gemm(pl.ff1, sms, s));
+    RMB_CUDA(launch_gemm(pl.ff2, sms, s));                     // y = relu(.) W2^T + b2 + x1
+    layernorm512_kernel<<<ln_grid, 256, 0, s>>>(e->y_f32, w.g2, w.be2, e->pos, L, e->tok_f32, e->tok_b, e->tok_pb, BL, 1, 1e-5f);
+  }
+  RMB_CUDA(launch_gemm(bp->dk, sms, s));
+  RMB_CUDA(launch_gemm(bp->dv, sms, s));
+  RMB_CUDA(launch_attention(bp->dattn, s));
+  RMB_CUDA(launch_gemm(bp->dout, sms, s));
+  const int lnd_grid = grid_for(BC * 32, 256, sms);
+  layernorm512_kernel<<<lnd_grid, 256, 0, s>>>(e->yd, e->dec.g2, e->dec.be2, nullptr, C, e->t_f32, e->t_b, nullptr, BC, 1, 1e-5f);
+  RMB_CUDA(launch_gemm(bp->dff1, sms, s));
+  RMB_CUDA(launch_gemm(bp->dff2, sms, s));
+  act_head_kernel<<<lnd_grid, 256, 0, s>>>(e->yd2, e->dec.g3, e->dec.be3, e->dec.gn, e->dec.ben, e->w_head, e->b_head, d_a_hat, BC, c.action_dim, 1e-5f);
+  RMB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int64_t rmb_act_debug_read(rmb_act_engine_t* e, int which, float* d_out, int batch, void* stream_) {
+  if (!e || !d_out) return fail("rmb_act_debug_read: null argument");
+  cudaStream_t s = static_cast<cudaStream_t>(stream_);
+  const int64_t n = (int64_t)batch * e->L * 512;
+  if (which == 1) {
+    RMB_CUDA(cudaMemcpyAsync(d_out, e->tok_f32, n * sizeof(float), cudaMemcpyDeviceToDevice, s));
+    return n;
+  }
+  return fail("rmb_act_debug_read: unknown tap");
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+int rmb_ensemble_step(float* d_ring, const float* d_chunks, int32_t* d_step, const uint8_t* d_reset,
+                      const double* d_wtab, int norm_type, const double* d_p0, const double* d_p1, double out_min,
+                      double* d_action, float* d_action_f32, double* d_action_norm, int batch, int C, int Da,
+                      void* stream_) {
+  if (!d_ring || !d_chunks || !d_step || !d_wtab || !d_p0 || !d_p1) return fail("rmb_ensemble_step: null argument");
+  if (batch < 1 || C < 1 || Da < 1 || Da > 128) return fail("rmb_ensemble_step: bad sizes");
+  if (norm_type != 0 && norm_type != 1) return fail("rmb_ensemble_step: norm_type must be 0 (gaussian) or 1 (limits)");
+  DenormParams dn{d_p0, d_p1, out_min, norm_type};
+  ensemble_step_kernel<<<batch, 128, 0, static_cast<cudaStream_t>(stream_)>>>(d_ring, d_chunks, d_step, d_reset, d_wtab, dn, d_action, d_action_f32, d_action_norm, C, Da);
+  RMB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int rmb_normalize(const double* d_x, int norm_type, const double* d_p0, const double* d_p1, double out_min, float* d_y,
+                  int64_t rows, int D, void* stream_) {
+  if (!d_x || !d_p0 || !d_p1 || !d_y) return fail("rmb_normalize: null argument");
+  if (norm_type != 0 && norm_type != 1) return fail("rmb_normalize: norm_type must be 0 or 1");
+  if (rows * D == 0) return 0;
+  normalize_state_kernel<<<grid_for(rows * D, 256, 148), 256, 0, static_cast<cudaStream_t>(stream_)>>>(d_x, d_p0, d_p1, out_min, norm_type, d_y, rows * D, D);
+  RMB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int rmb_denormalize(const double* d_x, int norm_type, const double* d_p0, const double* d_p1, double out_min,
+                    double* d_y, int64_t rows, int D, void* stream_) {
+  if (!d_x || !d_p0 || !d_p1 || !d_y) return fail("rmb_denormalize: null argument");
+  if (norm_type != 0 && norm_type != 1) return fail("rmb_denormalize: norm_type must be 0 or 1");
+  if (rows * D == 0) return 0;
+  DenormParams dn{d_p0, d_p1, out_min, norm_type};
+  denormalize_kernel<<<grid_for(rows * D, 256, 148), 256, 0, static_cast<cudaStream_t>(stream_)>>>(d_x, dn, d_y, rows * D, D);
+  RMB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int rmb_preprocess_images_u8(const uint8_t* d_images, void* d_out, int n_img, int H, int W, void* stream_) {
+  if (!d_images || !d_out) return fail("rmb_preprocess_images_u8: null argument");
+  if (W % 4 != 0) return fail("rmb_preprocess_images_u8: W must be a multiple of 4");
+  const long long items = (long long)n_img * H * (W / 4 + 2);
+  preprocess_u8_kernel<<<grid_for(items, 256, 148), 256, 0, static_cast<cudaStream_t>(stream_)>>>(
+      d_images, static_cast<__nv_bfloat16*>(d_out), n_img, H, W, make_float3(0.485f, 0.456f, 0.406f),
+      make_float3(1.0f / 0.229f, 1.0f / 0.224f, 1.0f / 0.225f));
+  RMB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int rmb_preprocess_images_f32(const float* d_images, void* d_out, int n_img, int H, int W, void* stream_) {
+  if (!d_images || !d_out) return fail("rmb_preprocess_images_f32: null argument");
+  if (W % 4 != 0) return fail("rmb_preprocess_images_f32: W must be a multiple of 4");
+  const long long items = (long long)n_img * H * (W / 4 + 2);
+  preprocess_f32_kernel<<<grid_for(items, 256, 148), 256, 0, static_cast<cudaStream_t>(stream_)>>>(
+      d_images, static_cast<__nv_bfloat16*>(d_out), n_img, H, W, make_float3(0.485f, 0.456f, 0.406f),
+      make_float3(1.0f / 0.229f, 1.0f / 0.224f, 1.0f / 0.225f));
+  RMB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+static int device_sms() {
+  int dev = 0, sms = 148;
+  if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  return sms;
+}
+
+int rmb_gemm_bf16(const void* d_A, const void* d_Wt, const float* d_bias, const void* d_residual, void* d_out,
+                  int64_t M, int N, int K, int flags, void* stream_) {
+  if (!d_A || !d_Wt || !d_out) return fail("rmb_gemm_bf16: null argument");
+  GemmPlan g;
+  std::string err;
+  if (!plan_linear(&g, d_A, M, K, K, d_Wt, N, d_bias, d_residual, N, (flags & 4) != 0, d_out, N, (flags & 2) != 0, (flags & 1) != 0, &err)) return fail(err);
+  RMB_CUDA(launch_gemm(g, device_sms(), static_cast<cudaStream_t>(stream_)));
+  return 0;
+}
+
+int rmb_conv2d_nhwc_bf16(const void* d_in, const void* d_Wt, const float* d_bias, const void* d_residual, void* d_out,
+                         int B, int H, int W, int Cin, int Cout, int ksize, int stride, int relu, void* stream_) {
+  if (!d_in || !d_Wt || !d_out) return fail("rmb_conv2d_nhwc_bf16: null argument");
+  GemmPlan g;
+  std::string err;
+  if (!plan_conv(&g, d_in, B, H, W, Cin, ksize, stride, d_Wt, Cout, d_bias, d_residual, false, d_out, Cout, false, relu != 0, &err)) return fail(err);
+  RMB_CUDA(launch_gemm(g, device_sms(), static_cast<cudaStream_t>(stream_)));
+  return 0;
+}
+
+int rmb_conv1_stem_bf16(const void* d_in_padded, const void* d_Wt, const float* d_bias, void* d_out, int B, int H, int W,
+                        void* stream_) {
+  if (!d_in_padded || !d_Wt || !d_out) return fail("rmb_conv1_stem_bf16: null argument");
+  GemmPlan g;
+  std::string err;
+  if (!plan_conv1(&g, d_in_padded, B, H, W, d_Wt, d_bias, d_out, &err)) return fail(err);
+  RMB_CUDA(launch_gemm(g, device_sms(), static_cast<cudaStream_t>(stream_)));
+  return 0;
+}
+
+int rmb_maxpool3x3s2_nhwc_bf16(const void* d_in, void* d_out, int B, int H, int W, int C, void* stream_) {
+  if (!d_in || !d_out) return fail("rmb_maxpool3x3s2_nhwc_bf16: null argument");
+  if (C % 8 != 0) return fail("rmb_maxpool3x3s2_nhwc_bf16: C must be a multiple of 8");
+  const long long items = (long long)B * ((H + 1) / 2) * ((W + 1) / 2) * (C / 8);
+  maxpool3x3s2_kernel<<<grid_for(items, 256, 148), 256, 0, static_cast<cudaStream_t>(stream_)>>>(
+      static_cast<const __nv_bfloat16*>(d_in), static_cast<__nv_bfloat16*>(d_out), B, H, W, C);
+  RMB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int rmb_attention_bf16(const void* d_Q, int ldq, int q_col0, int q_shared, const void* d_K, int ldk, int k_col0,
+                       const void* d_V, int ldv, int v_col0, void* d_out, int ld_out, int B, int n_heads, int Lq, int Lk,
+                       void* stream_) {
+  if (!d_Q || !d_K || !d_V || !d_out) return fail("rmb_attention_bf16: null argument");
+  AttnPlan a;
+  std::string err;
+  if (!plan_attention(&a, d_Q, ldq, q_col0, q_shared != 0, d_K, ldk, k_col0, d_V, ldv, v_col0, d_out, ld_out, B, n_heads, Lq, Lk, &err)) return fail(err);
+  RMB_CUDA(launch_attention(a, static_cast<cudaStream_t>(stream_)));
+  return 0;
+}
+
+int rmb_layernorm512(const float* d_x, const float* d_gamma, const float* d_beta, const float* d_pos, int L,
+                     float* d_y_f32, void* d_y_bf16, void* d_ypos_bf16, int64_t rows, int do_norm, void* stream_) {
+  if (!d_x) return fail("rmb_layernorm512: null argument");
+  if (do_norm && (!d_gamma || !d_beta)) return fail("rmb_layernorm512: gamma/beta required");
+  if (d_ypos_bf16 && (!d_pos || L < 1)) return fail("rmb_layernorm512: pos table required");
+  layernorm512_kernel<<<grid_for(rows * 32, 256, 148), 256, 0, static_cast<cudaStream_t>(stream_)>>>(
+      d_x, d_gamma, d_beta, d_pos, L < 1 ? 1 : L, d_y_f32, static_cast<__nv_bfloat16*>(d_y_bf16),
+      static_cast<__nv_bfloat16*>(d_ypos_bf16), rows, do_norm, 1e-5f);
+  RMB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,192 @@
+// Multi-head attention (head dim 64) on tcgen05/TMEM for the DETR encoder self-attention and decoder cross-attention
+// (nn.MultiheadAttention inside third_party/act/detr/models/transformer.py:166-179,229-250; 8 heads x 64, no masks,
+// dropout off at eval). One CTA = one (episode, head, 128-query tile).
+//
+// Sequence lengths here are short (S = 2 + 300*Ncam = 302..902 keys), so the softmax is done in two sweeps over the
+// keys instead of an online-rescaled single sweep:
+//   sweep 0: S = Q K^T per 128-key block (tcgen05.mma, fp32 in TMEM) -> exact row maximum
+//   sweep 1: S again, P = exp2((S - max) * scale*log2e) -> bf16 P tile in swizzled smem -> O += P V (tcgen05.mma)
+// No accumulator rescaling is ever needed, and every thread owns exactly one query row (TMEM lane), so row max / row sum
+// are thread-local. K/V tiles arrive by TMA (SWIZZLE_128B), double-buffered one block ahead.
+//   Q: K-major A operand [128 q x 64 d];  K: K-major B operand [128 kv x 64 d];
+//   P: K-major A operand [128 q x 128 kv] (two 64-wide swizzle atoms);  V: MN-major B operand [64 d x 128 kv].
+#pragma once
+#include <cuda.h>
+#include "ptx.cuh"
+
+namespace rmb {
+
+struct AttnParams {
+  int Lq, Lk;          // valid queries / keys per episode
+  int n_q_tiles;       // ceil(Lq / 128)
+  int n_heads;
+  int q_col0, k_col0, v_col0;   // first column of head 0 inside the Q / K / V source matrices
+  int q_shared;        // 1: Q is the same [Lq, *] matrix for every episode (decoder: input-independent queries)
+  float scale_log2e;   // (1/sqrt(64)) * log2(e)
+  __nv_bfloat16* out;  // [B*Lq, ld_out], head h at columns h*64
+  int ld_out;
+};
+
+constexpr int kAttnThreads = 128;
+constexpr int kAttnSmemBytes = 16384 /*Q*/ + 2 * 16384 /*K*/ + 2 * 16384 /*V*/ + 32768 /*P*/ + 256 + 1024;
+
+__device__ __forceinline__ float fast_exp2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+__global__ void __launch_bounds__(kAttnThreads, 2)
+attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_k,
+                    const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ AttnParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sQ = smem;
+  uint8_t* sK = smem + 16384;           // 2 stages
+  uint8_t* sV = smem + 16384 * 3;       // 2 stages
+  uint8_t* sP = smem + 16384 * 5;       // 32 KB
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 16384 * 7);
+  uint64_t* q_bar = bars;               // Q landed
+  uint64_t* kv_bar = bars + 1;          // [2] K (and V in sweep 1) landed
+  uint64_t* s_bar = bars + 3;           // S = QK^T complete
+  uint64_t* o_bar = bars + 4;           // O += PV complete
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 5);
+
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const int qt = blockIdx.x % p.n_q_tiles;
+  const int head = (blockIdx.x / p.n_q_tiles) % p.n_heads;
+  const int b = blockIdx.x / (p.n_q_tiles * p.n_heads);
+  const int nkt = (p.Lk + 127) / 128;
+
+  if (tid == 0) {
+    mbar_init(q_bar, 1); mbar_init(&kv_bar[0], 1); mbar_init(&kv_bar[1], 1); mbar_init(s_bar, 1); mbar_init(o_bar, 1);
+    fence_mbar_init();
+    prefetch_tmap(&tmap_q); prefetch_tmap(&tmap_k); prefetch_tmap(&tmap_v);
+  }
+  if (warp == 0) { tmem_alloc(tmem_ptr_smem, 256); tmem_relinquish(); }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+  const uint32_t tmem_S = tmem_base;          // 128 fp32 columns
+  const uint32_t tmem_O = tmem_base + 128;    // 64 fp32 columns
+  const uint32_t lane_off = static_cast<uint32_t>(warp * 32) << 16;
+
+  constexpr uint32_t kIdescS = make_idesc_bf16(128, 128, false, false);   // S[128 q,128 kv] = Q * K^T
+  constexpr uint32_t kIdescO = make_idesc_bf16(128, 64, false, true);     // O[128 q, 64 d] = P * V (V is MN-major)
+
+  auto issue_load = [&](int g) {
+    const int sweep = g / nkt, kt = g % nkt, st = g & 1;
+    mbar_arrive_expect_tx(&kv_bar[st], sweep == 0 ? 16384u : 32768u);
+    tma_load_3d(sK + st * 16384, &tmap_k, &kv_bar[st], p.k_col0 + head * 64, kt * 128, b);
+    if (sweep == 1) tma_load_3d(sV + st * 16384, &tmap_v, &kv_bar[st], p.v_col0 + head * 64, kt * 128, b);
+  };
+
+  if (tid == 0) {
+    mbar_arrive_expect_tx(q_bar, 16384u);
+    tma_load_3d(sQ, &tmap_q, q_bar, p.q_col0 + head * 64, qt * 128, p.q_shared ? 0 : b);
+    issue_load(0);
+  }
+
+  float row_max = -INFINITY, row_sum = 0.f;
+  const int total = 2 * nkt;
+  for (int g = 0; g < total; ++g) {
+    const int sweep = g / nkt, kt = g % nkt, st = g & 1;
+    if (sweep == 1 && kt > 0) {            // previous PV done: P tile and the other K/V stage are free again
+      mbar_wait(o_bar, (kt - 1) & 1);
+      tc_fence_after();
+    }
+    if (tid == 0) {
+      if (g + 1 < total) issue_load(g + 1);
+      if (g == 0) mbar_wait(q_bar, 0);
+      mbar_wait(&kv_bar[st], (g >> 1) & 1);
+      tc_fence_after();
+      const uint32_t qa = smem_u32(sQ), ka = smem_u32(sK + st * 16384);
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+        umma_bf16_ss(tmem_S, make_smem_desc(qa + k * 32, 0, 1024, 2), make_smem_desc(ka + k * 32, 0, 1024, 2), kIdescS,
+                     k != 0);
+      umma_commit(s_bar);
+    }
+    mbar_wait(s_bar, g & 1);
+    tc_fence_after();
+    const int kv_base = kt * 128;
+    if (sweep == 0) {
+#pragma unroll 1
+      for (int c = 0; c < 128; c += 32) {
+        uint32_t v[32];
+        tmem_ld_32x32b_x32(tmem_S + lane_off + c, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 32; ++i)
+          if (kv_base + c + i < p.Lk) row_max = fmaxf(row_max, __uint_as_float(v[i]));
+      }
+    } else {
+      const float mscaled = row_max * p.scale_log2e;
+#pragma unroll 1
+      for (int c = 0; c < 128; c += 32) {
+        uint32_t v[32];
+        tmem_ld_32x32b_x32(tmem_S + lane_off + c, v);
+        tmem_ld_wait();
+        uint32_t pk[16];
+#pragma unroll
+        for (int i = 0; i < 32; i += 2) {
+          float p0 = (kv_base + c + i < p.Lk) ? fast_exp2(__uint_as_float(v[i]) * p.scale_log2e - mscaled) : 0.f;
+          float p1 = (kv_base + c + i + 1 < p.Lk) ? fast_exp2(__uint_as_float(v[i + 1]) * p.scale_log2e - mscaled) : 0.f;
+          __nv_bfloat162 h2 = __floats2bfloat162_rn(p0, p1);
+          row_sum += __low2float(h2) + __high2float(h2);   // normalise by what the MMA will actually see
+          pk[i >> 1] = *reinterpret_cast<uint32_t*>(&h2);
+        }
+        // row `tid` of P, key columns [c, c+32): 4 x 16-byte chunks, 128B-swizzled inside its 64-key atom
+        const int atom = c >> 6;
+        uint8_t* prow = sP + atom * 16384 + tid * 128;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int chunk = ((c & 63) >> 3) + j;
+          *reinterpret_cast<uint4*>(prow + ((chunk ^ (tid & 7)) << 4)) =
+              make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+        }
+      }
+      fence_proxy_async_smem();            // generic-proxy smem writes -> visible to the tensor core (async proxy)
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (sweep == 1 && tid == 0) {
+      tc_fence_after();
+      const uint32_t pa = smem_u32(sP), va = smem_u32(sV + st * 16384);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const uint64_t dp = make_smem_desc(pa + (k >> 2) * 16384 + (k & 3) * 32, 0, 1024, 2);
+        const uint64_t dv = make_smem_desc(va + k * 2048, 0, 1024, 2);   // 16 keys = 2 groups of 8 x 128 B rows
+        umma_bf16_ss(tmem_O, dp, dv, kIdescO, (kt | k) != 0);
+      }
+      umma_commit(o_bar);
+    }
+  }
+  mbar_wait(o_bar, (nkt - 1) & 1);
+  tc_fence_after();
+
+  const int q = qt * 128 + tid;
+  const float inv = 1.0f / row_sum;
+  __nv_bfloat16* orow = p.out + (static_cast<long long>(b) * p.Lq + q) * p.ld_out + head * 64;
+#pragma unroll 1
+  for (int c = 0; c < 64; c += 32) {
+    uint32_t v[32];
+    tmem_ld_32x32b_x32(tmem_O + lane_off + c, v);
+    tmem_ld_wait();
+    if (q < p.Lq) {
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+        reinterpret_cast<uint4*>(orow + c)[i] =
+            make_uint4(pack_bf16x2(__uint_as_float(v[8 * i]) * inv, __uint_as_float(v[8 * i + 1]) * inv),
+                       pack_bf16x2(__uint_as_float(v[8 * i + 2]) * inv, __uint_as_float(v[8 * i + 3]) * inv),
+                       pack_bf16x2(__uint_as_float(v[8 * i + 4]) * inv, __uint_as_float(v[8 * i + 5]) * inv),
+                       pack_bf16x2(__uint_as_float(v[8 * i + 6]) * inv, __uint_as_float(v[8 * i + 7]) * inv));
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) { tc_fence_after(); tmem_dealloc(tmem_base, 256); }
+}
+
+}  // namespace rmb
