@@ -104,4 +104,5 @@ def get_images(rgb_images):
     """RolloutBase.get_images (:479-490): list of (H, W, 3) uint8 -> float32 (1, Ncam, 3, H, W) in [0, 1]."""
     images = np.stack(rgb_images, axis=0)
     images = np.moveaxis(images, -1, -3)
-    return (images.astype(np.float32) / 255.0)[np.newaxis]
+    # v2.ToDtype(float32, scale=True) multiplies by 1/255 in float32 (RolloutBase.py:353,488)
+    return (images.astype(np.float32) * np.float32(1.0 / 255.0))[np.newaxis]

@@ -1,0 +1,67 @@
+"""Deterministic random-init weights and observations for benchmarks, smoke tests and parity fixtures.
+
+There is no network for checkpoints, so "random-init weights of that architecture" are generated here as a pure
+function of (key name, shape, seed): the same state dict can be rebuilt on any machine and loaded both into the
+reference modules (golden generation) and into this package's policies.
+"""
+import zlib
+
+import numpy as np
+import torch
+
+
+def _gen(key, seed):
+    g = torch.Generator(device="cpu")
+    g.manual_seed((zlib.crc32(key.encode()) + 1000003 * int(seed)) % (2 ** 31 - 1))
+    return g
+
+
+def synthetic_tensor(key, shape, seed=0):
+    shape = tuple(int(s) for s in shape)
+    g = _gen(key, seed)
+    is_bn = (".bn" in key) or (".downsample.1." in key)
+    if key.endswith("running_var"):
+        return torch.rand(shape, generator=g) + 0.5
+    if is_bn and key.endswith(".weight"):
+        return torch.rand(shape, generator=g) + 0.5
+    if is_bn:
+        return torch.randn(shape, generator=g) * 0.1
+    if ".norm" in key and key.endswith(".weight"):
+        return 1.0 + 0.1 * torch.randn(shape, generator=g)
+    if len(shape) == 4:
+        fan_in = shape[1] * shape[2] * shape[3]
+        return torch.randn(shape, generator=g) * (2.0 / fan_in) ** 0.5
+    if "embed" in key and len(shape) == 2:
+        return torch.randn(shape, generator=g) * 0.5
+    if len(shape) == 2:
+        return torch.randn(shape, generator=g) * (1.0 / shape[1]) ** 0.5
+    if len(shape) == 1:
+        return torch.randn(shape, generator=g) * 0.05
+    return torch.randn(shape, generator=g)
+
+
+def synthetic_state_dict(shapes, seed=0):
+    """shapes: mapping key -> shape (e.g. {k: v.shape for k, v in module.state_dict().items()})."""
+    return {k: synthetic_tensor(k, s, seed) for k, s in shapes.items()}
+
+
+def synthetic_norm_stats(dim, seed=0, norm_type="gaussian"):
+    """model_meta_info['state'|'action']-style statistics with non-trivial values (TrainBase.py:309-344 layout)."""
+    rng = np.random.default_rng(1000 + seed)
+    mn = rng.normal(size=dim)
+    rg = np.clip(rng.uniform(0.5, 2.0, size=dim), 1e-3, None)
+    stats = {"mean": rng.normal(size=dim), "std": np.clip(rng.uniform(0.2, 1.5, size=dim), 1e-3, None), "min": mn,
+             "max": mn + rg, "range": rg, "example": np.zeros(dim)}
+    if norm_type == "limits":
+        stats["norm_config"] = {"type": "limits", "out_min": -1.0, "out_max": 1.0}
+    elif norm_type == "gaussian":
+        stats["norm_config"] = {"type": "gaussian"}
+    return stats
+
+
+def synthetic_act_observations(batch, num_cams, img_h, img_w, state_dim, seed=1):
+    """uint8 U{0..255} images (B, Ncam, H, W, 3) HWC and N(0,1) float64 raw joint states (B, Ds)."""
+    rng = np.random.default_rng(seed)
+    images = rng.integers(0, 256, size=(batch, num_cams, img_h, img_w, 3), dtype=np.uint8)
+    state = rng.standard_normal(size=(batch, state_dim))
+    return images, state

@@ -37,10 +37,11 @@ __global__ void preprocess_u8_kernel(const uint8_t* __restrict__ in, __nv_bfloat
       uint32_t w[8];
 #pragma unroll
       for (int p = 0; p < 4; ++p) {
-        // same arithmetic order as the reference: x/255, then (x - mean)/std, fp32
-        const float r = (static_cast<float>(px[3 * p + 0]) / 255.0f - mean.x) * inv_std.x;
-        const float g = (static_cast<float>(px[3 * p + 1]) / 255.0f - mean.y) * inv_std.y;
-        const float bl = (static_cast<float>(px[3 * p + 2]) / 255.0f - mean.z) * inv_std.z;
+        // same arithmetic as the reference: x * (1/255) in fp32 (v2.ToDtype scale=True), then (x - mean)/std
+        const float k255 = 1.0f / 255.0f;
+        const float r = (static_cast<float>(px[3 * p + 0]) * k255 - mean.x) * inv_std.x;
+        const float g = (static_cast<float>(px[3 * p + 1]) * k255 - mean.y) * inv_std.y;
+        const float bl = (static_cast<float>(px[3 * p + 2]) * k255 - mean.z) * inv_std.z;
         __nv_bfloat162 rg = __floats2bfloat162_rn(r, g);
         __nv_bfloat162 b0 = __floats2bfloat162_rn(bl, 0.0f);
         w[2 * p] = *reinterpret_cast<uint32_t*>(&rg);

@@ -1,0 +1,125 @@
+"""GPU parity of the full ACT engine (through ACTPolicy -> C ABI) against the golden vectors the reference produced,
+and of BatchedRollout against the rollout oracle. Tolerance from BASELINE.json north_star: actions max-abs <= 1e-2 in
+normalised action space; ensembling indices / buffer positions bit-exact."""
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(HERE, "golden"))
+
+from cases import ACT_CASES, act_inputs, policy_args  # noqa: E402
+from robomanipbaselines_b200.common.synthetic import synthetic_norm_stats, synthetic_state_dict  # noqa: E402
+from robomanipbaselines_b200.policy.act import ACTPolicy  # noqa: E402
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(HERE, "golden")
+ACTION_TOL = 1e-2   # north_star: max-abs in normalised action space
+
+
+def _policy(case, max_batch=1):
+    pol = ACTPolicy(policy_args(case), state_dim=case["state_dim"], action_dim=case["action_dim"], max_batch=max_batch)
+    shapes = {k: tuple(v.shape) for k, v in pol.state_dict().items()}
+    pol.load_state_dict(synthetic_state_dict(shapes, seed=case["weight_seed"]), strict=True)
+    return pol
+
+
+@pytest.mark.parametrize("name", ["small", "c1_1cam", "c1_2cam"])
+def test_act_forward_matches_reference_golden(cuda, name):
+    case = ACT_CASES[name]
+    gold = np.load(os.path.join(GOLD, f"act_golden_{name}.npz"))
+    pol = _policy(case)
+    qpos, img_u8 = act_inputs(case)
+    d_qpos = torch.from_numpy(qpos).to(cuda)
+    d_img = torch.from_numpy(img_u8).to(cuda)
+    a_u8 = pol(d_qpos, d_img)                                              # env-layout uint8 fast path
+    torch.cuda.synchronize()
+    eng = pol.engine_for(case["batch"], case["img_h"], case["img_w"], cuda)
+    mem = eng.debug_read(1, case["batch"]).cpu().numpy()
+    d_f32 = (d_img.permute(0, 1, 4, 2, 3).float() * (1.0 / 255.0)).contiguous()   # reference layout (B,Ncam,3,H,W)
+    a_f32 = pol(d_qpos, d_f32)
+    torch.cuda.synchronize()
+    err_u8 = np.abs(a_u8.cpu().numpy() - gold["a_hat"]).max()
+    err_f32 = np.abs(a_f32.cpu().numpy() - gold["a_hat"]).max()
+    if "memory" in gold:
+        merr = np.abs(mem - gold["memory"]).max()
+    else:
+        merr = np.abs(mem.mean(-1) - gold["memory_token_mean"]).max()
+    print(f"[act {name}] a_hat max-abs err: u8 path {err_u8:.3e}, f32 path {err_f32:.3e} (|a|max {np.abs(gold['a_hat']).max():.2f});"
+          f" encoder memory err {merr:.3e}")
+    assert np.isfinite(a_u8.cpu().numpy()).all()
+    assert err_u8 <= ACTION_TOL and err_f32 <= ACTION_TOL
+
+
+def test_batch_invariance_and_partial_batch(cuda):
+    """An episode's result must not depend on which other episodes share the batch (or on max_batch)."""
+    case = dict(ACT_CASES["small"], batch=3)
+    pol = _policy(case, max_batch=8)
+    qpos, img = act_inputs(case)
+    dq, di = torch.from_numpy(qpos).to(cuda), torch.from_numpy(img).to(cuda)
+    full = pol(dq, di).clone()
+    one = pol(dq[1:2].contiguous(), di[1:2].contiguous()).clone()
+    rev = pol(dq.flip(0).contiguous(), di.flip(0).contiguous()).clone()
+    torch.cuda.synchronize()
+    assert torch.equal(full[1:2], one)
+    assert torch.equal(full, rev.flip(0))
+
+
+def test_batched_rollout_matches_oracle(cuda):
+    """B episodes, 25 steps with C = 10 (ring wraps twice): ring slots / counters bit-exact; float64 actions equal the
+    numpy oracle fed with the engine's own chunks; chunks within tolerance of the fp32 oracle network."""
+    from oracle import act_oracle, rollout_oracle
+    from robomanipbaselines_b200.common.batched_rollout import BatchedRollout
+
+    case = dict(ACT_CASES["small"], batch=4)
+    pol = _policy(case, max_batch=4)
+    B, C, Da, Ds = 4, case["chunk_size"], case["action_dim"], case["state_dim"]
+    meta = {"data": {"chunk_size": C}, "state": synthetic_norm_stats(Ds, 1), "action": synthetic_norm_stats(Da, 2, "limits")}
+    br = BatchedRollout(pol, B, meta, device="cuda:0")
+    oracles = [rollout_oracle.ActRolloutOracle(C, Da, meta["action"]) for _ in range(B)]
+    sd = {k: v.cpu() for k, v in pol.state_dict().items()}
+    cfg = policy_args(case)
+    rng = np.random.default_rng(5)
+    n_calls = [0] * B
+    br.reset()
+    for t in range(25):
+        imgs = rng.integers(0, 256, size=(B, case["num_cams"], case["img_h"], case["img_w"], 3), dtype=np.uint8)
+        raw = rng.standard_normal(size=(B, Ds))
+        if t == 13:
+            br.reset([False, True, False, False])
+            oracles[1].reset()
+            n_calls[1] = 0
+        act = br.infer(torch.from_numpy(imgs).to(cuda), torch.from_numpy(raw).to(cuda))
+        torch.cuda.synchronize()
+        chunks = br.chunks.cpu().numpy()
+        qpos_ref = np.concatenate([rollout_oracle.get_state(raw[b], meta["state"]) for b in range(B)])
+        assert np.array_equal(br.qpos.cpu().numpy(), qpos_ref)                     # normalize_data bit-exact
+        if t in (0, 24):                                                           # network parity (fp32 oracle is slow)
+            image = torch.from_numpy(np.concatenate([rollout_oracle.get_images(list(imgs[b])) for b in range(B)]))
+            ref_chunks = act_oracle.act_forward(sd, cfg, torch.from_numpy(qpos_ref), image, live_only=True).numpy()
+            err = np.abs(chunks - ref_chunks).max()
+            print(f"[rollout t={t}] chunk max-abs err vs fp32 oracle {err:.3e}")
+            assert err <= ACTION_TOL
+        for b in range(B):
+            ref = oracles[b].step(chunks[b])
+            n_calls[b] += 1
+            assert np.array_equal(act[b].cpu().numpy(), ref), (t, b)
+            oring, filled = oracles[b].ring_view(n_calls[b])
+            assert np.array_equal(br.ring[b].cpu().numpy()[filled], oring[filled]), (t, b)
+        assert br.step.cpu().tolist() == n_calls
+
+
+def test_engine_rejects_bad_input(cuda):
+    case = ACT_CASES["small"]
+    pol = _policy(case)
+    qpos, img = act_inputs(case)
+    with pytest.raises(RuntimeError):
+        pol(torch.from_numpy(qpos), torch.from_numpy(img))                       # CPU tensors: no fallback
+    with pytest.raises(NotImplementedError):
+        pol(torch.from_numpy(qpos).to(cuda), torch.from_numpy(img).to(cuda), actions=torch.zeros(1))
+    eng = pol.engine_for(case["batch"], case["img_h"], case["img_w"], cuda)
+    with pytest.raises(ValueError):
+        eng.forward(torch.zeros(3, 2, 64, 96, 4, dtype=torch.uint8, device=cuda), torch.from_numpy(qpos).to(cuda))

@@ -1,0 +1,86 @@
+"""CPU tests: the oracle restatements must reproduce the golden vectors produced by the real reference
+(tests/golden/make_golden.py, run in the build container against /root/reference)."""
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(HERE, "golden"))
+
+from cases import ACT_CASES, act_inputs, policy_args  # noqa: E402
+from oracle import act_oracle, rollout_oracle  # noqa: E402
+from robomanipbaselines_b200.common.synthetic import synthetic_state_dict  # noqa: E402
+from robomanipbaselines_b200.policy.act.policy import ACTPolicy  # noqa: E402
+
+GOLD = os.path.join(HERE, "golden")
+
+
+def _case_state_dict(case):
+    shell = ACTPolicy(policy_args(case), state_dim=case["state_dim"], action_dim=case["action_dim"])
+    shapes = {k: tuple(v.shape) for k, v in shell.state_dict().items()}
+    return synthetic_state_dict(shapes, seed=case["weight_seed"])
+
+
+@pytest.mark.parametrize("name", ["small", "c1_1cam", "c1_2cam"])
+def test_act_oracle_matches_reference_golden(name):
+    case = ACT_CASES[name]
+    gold = np.load(os.path.join(GOLD, f"act_golden_{name}.npz"))
+    sd = _case_state_dict(case)
+    assert len(sd) == int(gold["n_keys"][0])
+    wsum = float(sum(v.double().abs().sum() for v in sd.values()))
+    assert abs(wsum - gold["weight_checksum"][0]) <= 1e-9 * wsum      # same synthetic weights as at golden time
+    qpos, img_u8 = act_inputs(case)
+    assert abs(float(np.abs(qpos).sum()) - gold["input_checksum"][0]) < 1e-4
+    assert int(img_u8.astype(np.int64).sum()) == int(gold["input_checksum"][1])
+    image = torch.from_numpy(np.concatenate([rollout_oracle.get_images(list(img_u8[b])) for b in range(case["batch"])]))
+    taps = {}
+    cfg = dict(policy_args(case))
+    a_full = act_oracle.act_forward(sd, cfg, torch.from_numpy(qpos), image, live_only=False, taps=taps)
+    err = np.abs(a_full.numpy() - gold["a_hat"]).max()
+    print(f"[oracle {name}] max-abs vs reference {err:.3e}")
+    assert err <= 2e-5
+    # dead-layer claim: dropping decoder layers 1.. changes nothing
+    a_live = act_oracle.act_forward(sd, cfg, torch.from_numpy(qpos), image, live_only=True)
+    assert torch.equal(a_live, a_full)
+    if "memory" in gold:
+        assert np.abs(taps["memory"].numpy() - gold["memory"]).max() <= 2e-4          # post-LayerNorm, O(1)
+        scale = np.abs(gold["src_tokens"]).max()                                      # raw backbone features
+        assert np.abs(taps["src_tokens"].numpy() - gold["src_tokens"]).max() <= 1e-5 * scale
+    else:
+        assert np.abs(taps["memory"].mean(-1).numpy() - gold["memory_token_mean"]).max() <= 2e-4
+
+
+@pytest.mark.parametrize("norm", ["gaussian", "limits", "legacy"])
+def test_rollout_oracle_matches_reference_golden(norm):
+    g = np.load(os.path.join(GOLD, "rollout_act_golden.npz"))
+    stats = {k: g[f"{norm}_stat_{k}"] for k in ("mean", "std", "min", "range")}
+    if norm == "limits":
+        stats["norm_config"] = {"type": "limits", "out_min": -1.0, "out_max": 1.0}
+    elif norm == "gaussian":
+        stats["norm_config"] = {"type": "gaussian"}
+    chunks = g[f"{norm}_chunks"]
+    T, C, Da = chunks.shape
+    for mode in ("ensemble", "fifo"):
+        o = rollout_oracle.ActRolloutOracle(C, Da, stats, no_temp_ensem=(mode == "fifo"))
+        calls, acts = 0, []
+        for t in range(T):
+            need = o.needs_inference()
+            calls += int(need)
+            acts.append(o.step(chunks[t] if need else None))
+        assert np.array_equal(np.array(acts), g[f"{norm}_{mode}_actions"])          # bit-exact float64
+        assert calls == int(g[f"{norm}_{mode}_calls"][0])
+        if mode == "ensemble":
+            assert np.array_equal(np.array(o.policy_action_buf_history), g[f"{norm}_history"])
+    x = g[f"{norm}_norm_in"]
+    assert np.array_equal(rollout_oracle.normalize_data(x, stats), g[f"{norm}_normalize"])
+    assert np.array_equal(rollout_oracle.denormalize_data(x, stats), g[f"{norm}_denormalize"])
+
+
+def test_get_state_and_images_oracle():
+    g = np.load(os.path.join(GOLD, "rollout_act_golden.npz"))
+    stats = {"mean": g["get_state_mean"], "std": g["get_state_std"], "norm_config": {"type": "gaussian"}}
+    assert np.array_equal(rollout_oracle.get_state(g["get_state_raw"], stats), g["get_state_out"])
+    assert np.array_equal(rollout_oracle.get_images(list(g["get_images_in"])), g["get_images_out"])
