@@ -41,6 +41,9 @@ typedef struct rmb_act_config {
 const char* rmb_last_error(void);
 /* Library version string and a cheap "is this a B200" probe (returns 0 if device `dev` is sm_100). */
 const char* rmb_version(void);
+/* 16-bit storage / tensor-core operand type the library was built with: "fp16" (default) or "bf16". Every `act`
+ * buffer below holds this type; accumulation is always fp32. */
+const char* rmb_act_dtype(void);
 int rmb_check_device(int dev);
 
 /* ---- engine lifetime: replaces ACTPolicy.__init__ (third_party/act/policy.py:10-16) + RolloutBase.load_ckpt
@@ -52,7 +55,7 @@ void rmb_act_engine_destroy(rmb_act_engine_t* e);
  * and ignored (the CVAE encoder, is_pad_head, decoder layers 1..6). */
 int rmb_act_load_tensor(rmb_act_engine_t* e, const char* name, const float* host_data, int64_t numel);
 /* Fold FrozenBatchNorm2d into the conv weights, precompute the input-independent tensors (sine position table,
- * latent token, decoder query projection), upload bf16 weights. Must be called once after all tensors are loaded. */
+ * latent token, decoder query projection), upload 16-bit weights. Must be called once after all tensors are loaded. */
 int rmb_act_finalize(rmb_act_engine_t* e);
 
 /* ---- ACTPolicy.__call__ inference branch (third_party/act/policy.py:18-38) -> DETRVAE.forward
@@ -95,29 +98,29 @@ int rmb_denormalize(const double* d_x, int norm_type, const double* d_p0, const 
                     double* d_y, int64_t rows, int D, void* stream);
 
 /* ---- RolloutBase.get_images (:479-490) + ImageNet normalise (third_party/act/policy.py:20-22) alone:
- * uint8 [n_img, H, W, 3] -> bf16 [n_img, H, W + 8, 4] (4 zero pixels either side, 4th channel zero). */
-int rmb_preprocess_images_u8(const uint8_t* d_images, void* d_out_bf16, int n_img, int H, int W, void* stream);
-int rmb_preprocess_images_f32(const float* d_images_chw, void* d_out_bf16, int n_img, int H, int W, void* stream);
+ * uint8 [n_img, H, W, 3] -> act [n_img, H, W + 8, 4] (4 zero pixels either side, 4th channel zero). */
+int rmb_preprocess_images_u8(const uint8_t* d_images, void* d_out_act, int n_img, int H, int W, void* stream);
+int rmb_preprocess_images_f32(const float* d_images_chw, void* d_out_act, int n_img, int H, int W, void* stream);
 
 /* ---- kernel-level entry points (used by the parity tests; same kernels the engine launches) */
-/* out[M,N] = A[M,K](bf16) * Wt[N,K]^T(bf16) + bias (+ residual) (ReLU); flags: bit0 relu, bit1 out fp32, bit2 residual fp32 */
-int rmb_gemm_bf16(const void* d_A, const void* d_Wt, const float* d_bias, const void* d_residual, void* d_out,
+/* out[M,N] = A[M,K](act) * Wt[N,K]^T(act) + bias (+ residual) (ReLU); flags: bit0 relu, bit1 out fp32, bit2 residual fp32 */
+int rmb_gemm(const void* d_A, const void* d_Wt, const float* d_bias, const void* d_residual, void* d_out,
                   int64_t M, int N, int K, int flags, void* stream);
-/* NHWC bf16 conv k in {1,3}, stride in {1,2}, pad k/2; Wt [Cout, k*k*Cin] tap-major; residual/out [B,OH,OW,Cout] bf16 */
-int rmb_conv2d_nhwc_bf16(const void* d_in, const void* d_Wt, const float* d_bias, const void* d_residual, void* d_out,
+/* NHWC act conv k in {1,3}, stride in {1,2}, pad k/2; Wt [Cout, k*k*Cin] tap-major; residual/out [B,OH,OW,Cout] act */
+int rmb_conv2d_nhwc(const void* d_in, const void* d_Wt, const float* d_bias, const void* d_residual, void* d_out,
                          int B, int H, int W, int Cin, int Cout, int ksize, int stride, int relu, void* stream);
-/* ResNet stem on the padded NHWC4 input: Wt [64, 7*32] (see gemm_plan.h), out [B, H/2, W/2, 64] bf16, ReLU */
-int rmb_conv1_stem_bf16(const void* d_in_padded, const void* d_Wt, const float* d_bias, void* d_out, int B, int H, int W,
+/* ResNet stem on the padded NHWC4 input: Wt [64, 7*32] (see gemm_plan.h), out [B, H/2, W/2, 64] act, ReLU */
+int rmb_conv1_stem(const void* d_in_padded, const void* d_Wt, const float* d_bias, void* d_out, int B, int H, int W,
                         void* stream);
-int rmb_maxpool3x3s2_nhwc_bf16(const void* d_in, void* d_out, int B, int H, int W, int C, void* stream);
-/* softmax(Q K^T / 8) V for 64-wide heads. Q [B*Lq (or Lq if q_shared), ldq], K [B*Lk, ldk], V [B*Lk, ldv], bf16;
- * head h reads columns col0 + 64h; out [B*Lq, ld_out] bf16 */
-int rmb_attention_bf16(const void* d_Q, int ldq, int q_col0, int q_shared, const void* d_K, int ldk, int k_col0,
+int rmb_maxpool3x3s2_nhwc(const void* d_in, void* d_out, int B, int H, int W, int C, void* stream);
+/* softmax(Q K^T / 8) V for 64-wide heads. Q [B*Lq (or Lq if q_shared), ldq], K [B*Lk, ldk], V [B*Lk, ldv], act;
+ * head h reads columns col0 + 64h; out [B*Lq, ld_out] act */
+int rmb_attention(const void* d_Q, int ldq, int q_col0, int q_shared, const void* d_K, int ldk, int k_col0,
                        const void* d_V, int ldv, int v_col0, void* d_out, int ld_out, int B, int n_heads, int Lq, int Lk,
                        void* stream);
-/* LayerNorm over 512 columns: x fp32 [rows,512]; outputs optional (NULL): y fp32, y bf16, bf16(y + pos[row % L]) */
+/* LayerNorm over 512 columns: x fp32 [rows,512]; outputs optional (NULL): y fp32, y act, act(y + pos[row % L]) */
 int rmb_layernorm512(const float* d_x, const float* d_gamma, const float* d_beta, const float* d_pos, int L,
-                     float* d_y_f32, void* d_y_bf16, void* d_ypos_bf16, int64_t rows, int do_norm, void* stream);
+                     float* d_y_f32, void* d_y_act, void* d_ypos_act, int64_t rows, int do_norm, void* stream);
 
 #ifdef __cplusplus
 }

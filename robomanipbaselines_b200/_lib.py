@@ -30,6 +30,7 @@ class ActConfig(ctypes.Structure):
 SIGNATURES = {
     "rmb_last_error": (c_char_p, []),
     "rmb_version": (c_char_p, []),
+    "rmb_act_dtype": (c_char_p, []),
     "rmb_check_device": (c_int, [c_int]),
     "rmb_act_engine_create": (c_int, [POINTER(ActConfig), POINTER(c_void_p)]),
     "rmb_act_engine_destroy": (None, [c_void_p]),
@@ -45,13 +46,13 @@ SIGNATURES = {
     "rmb_denormalize": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_double, c_void_p, c_int64, c_int, c_void_p]),
     "rmb_preprocess_images_u8": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
     "rmb_preprocess_images_f32": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
-    "rmb_gemm_bf16": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int,
+    "rmb_gemm": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int,
                               c_void_p]),
-    "rmb_conv2d_nhwc_bf16": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int,
+    "rmb_conv2d_nhwc": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int,
                                      c_int, c_int, c_int, c_int, c_void_p]),
-    "rmb_conv1_stem_bf16": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
-    "rmb_maxpool3x3s2_nhwc_bf16": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
-    "rmb_attention_bf16": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_int, c_int, c_void_p, c_int, c_int,
+    "rmb_conv1_stem": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
+    "rmb_maxpool3x3s2_nhwc": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
+    "rmb_attention": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_int, c_int, c_void_p, c_int, c_int,
                                    c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p]),
     "rmb_layernorm512": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p,
                                  c_int64, c_int, c_void_p]),
@@ -92,6 +93,13 @@ def ptr(t):
     if t is None:
         return None
     return ctypes.c_void_p(t.data_ptr())
+
+
+def act_torch_dtype():
+    """torch dtype of the library's 16-bit operand type (rmb_act_dtype())."""
+    import torch
+
+    return {"fp16": torch.float16, "bf16": torch.bfloat16}[load().rmb_act_dtype().decode()]
 
 
 def cur_stream():

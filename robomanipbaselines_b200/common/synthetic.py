@@ -3,6 +3,12 @@
 There is no network for checkpoints, so "random-init weights of that architecture" are generated here as a pure
 function of (key name, shape, seed): the same state dict can be rebuilt on any machine and loaded both into the
 reference modules (golden generation) and into this package's policies.
+
+The distributions are chosen so that the network is conditioned like a trained one (BatchNorm-bounded activations,
+unsaturated softmax). With PyTorch's default initialisation the ResNet trunk grows activations ~16x, the attention
+logits reach ~1e3 and the softmax degenerates to an arg-max: the fp32 reference itself then changes its output by
+>1e-2 (measured 3.4e-2 on the "small" case) when only the normalised input image is rounded to bf16, so no reduced-precision engine (nor a reordering of fp32
+sums) could be compared against it at the 1e-2 action tolerance.
 """
 import zlib
 
@@ -22,6 +28,10 @@ def synthetic_tensor(key, shape, seed=0):
     is_bn = (".bn" in key) or (".downsample.1." in key)
     if key.endswith("running_var"):
         return torch.rand(shape, generator=g) + 0.5
+    if key.endswith("bn2.weight"):
+        # small gain on the last BN of every residual branch (cf. torchvision's zero_init_residual): keeps the
+        # activations O(1) through 8 residual blocks, as trained BN statistics do
+        return 0.15 + 0.2 * torch.rand(shape, generator=g)
     if is_bn and key.endswith(".weight"):
         return torch.rand(shape, generator=g) + 0.5
     if is_bn:
@@ -31,6 +41,8 @@ def synthetic_tensor(key, shape, seed=0):
     if len(shape) == 4:
         fan_in = shape[1] * shape[2] * shape[3]
         return torch.randn(shape, generator=g) * (2.0 / fan_in) ** 0.5
+    if key.endswith("in_proj_weight"):
+        return torch.randn(shape, generator=g) * 0.5 * (1.0 / shape[1]) ** 0.5     # moderate attention logits
     if "embed" in key and len(shape) == 2:
         return torch.randn(shape, generator=g) * 0.5
     if len(shape) == 2:

@@ -6,7 +6,6 @@
 // Only the live graph is executed: decoder layers 1..6 and the CVAE encoder never influence a_hat (detr_vae.py:142
 // takes hs[0]); decoder layer 0's self-attention sees tgt = 0, so its output is the constant W_o b_v + b_o.
 #include <cuda.h>
-#include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdint.h>
@@ -48,23 +47,23 @@ bool plan_attention(AttnPlan* a, const void* Q, int ldq, int q_col0, bool q_shar
   {
     const uint64_t dims[3] = {(uint64_t)ldq, (uint64_t)Lq, (uint64_t)(q_shared ? 1 : B)};
     const uint64_t str[2] = {(uint64_t)ldq * 2, (uint64_t)ldq * 2 * Lq};
-    if (!make_tmap_bf16(&a->tq, Q, 3, dims, str, box, 128, err)) return false;
+    if (!make_tmap_act(&a->tq, Q, 3, dims, str, box, 128, err)) return false;
   }
   {
     const uint64_t dims[3] = {(uint64_t)ldk, (uint64_t)Lk, (uint64_t)B};
     const uint64_t str[2] = {(uint64_t)ldk * 2, (uint64_t)ldk * 2 * Lk};
-    if (!make_tmap_bf16(&a->tk, K, 3, dims, str, box, 128, err)) return false;
+    if (!make_tmap_act(&a->tk, K, 3, dims, str, box, 128, err)) return false;
   }
   {
     const uint64_t dims[3] = {(uint64_t)ldv, (uint64_t)Lk, (uint64_t)B};
     const uint64_t str[2] = {(uint64_t)ldv * 2, (uint64_t)ldv * 2 * Lk};
-    if (!make_tmap_bf16(&a->tv, V, 3, dims, str, box, 128, err)) return false;
+    if (!make_tmap_act(&a->tv, V, 3, dims, str, box, 128, err)) return false;
   }
   AttnParams& p = a->p;
   p.Lq = Lq; p.Lk = Lk; p.n_q_tiles = (Lq + 127) / 128; p.n_heads = n_heads;
   p.q_col0 = q_col0; p.k_col0 = k_col0; p.v_col0 = v_col0; p.q_shared = q_shared ? 1 : 0;
   p.scale_log2e = 0.125f * 1.4426950408889634f;
-  p.out = static_cast<__nv_bfloat16*>(out); p.ld_out = ld_out;
+  p.out = static_cast<act_t*>(out); p.ld_out = ld_out;
   a->grid = B * n_heads * p.n_q_tiles;
   return true;
 }
@@ -102,30 +101,30 @@ struct rmb_act_engine {
   int Hf = 0, Wf = 0, L = 0, n_img_max = 0;
 
   // ---- device weights
-  struct ConvW { __nv_bfloat16* w = nullptr; float* b = nullptr; int cin = 0, cout = 0, k = 0, stride = 1; };
+  struct ConvW { act_t* w = nullptr; float* b = nullptr; int cin = 0, cout = 0, k = 0, stride = 1; };
   ConvW stem;
   ConvW blk[4][2][2];      // [layer][block][conv]
   ConvW down[4];           // layer 1..3 (index = layer), layer 0 unused
   ConvW input_proj;
   struct EncW {
-    __nv_bfloat16 *w_qk, *w_v, *w_o, *w_1, *w_2;
+    act_t *w_qk, *w_v, *w_o, *w_1, *w_2;
     float *b_qk, *b_v, *b_o, *b_1, *b_2, *g1, *be1, *g2, *be2;
   };
   std::vector<EncW> enc;
   struct DecW {
-    __nv_bfloat16 *q_const;                 // [C, 512] projected queries (input independent)
-    __nv_bfloat16 *w_k, *w_v, *w_o, *w_1, *w_2;
+    act_t *q_const;                 // [C, 512] projected queries (input independent)
+    act_t *w_k, *w_v, *w_o, *w_1, *w_2;
     float *b_k, *b_v, *b_o_fold, *b_1, *b_2, *g2, *be2, *g3, *be3, *gn, *ben;
   } dec{};
   float *w_head = nullptr, *b_head = nullptr, *w_state = nullptr, *b_state = nullptr, *latent_bias = nullptr;
   float* pos = nullptr;    // [L, 512]
 
   // ---- workspace (sized for max_batch)
-  __nv_bfloat16 *x0 = nullptr, *c1 = nullptr;
-  __nv_bfloat16* stage[4][3] = {};
+  act_t *x0 = nullptr, *c1 = nullptr;
+  act_t* stage[4][3] = {};
   float *tok_f32 = nullptr, *y_f32 = nullptr, *x1_f32 = nullptr;
-  __nv_bfloat16 *tok_b = nullptr, *tok_pb = nullptr, *qk = nullptr, *v = nullptr, *ao = nullptr, *x1_b = nullptr, *hh = nullptr;
-  __nv_bfloat16 *kd = nullptr, *vd = nullptr, *aod = nullptr, *t_b = nullptr, *hd = nullptr;
+  act_t *tok_b = nullptr, *tok_pb = nullptr, *qk = nullptr, *v = nullptr, *ao = nullptr, *x1_b = nullptr, *hh = nullptr;
+  act_t *kd = nullptr, *vd = nullptr, *aod = nullptr, *t_b = nullptr, *hd = nullptr;
   float *yd = nullptr, *t_f32 = nullptr, *yd2 = nullptr;
 
   struct BatchPlans {
@@ -167,12 +166,12 @@ bool upload_f32(rmb_act_engine* e, const std::vector<float>& h, float** d, std::
   if (cudaMemcpy(*d, h.data(), h.size() * sizeof(float), cudaMemcpyHostToDevice) != cudaSuccess) { *err = "cudaMemcpy H2D failed"; return false; }
   return true;
 }
-bool upload_bf16(rmb_act_engine* e, const std::vector<float>& h, __nv_bfloat16** d, std::string* err) {
-  std::vector<__nv_bfloat16> t(h.size());
-  for (size_t i = 0; i < h.size(); ++i) t[i] = __float2bfloat16_rn(h[i]);
-  *d = e->dalloc<__nv_bfloat16>(h.size());
+bool upload_act(rmb_act_engine* e, const std::vector<float>& h, act_t** d, std::string* err) {
+  std::vector<act_t> t(h.size());
+  for (size_t i = 0; i < h.size(); ++i) t[i] = to_act(h[i]);
+  *d = e->dalloc<act_t>(h.size());
   if (!*d) { *err = "cudaMalloc failed (weights)"; return false; }
-  if (cudaMemcpy(*d, t.data(), t.size() * sizeof(__nv_bfloat16), cudaMemcpyHostToDevice) != cudaSuccess) { *err = "cudaMemcpy H2D failed"; return false; }
+  if (cudaMemcpy(*d, t.data(), t.size() * sizeof(act_t), cudaMemcpyHostToDevice) != cudaSuccess) { *err = "cudaMemcpy H2D failed"; return false; }
   return true;
 }
 
@@ -204,7 +203,7 @@ bool make_conv(rmb_act_engine* e, const std::string& conv, const std::string& bn
         for (int kw = 0; kw < k; ++kw)
           r[(((size_t)co * k + kh) * k + kw) * cin + ci] = (*w)[(((size_t)co * cin + ci) * k + kh) * k + kw] * scale[co];
   out->cin = cin; out->cout = cout; out->k = k; out->stride = stride;
-  return upload_bf16(e, r, &out->w, err) && upload_f32(e, bias, &out->b, err);
+  return upload_act(e, r, &out->w, err) && upload_f32(e, bias, &out->b, err);
 }
 
 void layernorm_host(const std::vector<double>& x, const std::vector<float>& g, const std::vector<float>& b, std::vector<double>* y) {
@@ -222,7 +221,8 @@ void layernorm_host(const std::vector<double>& x, const std::vector<float>& g, c
 extern "C" {
 
 const char* rmb_last_error(void) { return g_last_error.c_str(); }
-const char* rmb_version(void) { return "rmb_b200 0.1 (sm_100a)"; }
+const char* rmb_version(void) { return "rmb_b200 0.1 (sm_100a, " RMB_ACT_DTYPE_NAME " operands, fp32 accumulate)"; }
+const char* rmb_act_dtype(void) { return RMB_ACT_DTYPE_NAME; }
 
 int rmb_check_device(int dev) {
   cudaDeviceProp prop;
@@ -290,7 +290,7 @@ int rmb_act_finalize(rmb_act_engine_t* e) {
           for (int kw = 0; kw < 7; ++kw)
             r[((co * 7 + kh) * 8 + (kw + 1)) * 4 + ci] = (*w)[((co * 3 + ci) * 7 + kh) * 7 + kw] * scale[co];
     e->stem.cin = 3; e->stem.cout = 64; e->stem.k = 7; e->stem.stride = 2;
-    if (!upload_bf16(e, r, &e->stem.w, &err) || !upload_f32(e, bias, &e->stem.b, &err)) return fail(err);
+    if (!upload_act(e, r, &e->stem.w, &err) || !upload_f32(e, bias, &e->stem.b, &err)) return fail(err);
   }
   const int chans[4] = {64, 128, 256, 512};
   for (int li = 0; li < 4; ++li)
@@ -308,7 +308,7 @@ int rmb_act_finalize(rmb_act_engine_t* e) {
     const auto* w = find_w(e, "model.input_proj.weight", (size_t)D * 512, &err); if (!w) return fail(err);
     const auto* b = find_w(e, "model.input_proj.bias", D, &err); if (!b) return fail(err);
     e->input_proj.cin = 512; e->input_proj.cout = D; e->input_proj.k = 1; e->input_proj.stride = 1;
-    if (!upload_bf16(e, *w, &e->input_proj.w, &err) || !upload_f32(e, *b, &e->input_proj.b, &err)) return fail(err);
+    if (!upload_act(e, *w, &e->input_proj.w, &err) || !upload_f32(e, *b, &e->input_proj.b, &err)) return fail(err);
   }
 
   // ---- encoder layers (transformer.py:143-197)
@@ -330,8 +330,8 @@ int rmb_act_finalize(rmb_act_engine_t* e) {
     rmb_act_engine::EncW& w = e->enc[l];
     std::vector<float> wqk(wi->begin(), wi->begin() + (size_t)2 * D * D), wv(wi->begin() + (size_t)2 * D * D, wi->end());
     std::vector<float> bqk(bi->begin(), bi->begin() + 2 * D), bv(bi->begin() + 2 * D, bi->end());
-    if (!upload_bf16(e, wqk, &w.w_qk, &err) || !upload_bf16(e, wv, &w.w_v, &err) || !upload_bf16(e, *wo, &w.w_o, &err) ||
-        !upload_bf16(e, *w1, &w.w_1, &err) || !upload_bf16(e, *w2, &w.w_2, &err) || !upload_f32(e, bqk, &w.b_qk, &err) ||
+    if (!upload_act(e, wqk, &w.w_qk, &err) || !upload_act(e, wv, &w.w_v, &err) || !upload_act(e, *wo, &w.w_o, &err) ||
+        !upload_act(e, *w1, &w.w_1, &err) || !upload_act(e, *w2, &w.w_2, &err) || !upload_f32(e, bqk, &w.b_qk, &err) ||
         !upload_f32(e, bv, &w.b_v, &err) || !upload_f32(e, *bo, &w.b_o, &err) || !upload_f32(e, *b1, &w.b_1, &err) ||
         !upload_f32(e, *b2, &w.b_2, &err) || !upload_f32(e, *g1, &w.g1, &err) || !upload_f32(e, *be1, &w.be1, &err) ||
         !upload_f32(e, *g2, &w.g2, &err) || !upload_f32(e, *be2, &w.be2, &err))
@@ -382,8 +382,8 @@ int rmb_act_finalize(rmb_act_engine_t* e) {
     std::vector<float> bo_fold(D);
     for (int i = 0; i < D; ++i) bo_fold[i] = (float)((double)(*bo)[i] + tgt1[i]);   // residual tgt1 folded into the bias
     auto& d = e->dec;
-    if (!upload_bf16(e, qc, &d.q_const, &err) || !upload_bf16(e, wk, &d.w_k, &err) || !upload_bf16(e, wv, &d.w_v, &err) ||
-        !upload_bf16(e, *wo, &d.w_o, &err) || !upload_bf16(e, *w1, &d.w_1, &err) || !upload_bf16(e, *w2, &d.w_2, &err) ||
+    if (!upload_act(e, qc, &d.q_const, &err) || !upload_act(e, wk, &d.w_k, &err) || !upload_act(e, wv, &d.w_v, &err) ||
+        !upload_act(e, *wo, &d.w_o, &err) || !upload_act(e, *w1, &d.w_1, &err) || !upload_act(e, *w2, &d.w_2, &err) ||
         !upload_f32(e, bk, &d.b_k, &err) || !upload_f32(e, bv, &d.b_v, &err) || !upload_f32(e, bo_fold, &d.b_o_fold, &err) ||
         !upload_f32(e, *b1, &d.b_1, &err) || !upload_f32(e, *b2, &d.b_2, &err) || !upload_f32(e, *g2, &d.g2, &err) ||
         !upload_f32(e, *be2, &d.be2, &err) || !upload_f32(e, *g3, &d.g3, &err) || !upload_f32(e, *be3, &d.be3, &err) ||
@@ -430,26 +430,26 @@ int rmb_act_finalize(rmb_act_engine_t* e) {
     const size_t NI = e->n_img_max, H = c.img_h, W = c.img_w;
     const size_t BL = (size_t)c.max_batch * e->L, BC = (size_t)c.max_batch * C;
     bool ok = true;
-    ok &= (e->x0 = e->dalloc<__nv_bfloat16>(NI * H * (W + 8) * 4)) != nullptr;
-    ok &= (e->c1 = e->dalloc<__nv_bfloat16>(NI * (H / 2) * (W / 2) * 64)) != nullptr;
+    ok &= (e->x0 = e->dalloc<act_t>(NI * H * (W + 8) * 4)) != nullptr;
+    ok &= (e->c1 = e->dalloc<act_t>(NI * (H / 2) * (W / 2) * 64)) != nullptr;
     for (int li = 0; li < 4; ++li)
       for (int k = 0; k < 3; ++k)
-        ok &= (e->stage[li][k] = e->dalloc<__nv_bfloat16>(NI * (H >> (2 + li)) * (W >> (2 + li)) * chans[li])) != nullptr;
+        ok &= (e->stage[li][k] = e->dalloc<act_t>(NI * (H >> (2 + li)) * (W >> (2 + li)) * chans[li])) != nullptr;
     ok &= (e->tok_f32 = e->dalloc<float>(BL * D)) != nullptr;
     ok &= (e->y_f32 = e->dalloc<float>(BL * D)) != nullptr;
     ok &= (e->x1_f32 = e->dalloc<float>(BL * D)) != nullptr;
-    ok &= (e->tok_b = e->dalloc<__nv_bfloat16>(BL * D)) != nullptr;
-    ok &= (e->tok_pb = e->dalloc<__nv_bfloat16>(BL * D)) != nullptr;
-    ok &= (e->qk = e->dalloc<__nv_bfloat16>(BL * 2 * D)) != nullptr;
-    ok &= (e->v = e->dalloc<__nv_bfloat16>(BL * D)) != nullptr;
-    ok &= (e->ao = e->dalloc<__nv_bfloat16>(BL * D)) != nullptr;
-    ok &= (e->x1_b = e->dalloc<__nv_bfloat16>(BL * D)) != nullptr;
-    ok &= (e->hh = e->dalloc<__nv_bfloat16>(BL * FF)) != nullptr;
-    ok &= (e->kd = e->dalloc<__nv_bfloat16>(BL * D)) != nullptr;
-    ok &= (e->vd = e->dalloc<__nv_bfloat16>(BL * D)) != nullptr;
-    ok &= (e->aod = e->dalloc<__nv_bfloat16>(BC * D)) != nullptr;
-    ok &= (e->t_b = e->dalloc<__nv_bfloat16>(BC * D)) != nullptr;
-    ok &= (e->hd = e->dalloc<__nv_bfloat16>(BC * FF)) != nullptr;
+    ok &= (e->tok_b = e->dalloc<act_t>(BL * D)) != nullptr;
+    ok &= (e->tok_pb = e->dalloc<act_t>(BL * D)) != nullptr;
+    ok &= (e->qk = e->dalloc<act_t>(BL * 2 * D)) != nullptr;
+    ok &= (e->v = e->dalloc<act_t>(BL * D)) != nullptr;
+    ok &= (e->ao = e->dalloc<act_t>(BL * D)) != nullptr;
+    ok &= (e->x1_b = e->dalloc<act_t>(BL * D)) != nullptr;
+    ok &= (e->hh = e->dalloc<act_t>(BL * FF)) != nullptr;
+    ok &= (e->kd = e->dalloc<act_t>(BL * D)) != nullptr;
+    ok &= (e->vd = e->dalloc<act_t>(BL * D)) != nullptr;
+    ok &= (e->aod = e->dalloc<act_t>(BC * D)) != nullptr;
+    ok &= (e->t_b = e->dalloc<act_t>(BC * D)) != nullptr;
+    ok &= (e->hd = e->dalloc<act_t>(BC * FF)) != nullptr;
     ok &= (e->yd = e->dalloc<float>(BC * D)) != nullptr;
     ok &= (e->t_f32 = e->dalloc<float>(BC * D)) != nullptr;
     ok &= (e->yd2 = e->dalloc<float>(BC * D)) != nullptr;
@@ -473,8 +473,8 @@ static int build_plans(rmb_act_engine* e, int nb, rmb_act_engine::BatchPlans** o
   // stage buffers: [0] = t (mid), [1] = y (block 0 out), [2] = d (downsample) then z (block 1 out)
   for (int li = 0; li < 4; ++li) {
     const int h = H >> (2 + li), w = W >> (2 + li);
-    const __nv_bfloat16* x_in = (li == 0) ? e->stage[0][2] /* maxpool output lives in stage[0][2] */ : e->stage[li - 1][2];
-    __nv_bfloat16 *t = e->stage[li][0], *y = e->stage[li][1], *z = e->stage[li][2];
+    const act_t* x_in = (li == 0) ? e->stage[0][2] /* maxpool output lives in stage[0][2] */ : e->stage[li - 1][2];
+    act_t *t = e->stage[li][0], *y = e->stage[li][1], *z = e->stage[li][2];
     const int hin = (li == 0) ? h : h * 2, win = (li == 0) ? w : w * 2;
     const int cin = (li == 0) ? 64 : chans[li - 1];
     const void* identity = x_in;
@@ -657,7 +657,7 @@ int rmb_preprocess_images_u8(const uint8_t* d_images, void* d_out, int n_img, in
   if (W % 4 != 0) return fail("rmb_preprocess_images_u8: W must be a multiple of 4");
   const long long items = (long long)n_img * H * (W / 4 + 2);
   preprocess_u8_kernel<<<grid_for(items, 256, 148), 256, 0, static_cast<cudaStream_t>(stream_)>>>(
-      d_images, static_cast<__nv_bfloat16*>(d_out), n_img, H, W, make_float3(0.485f, 0.456f, 0.406f),
+      d_images, static_cast<act_t*>(d_out), n_img, H, W, make_float3(0.485f, 0.456f, 0.406f),
       make_float3(1.0f / 0.229f, 1.0f / 0.224f, 1.0f / 0.225f));
   RMB_CUDA(cudaGetLastError());
   return 0;
@@ -668,7 +668,7 @@ int rmb_preprocess_images_f32(const float* d_images, void* d_out, int n_img, int
   if (W % 4 != 0) return fail("rmb_preprocess_images_f32: W must be a multiple of 4");
   const long long items = (long long)n_img * H * (W / 4 + 2);
   preprocess_f32_kernel<<<grid_for(items, 256, 148), 256, 0, static_cast<cudaStream_t>(stream_)>>>(
-      d_images, static_cast<__nv_bfloat16*>(d_out), n_img, H, W, make_float3(0.485f, 0.456f, 0.406f),
+      d_images, static_cast<act_t*>(d_out), n_img, H, W, make_float3(0.485f, 0.456f, 0.406f),
       make_float3(1.0f / 0.229f, 1.0f / 0.224f, 1.0f / 0.225f));
   RMB_CUDA(cudaGetLastError());
   return 0;
@@ -680,9 +680,9 @@ static int device_sms() {
   return sms;
 }
 
-int rmb_gemm_bf16(const void* d_A, const void* d_Wt, const float* d_bias, const void* d_residual, void* d_out,
+int rmb_gemm(const void* d_A, const void* d_Wt, const float* d_bias, const void* d_residual, void* d_out,
                   int64_t M, int N, int K, int flags, void* stream_) {
-  if (!d_A || !d_Wt || !d_out) return fail("rmb_gemm_bf16: null argument");
+  if (!d_A || !d_Wt || !d_out) return fail("rmb_gemm: null argument");
   GemmPlan g;
   std::string err;
   if (!plan_linear(&g, d_A, M, K, K, d_Wt, N, d_bias, d_residual, N, (flags & 4) != 0, d_out, N, (flags & 2) != 0, (flags & 1) != 0, &err)) return fail(err);
@@ -690,9 +690,9 @@ int rmb_gemm_bf16(const void* d_A, const void* d_Wt, const float* d_bias, const 
   return 0;
 }
 
-int rmb_conv2d_nhwc_bf16(const void* d_in, const void* d_Wt, const float* d_bias, const void* d_residual, void* d_out,
+int rmb_conv2d_nhwc(const void* d_in, const void* d_Wt, const float* d_bias, const void* d_residual, void* d_out,
                          int B, int H, int W, int Cin, int Cout, int ksize, int stride, int relu, void* stream_) {
-  if (!d_in || !d_Wt || !d_out) return fail("rmb_conv2d_nhwc_bf16: null argument");
+  if (!d_in || !d_Wt || !d_out) return fail("rmb_conv2d_nhwc: null argument");
   GemmPlan g;
   std::string err;
   if (!plan_conv(&g, d_in, B, H, W, Cin, ksize, stride, d_Wt, Cout, d_bias, d_residual, false, d_out, Cout, false, relu != 0, &err)) return fail(err);
@@ -700,9 +700,9 @@ int rmb_conv2d_nhwc_bf16(const void* d_in, const void* d_Wt, const float* d_bias
   return 0;
 }
 
-int rmb_conv1_stem_bf16(const void* d_in_padded, const void* d_Wt, const float* d_bias, void* d_out, int B, int H, int W,
+int rmb_conv1_stem(const void* d_in_padded, const void* d_Wt, const float* d_bias, void* d_out, int B, int H, int W,
                         void* stream_) {
-  if (!d_in_padded || !d_Wt || !d_out) return fail("rmb_conv1_stem_bf16: null argument");
+  if (!d_in_padded || !d_Wt || !d_out) return fail("rmb_conv1_stem: null argument");
   GemmPlan g;
   std::string err;
   if (!plan_conv1(&g, d_in_padded, B, H, W, d_Wt, d_bias, d_out, &err)) return fail(err);
@@ -710,20 +710,20 @@ int rmb_conv1_stem_bf16(const void* d_in_padded, const void* d_Wt, const float* 
   return 0;
 }
 
-int rmb_maxpool3x3s2_nhwc_bf16(const void* d_in, void* d_out, int B, int H, int W, int C, void* stream_) {
-  if (!d_in || !d_out) return fail("rmb_maxpool3x3s2_nhwc_bf16: null argument");
-  if (C % 8 != 0) return fail("rmb_maxpool3x3s2_nhwc_bf16: C must be a multiple of 8");
+int rmb_maxpool3x3s2_nhwc(const void* d_in, void* d_out, int B, int H, int W, int C, void* stream_) {
+  if (!d_in || !d_out) return fail("rmb_maxpool3x3s2_nhwc: null argument");
+  if (C % 8 != 0) return fail("rmb_maxpool3x3s2_nhwc: C must be a multiple of 8");
   const long long items = (long long)B * ((H + 1) / 2) * ((W + 1) / 2) * (C / 8);
   maxpool3x3s2_kernel<<<grid_for(items, 256, 148), 256, 0, static_cast<cudaStream_t>(stream_)>>>(
-      static_cast<const __nv_bfloat16*>(d_in), static_cast<__nv_bfloat16*>(d_out), B, H, W, C);
+      static_cast<const act_t*>(d_in), static_cast<act_t*>(d_out), B, H, W, C);
   RMB_CUDA(cudaGetLastError());
   return 0;
 }
 
-int rmb_attention_bf16(const void* d_Q, int ldq, int q_col0, int q_shared, const void* d_K, int ldk, int k_col0,
+int rmb_attention(const void* d_Q, int ldq, int q_col0, int q_shared, const void* d_K, int ldk, int k_col0,
                        const void* d_V, int ldv, int v_col0, void* d_out, int ld_out, int B, int n_heads, int Lq, int Lk,
                        void* stream_) {
-  if (!d_Q || !d_K || !d_V || !d_out) return fail("rmb_attention_bf16: null argument");
+  if (!d_Q || !d_K || !d_V || !d_out) return fail("rmb_attention: null argument");
   AttnPlan a;
   std::string err;
   if (!plan_attention(&a, d_Q, ldq, q_col0, q_shared != 0, d_K, ldk, k_col0, d_V, ldv, v_col0, d_out, ld_out, B, n_heads, Lq, Lk, &err)) return fail(err);
@@ -732,13 +732,13 @@ int rmb_attention_bf16(const void* d_Q, int ldq, int q_col0, int q_shared, const
 }
 
 int rmb_layernorm512(const float* d_x, const float* d_gamma, const float* d_beta, const float* d_pos, int L,
-                     float* d_y_f32, void* d_y_bf16, void* d_ypos_bf16, int64_t rows, int do_norm, void* stream_) {
+                     float* d_y_f32, void* d_y_act, void* d_ypos_act, int64_t rows, int do_norm, void* stream_) {
   if (!d_x) return fail("rmb_layernorm512: null argument");
   if (do_norm && (!d_gamma || !d_beta)) return fail("rmb_layernorm512: gamma/beta required");
-  if (d_ypos_bf16 && (!d_pos || L < 1)) return fail("rmb_layernorm512: pos table required");
+  if (d_ypos_act && (!d_pos || L < 1)) return fail("rmb_layernorm512: pos table required");
   layernorm512_kernel<<<grid_for(rows * 32, 256, 148), 256, 0, static_cast<cudaStream_t>(stream_)>>>(
-      d_x, d_gamma, d_beta, d_pos, L < 1 ? 1 : L, d_y_f32, static_cast<__nv_bfloat16*>(d_y_bf16),
-      static_cast<__nv_bfloat16*>(d_ypos_bf16), rows, do_norm, 1e-5f);
+      d_x, d_gamma, d_beta, d_pos, L < 1 ? 1 : L, d_y_f32, static_cast<act_t*>(d_y_act),
+      static_cast<act_t*>(d_ypos_act), rows, do_norm, 1e-5f);
   RMB_CUDA(cudaGetLastError());
   return 0;
 }

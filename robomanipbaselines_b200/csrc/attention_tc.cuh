@@ -5,7 +5,7 @@
 // Sequence lengths here are short (S = 2 + 300*Ncam = 302..902 keys), so the softmax is done in two sweeps over the
 // keys instead of an online-rescaled single sweep:
 //   sweep 0: S = Q K^T per 128-key block (tcgen05.mma, fp32 in TMEM) -> exact row maximum
-//   sweep 1: S again, P = exp2((S - max) * scale*log2e) -> bf16 P tile in swizzled smem -> O += P V (tcgen05.mma)
+//   sweep 1: S again, P = exp2((S - max) * scale*log2e) -> 16-bit P tile in swizzled smem -> O += P V (tcgen05.mma)
 // No accumulator rescaling is ever needed, and every thread owns exactly one query row (TMEM lane), so row max / row sum
 // are thread-local. K/V tiles arrive by TMA (SWIZZLE_128B), double-buffered one block ahead.
 //   Q: K-major A operand [128 q x 64 d];  K: K-major B operand [128 kv x 64 d];
@@ -23,7 +23,7 @@ struct AttnParams {
   int q_col0, k_col0, v_col0;   // first column of head 0 inside the Q / K / V source matrices
   int q_shared;        // 1: Q is the same [Lq, *] matrix for every episode (decoder: input-independent queries)
   float scale_log2e;   // (1/sqrt(64)) * log2(e)
-  __nv_bfloat16* out;  // [B*Lq, ld_out], head h at columns h*64
+  act_t* out;  // [B*Lq, ld_out], head h at columns h*64
   int ld_out;
 };
 
@@ -72,8 +72,8 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
   const uint32_t tmem_O = tmem_base + 128;    // 64 fp32 columns
   const uint32_t lane_off = static_cast<uint32_t>(warp * 32) << 16;
 
-  constexpr uint32_t kIdescS = make_idesc_bf16(128, 128, false, false);   // S[128 q,128 kv] = Q * K^T
-  constexpr uint32_t kIdescO = make_idesc_bf16(128, 64, false, true);     // O[128 q, 64 d] = P * V (V is MN-major)
+  constexpr uint32_t kIdescS = make_idesc_f16(128, 128, false, false);   // S[128 q,128 kv] = Q * K^T
+  constexpr uint32_t kIdescO = make_idesc_f16(128, 64, false, true);     // O[128 q, 64 d] = P * V (V is MN-major)
 
   auto issue_load = [&](int g) {
     const int sweep = g / nkt, kt = g % nkt, st = g & 1;
@@ -104,7 +104,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
       const uint32_t qa = smem_u32(sQ), ka = smem_u32(sK + st * 16384);
 #pragma unroll
       for (int k = 0; k < 4; ++k)
-        umma_bf16_ss(tmem_S, make_smem_desc(qa + k * 32, 0, 1024, 2), make_smem_desc(ka + k * 32, 0, 1024, 2), kIdescS,
+        umma_f16_ss(tmem_S, make_smem_desc(qa + k * 32, 0, 1024, 2), make_smem_desc(ka + k * 32, 0, 1024, 2), kIdescS,
                      k != 0);
       umma_commit(s_bar);
     }
@@ -133,9 +133,9 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
         for (int i = 0; i < 32; i += 2) {
           float p0 = (kv_base + c + i < p.Lk) ? fast_exp2(__uint_as_float(v[i]) * p.scale_log2e - mscaled) : 0.f;
           float p1 = (kv_base + c + i + 1 < p.Lk) ? fast_exp2(__uint_as_float(v[i + 1]) * p.scale_log2e - mscaled) : 0.f;
-          __nv_bfloat162 h2 = __floats2bfloat162_rn(p0, p1);
-          row_sum += __low2float(h2) + __high2float(h2);   // normalise by what the MMA will actually see
-          pk[i >> 1] = *reinterpret_cast<uint32_t*>(&h2);
+          pk[i >> 1] = pack_act2(p0, p1);
+          const float2 pr = unpack_act2(pk[i >> 1]);
+          row_sum += pr.x + pr.y;                          // normalise by what the MMA will actually see
         }
         // row `tid` of P, key columns [c, c+32): 4 x 16-byte chunks, 128B-swizzled inside its 64-key atom
         const int atom = c >> 6;
@@ -158,7 +158,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
       for (int k = 0; k < 8; ++k) {
         const uint64_t dp = make_smem_desc(pa + (k >> 2) * 16384 + (k & 3) * 32, 0, 1024, 2);
         const uint64_t dv = make_smem_desc(va + k * 2048, 0, 1024, 2);   // 16 keys = 2 groups of 8 x 128 B rows
-        umma_bf16_ss(tmem_O, dp, dv, kIdescO, (kt | k) != 0);
+        umma_f16_ss(tmem_O, dp, dv, kIdescO, (kt | k) != 0);
       }
       umma_commit(o_bar);
     }
@@ -168,7 +168,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
 
   const int q = qt * 128 + tid;
   const float inv = 1.0f / row_sum;
-  __nv_bfloat16* orow = p.out + (static_cast<long long>(b) * p.Lq + q) * p.ld_out + head * 64;
+  act_t* orow = p.out + (static_cast<long long>(b) * p.Lq + q) * p.ld_out + head * 64;
 #pragma unroll 1
   for (int c = 0; c < 64; c += 32) {
     uint32_t v[32];
@@ -178,10 +178,10 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
 #pragma unroll
       for (int i = 0; i < 4; ++i)
         reinterpret_cast<uint4*>(orow + c)[i] =
-            make_uint4(pack_bf16x2(__uint_as_float(v[8 * i]) * inv, __uint_as_float(v[8 * i + 1]) * inv),
-                       pack_bf16x2(__uint_as_float(v[8 * i + 2]) * inv, __uint_as_float(v[8 * i + 3]) * inv),
-                       pack_bf16x2(__uint_as_float(v[8 * i + 4]) * inv, __uint_as_float(v[8 * i + 5]) * inv),
-                       pack_bf16x2(__uint_as_float(v[8 * i + 6]) * inv, __uint_as_float(v[8 * i + 7]) * inv));
+            make_uint4(pack_act2(__uint_as_float(v[8 * i]) * inv, __uint_as_float(v[8 * i + 1]) * inv),
+                       pack_act2(__uint_as_float(v[8 * i + 2]) * inv, __uint_as_float(v[8 * i + 3]) * inv),
+                       pack_act2(__uint_as_float(v[8 * i + 4]) * inv, __uint_as_float(v[8 * i + 5]) * inv),
+                       pack_act2(__uint_as_float(v[8 * i + 6]) * inv, __uint_as_float(v[8 * i + 7]) * inv));
     }
   }
   tc_fence_before();

@@ -1,24 +1,25 @@
 // Memory-bound kernels of the ACT rollout path (coalesced, vectorised, warp-shuffle; no tensor cores).
 //   preprocess_u8 / preprocess_f32 : RolloutBase.get_images (common/base/RolloutBase.py:479-490) + ACTPolicy's ImageNet
-//                                    normalise (third_party/act/policy.py:20-22), written as padded NHWC4 bf16 for conv1
+//                                    normalise (third_party/act/policy.py:20-22), written as padded NHWC4 act_t for conv1
 //   maxpool3x3s2                   : torchvision resnet18 maxpool (via backbone.py:86-96)
 //   layernorm_rows                 : nn.LayerNorm after each transformer sub-block (transformer.py:166-179,229-250)
 //   act_head                       : norm3 -> decoder.norm -> action_head (transformer.py:129-139, detr_vae.py:148)
 //   ensemble_step                  : temporal ensembling + denormalise (policy/act/RolloutAct.py:68-101, DataUtils.py:26-40)
 //   normalize_state                : normalize_data (common/utils/DataUtils.py:9-23) + f64->f32 cast (RolloutBase.py:474-475)
 #pragma once
-#include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
+
+#include "ptx.cuh"
 
 namespace rmb {
 
 constexpr int kConv1PadPixels = 4;  // zero pixels on each side of a row in the padded NHWC4 conv1 input
 
 // ---------------------------------------------------------------------------------------------------------------------
-// uint8 HWC image -> normalised bf16, 4 channels (4th = 0), row pitch (W + 8) pixels with 4 zero pixels either side.
+// uint8 HWC image -> normalised 16-bit (act_t), 4 channels (4th = 0), row pitch (W + 8) pixels with 4 zero pixels either side.
 // One thread = 4 pixels (12 input bytes as 3 x u32, 32 output bytes as 2 x uint4).
-__global__ void preprocess_u8_kernel(const uint8_t* __restrict__ in, __nv_bfloat16* __restrict__ out, int n_img, int H,
+__global__ void preprocess_u8_kernel(const uint8_t* __restrict__ in, act_t* __restrict__ out, int n_img, int H,
                                      int W, float3 mean, float3 inv_std) {
   const int quads_per_row = W / 4 + 2;  // incl. one zero quad on each side
   const long long total = static_cast<long long>(n_img) * H * quads_per_row;
@@ -42,10 +43,8 @@ __global__ void preprocess_u8_kernel(const uint8_t* __restrict__ in, __nv_bfloat
         const float r = (static_cast<float>(px[3 * p + 0]) * k255 - mean.x) * inv_std.x;
         const float g = (static_cast<float>(px[3 * p + 1]) * k255 - mean.y) * inv_std.y;
         const float bl = (static_cast<float>(px[3 * p + 2]) * k255 - mean.z) * inv_std.z;
-        __nv_bfloat162 rg = __floats2bfloat162_rn(r, g);
-        __nv_bfloat162 b0 = __floats2bfloat162_rn(bl, 0.0f);
-        w[2 * p] = *reinterpret_cast<uint32_t*>(&rg);
-        w[2 * p + 1] = *reinterpret_cast<uint32_t*>(&b0);
+        w[2 * p] = pack_act2(r, g);
+        w[2 * p + 1] = pack_act2(bl, 0.0f);
       }
       o0 = make_uint4(w[0], w[1], w[2], w[3]);
       o1 = make_uint4(w[4], w[5], w[6], w[7]);
@@ -56,8 +55,8 @@ __global__ void preprocess_u8_kernel(const uint8_t* __restrict__ in, __nv_bfloat
   }
 }
 
-// float32 CHW image in [0,1] (the reference nn.Module's input) -> same padded NHWC4 bf16 layout.
-__global__ void preprocess_f32_kernel(const float* __restrict__ in, __nv_bfloat16* __restrict__ out, int n_img, int H,
+// float32 CHW image in [0,1] (the reference nn.Module's input) -> same padded NHWC4 act_t layout.
+__global__ void preprocess_f32_kernel(const float* __restrict__ in, act_t* __restrict__ out, int n_img, int H,
                                       int W, float3 mean, float3 inv_std) {
   const int quads_per_row = W / 4 + 2;
   const long long total = static_cast<long long>(n_img) * H * quads_per_row;
@@ -78,10 +77,8 @@ __global__ void preprocess_f32_kernel(const float* __restrict__ in, __nv_bfloat1
       uint32_t w[8];
 #pragma unroll
       for (int p = 0; p < 4; ++p) {
-        __nv_bfloat162 rg = __floats2bfloat162_rn((rr[p] - mean.x) * inv_std.x, (gg[p] - mean.y) * inv_std.y);
-        __nv_bfloat162 b0 = __floats2bfloat162_rn((bb[p] - mean.z) * inv_std.z, 0.0f);
-        w[2 * p] = *reinterpret_cast<uint32_t*>(&rg);
-        w[2 * p + 1] = *reinterpret_cast<uint32_t*>(&b0);
+        w[2 * p] = pack_act2((rr[p] - mean.x) * inv_std.x, (gg[p] - mean.y) * inv_std.y);
+        w[2 * p + 1] = pack_act2((bb[p] - mean.z) * inv_std.z, 0.0f);
       }
       o0 = make_uint4(w[0], w[1], w[2], w[3]);
       o1 = make_uint4(w[4], w[5], w[6], w[7]);
@@ -93,12 +90,8 @@ __global__ void preprocess_f32_kernel(const float* __restrict__ in, __nv_bfloat1
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
-// 3x3 stride-2 pad-1 max-pool, NHWC bf16. One thread = 8 channels (16 B) of one output pixel.
-__device__ __forceinline__ uint32_t bf162_max(uint32_t a, uint32_t b) {
-  __nv_bfloat162 r = __hmax2(*reinterpret_cast<__nv_bfloat162*>(&a), *reinterpret_cast<__nv_bfloat162*>(&b));
-  return *reinterpret_cast<uint32_t*>(&r);
-}
-__global__ void maxpool3x3s2_kernel(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict__ out, int n_img,
+// 3x3 stride-2 pad-1 max-pool, NHWC act_t. One thread = 8 channels (16 B) of one output pixel.
+__global__ void maxpool3x3s2_kernel(const act_t* __restrict__ in, act_t* __restrict__ out, int n_img,
                                     int H, int W, int C) {
   const int OH = (H + 1) / 2, OW = (W + 1) / 2, CV = C / 8;
   const long long total = static_cast<long long>(n_img) * OH * OW * CV;
@@ -109,7 +102,7 @@ __global__ void maxpool3x3s2_kernel(const __nv_bfloat16* __restrict__ in, __nv_b
     const int ox = static_cast<int>(t % OW); t /= OW;
     const int oy = static_cast<int>(t % OH);
     const long long img = t / OH;
-    uint4 m = make_uint4(0xff80ff80u, 0xff80ff80u, 0xff80ff80u, 0xff80ff80u);  // -inf pairs
+    uint4 m = make_uint4(kActNegInf2, kActNegInf2, kActNegInf2, kActNegInf2);  // -inf pairs
 #pragma unroll
     for (int dy = -1; dy <= 1; ++dy) {
       const int y = 2 * oy + dy;
@@ -119,7 +112,7 @@ __global__ void maxpool3x3s2_kernel(const __nv_bfloat16* __restrict__ in, __nv_b
         const int x = 2 * ox + dx;
         if (x < 0 || x >= W) continue;
         const uint4 v = __ldg(reinterpret_cast<const uint4*>(in + ((img * H + y) * W + x) * C) + cv);
-        m.x = bf162_max(m.x, v.x); m.y = bf162_max(m.y, v.y); m.z = bf162_max(m.z, v.z); m.w = bf162_max(m.w, v.w);
+        m.x = act2_max(m.x, v.x); m.y = act2_max(m.y, v.y); m.z = act2_max(m.z, v.z); m.w = act2_max(m.w, v.w);
       }
     }
     reinterpret_cast<uint4*>(out + ((img * OH + oy) * OW + ox) * C)[cv] = m;
@@ -129,13 +122,13 @@ __global__ void maxpool3x3s2_kernel(const __nv_bfloat16* __restrict__ in, __nv_b
 // ---------------------------------------------------------------------------------------------------------------------
 // Row-wise LayerNorm over D = 512 (one warp per row; fp32 statistics, eps inside the sqrt like torch).
 //   x_in  [rows, 512] fp32
-//   outputs (each optional): y_f32 (residual stream), y_bf16 (GEMM A operand), ypos_bf16 = bf16(y + pos[row % L])
+//   outputs (each optional): y_f32 (residual stream), y_act (GEMM A operand), ypos_act = act_t(y + pos[row % L])
 //   do_norm = 0 turns it into the plain cast(+pos) pass used once on the assembled input tokens.
 constexpr int kD = 512;
 __global__ void layernorm512_kernel(const float* __restrict__ x_in, const float* __restrict__ gamma,
                                     const float* __restrict__ beta, const float* __restrict__ pos, int L,
-                                    float* __restrict__ y_f32, __nv_bfloat16* __restrict__ y_bf16,
-                                    __nv_bfloat16* __restrict__ ypos_bf16, long long rows, int do_norm, float eps) {
+                                    float* __restrict__ y_f32, act_t* __restrict__ y_act,
+                                    act_t* __restrict__ ypos_act, long long rows, int do_norm, float eps) {
   const int lane = threadIdx.x & 31;
   const long long warp_global = (blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x) >> 5;
   const long long warps_total = (static_cast<long long>(gridDim.x) * blockDim.x) >> 5;
@@ -175,24 +168,21 @@ __global__ void layernorm512_kernel(const float* __restrict__ x_in, const float*
 #pragma unroll
       for (int i = 0; i < 4; ++i) yp[i * 32 + lane] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
     }
-    if (y_bf16 != nullptr) {
-      uint2* yp = reinterpret_cast<uint2*>(y_bf16 + row * kD);
+    if (y_act != nullptr) {
+      uint2* yp = reinterpret_cast<uint2*>(y_act + row * kD);
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
-        __nv_bfloat162 a = __floats2bfloat162_rn(v[4 * i], v[4 * i + 1]);
-        __nv_bfloat162 b = __floats2bfloat162_rn(v[4 * i + 2], v[4 * i + 3]);
-        yp[i * 32 + lane] = make_uint2(*reinterpret_cast<uint32_t*>(&a), *reinterpret_cast<uint32_t*>(&b));
+        yp[i * 32 + lane] = make_uint2(pack_act2(v[4 * i], v[4 * i + 1]), pack_act2(v[4 * i + 2], v[4 * i + 3]));
       }
     }
-    if (ypos_bf16 != nullptr) {
+    if (ypos_act != nullptr) {
       const float4* pp = reinterpret_cast<const float4*>(pos + (row % L) * kD);
-      uint2* yp = reinterpret_cast<uint2*>(ypos_bf16 + row * kD);
+      uint2* yp = reinterpret_cast<uint2*>(ypos_act + row * kD);
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
         const float4 pv = __ldg(pp + i * 32 + lane);
-        __nv_bfloat162 a = __floats2bfloat162_rn(v[4 * i] + pv.x, v[4 * i + 1] + pv.y);
-        __nv_bfloat162 b = __floats2bfloat162_rn(v[4 * i + 2] + pv.z, v[4 * i + 3] + pv.w);
-        yp[i * 32 + lane] = make_uint2(*reinterpret_cast<uint32_t*>(&a), *reinterpret_cast<uint32_t*>(&b));
+        yp[i * 32 + lane] = make_uint2(pack_act2(v[4 * i] + pv.x, v[4 * i + 1] + pv.y),
+                                       pack_act2(v[4 * i + 2] + pv.z, v[4 * i + 3] + pv.w));
       }
     }
   }

@@ -68,16 +68,16 @@ inline bool plan_linear(GemmPlan* g, const void* A, long long M, int K, int lda,
   const uint64_t row = static_cast<uint64_t>(lda) * 2;
   const uint64_t strides[4] = {row, row * M, row * M, row * M};
   const uint32_t box[5] = {64, 128, 1, 1, 1};
-  if (!make_tmap_bf16(&g->ta, A, 5, dims, strides, box, 128, err)) return false;
+  if (!make_tmap_act(&g->ta, A, 5, dims, strides, box, 128, err)) return false;
   const uint64_t wdims[2] = {static_cast<uint64_t>(K), static_cast<uint64_t>(N)};
   const uint64_t wstr[1] = {static_cast<uint64_t>(K) * 2};
   const uint32_t wbox[2] = {64, static_cast<uint32_t>(g->block_n)};
-  if (!make_tmap_bf16(&g->tb, Wt, 2, wdims, wstr, wbox, 128, err)) return false;
+  if (!make_tmap_act(&g->tb, Wt, 2, wdims, wstr, wbox, 128, err)) return false;
   g->flops = 2ll * M * N * K;
   return true;
 }
 
-// NHWC bf16 conv, k x k (k = 1 or 3), stride 1 or 2, pad = k/2, as an implicit GEMM.
+// NHWC 16-bit conv, k x k (k = 1 or 3), stride 1 or 2, pad = k/2, as an implicit GEMM.
 //   in [B, H, W, Cin], Wt [Cout, k*k*Cin] (tap-major, channel-minor), out rows = B*OH*OW, ld = Cout (or ld_out)
 inline bool plan_conv(GemmPlan* g, const void* in, int B, int H, int W, int Cin, int ksize, int stride, const void* Wt,
                       int Cout, const float* bias, const void* residual, bool res_f32, void* out, int ld_out,
@@ -115,24 +115,24 @@ inline bool plan_conv(GemmPlan* g, const void* in, int B, int H, int W, int Cin,
     const uint64_t dims[5] = {(uint64_t)Cin, (uint64_t)W, 1, (uint64_t)H, (uint64_t)B};
     const uint64_t strides[4] = {Cin * e, (uint64_t)W * Cin * e, (uint64_t)W * Cin * e, (uint64_t)H * W * Cin * e};
     const uint32_t box[5] = {64, (uint32_t)p.box_w, 1, (uint32_t)p.box_h, (uint32_t)p.box_b};
-    if (!make_tmap_bf16(&g->ta, in, 5, dims, strides, box, 128, err)) return false;
+    if (!make_tmap_act(&g->ta, in, 5, dims, strides, box, 128, err)) return false;
   } else {
     // phase view: [B, H/2, 2, W/2, 2*Cin]
     const uint64_t dims[5] = {(uint64_t)2 * Cin, (uint64_t)W / 2, 2, (uint64_t)H / 2, (uint64_t)B};
     const uint64_t strides[4] = {2 * Cin * e, (uint64_t)W * Cin * e, 2 * (uint64_t)W * Cin * e, (uint64_t)H * W * Cin * e};
     const uint32_t box[5] = {64, (uint32_t)p.box_w, 1, (uint32_t)p.box_h, (uint32_t)p.box_b};
-    if (!make_tmap_bf16(&g->ta, in, 5, dims, strides, box, 128, err)) return false;
+    if (!make_tmap_act(&g->ta, in, 5, dims, strides, box, 128, err)) return false;
   }
   const uint64_t K = (uint64_t)ksize * ksize * Cin;
   const uint64_t wdims[2] = {K, (uint64_t)Cout};
   const uint64_t wstr[1] = {K * e};
   const uint32_t wbox[2] = {64, (uint32_t)g->block_n};
-  if (!make_tmap_bf16(&g->tb, Wt, 2, wdims, wstr, wbox, 128, err)) return false;
+  if (!make_tmap_act(&g->tb, Wt, 2, wdims, wstr, wbox, 128, err)) return false;
   g->flops = 2ll * B * OH * OW * Cout * (long long)K;
   return true;
 }
 
-// ResNet stem: 7x7 stride-2 pad-3 conv over the padded NHWC4 bf16 image written by preprocess_*_kernel
+// ResNet stem: 7x7 stride-2 pad-3 conv over the padded NHWC4 16-bit image written by preprocess_*_kernel
 // ([B, H, W + 8, 4], 4 zero pixels either side). For output pixel (oh, ow) and filter row kh the 8 input pixels
 // starting at padded column 2*ow are ONE contiguous 64-byte run = one 32-element K chunk (slot 0 carries a zero
 // weight, slots 1..7 are kw = 0..6), so the A tile is a plain TMA box over an overlapping-row view of the image:
@@ -162,11 +162,11 @@ inline bool plan_conv1(GemmPlan* g, const void* in_padded, int B, int H, int W, 
   const uint64_t dims[5] = {32, (uint64_t)OW, 2, (uint64_t)H / 2, (uint64_t)B};
   const uint64_t strides[4] = {16, rowb, 2 * rowb, (uint64_t)H * rowb};
   const uint32_t box[5] = {32, (uint32_t)p.box_w, 1, (uint32_t)p.box_h, (uint32_t)p.box_b};
-  if (!make_tmap_bf16(&g->ta, in_padded, 5, dims, strides, box, 64, err)) return false;
+  if (!make_tmap_act(&g->ta, in_padded, 5, dims, strides, box, 64, err)) return false;
   const uint64_t wdims[2] = {224, 64};
   const uint64_t wstr[1] = {224 * 2};
   const uint32_t wbox[2] = {32, 64};
-  if (!make_tmap_bf16(&g->tb, Wt, 2, wdims, wstr, wbox, 64, err)) return false;
+  if (!make_tmap_act(&g->tb, Wt, 2, wdims, wstr, wbox, 64, err)) return false;
   g->flops = 2ll * B * OH * OW * 64 * 147;
   return true;
 }

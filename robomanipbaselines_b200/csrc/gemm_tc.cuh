@@ -1,5 +1,5 @@
 // tcgen05/TMEM implicit-GEMM kernel shared by every dense contraction on the ACT path:
-//   * ResNet-18 convs (NHWC bf16, FrozenBN folded into weights/bias)  -- reference: third_party/act/detr/models/backbone.py:21-57,86-96
+//   * ResNet-18 convs (NHWC 16-bit, FrozenBN folded into weights/bias)  -- reference: third_party/act/detr/models/backbone.py:21-57,86-96
 //   * 1x1 input_proj + token scatter                                   -- third_party/act/detr/models/detr_vae.py:131-141
 //   * transformer linear layers                                        -- third_party/act/detr/models/transformer.py:166-179,229-250
 //
@@ -58,7 +58,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
   constexpr uint32_t kSwizzleLayout = (BLOCK_K == 64) ? 2u : 4u;   // SWIZZLE_128B : SWIZZLE_64B
   constexpr uint32_t kSBO = 8u * BLOCK_K * 2u;                      // 8-row core-matrix group stride
   constexpr uint32_t kTmemCols = 2 * BLOCK_N;                       // double-buffered accumulator
-  constexpr uint32_t kIdesc = make_idesc_bf16(128, BLOCK_N, false, false);
+  constexpr uint32_t kIdesc = make_idesc_f16(128, BLOCK_N, false, false);
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -133,7 +133,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
           for (int k = 0; k < BLOCK_K / 16; ++k) {
             const uint64_t da = make_smem_desc(a_addr + k * 32, 0, kSBO, kSwizzleLayout);
             const uint64_t db = make_smem_desc(b_addr + k * 32, 0, kSBO, kSwizzleLayout);
-            umma_bf16_ss(d_tmem, da, db, kIdesc, (kb | k) != 0 ? 1u : 0u);
+            umma_f16_ss(d_tmem, da, db, kIdesc, (kb | k) != 0 ? 1u : 0u);
           }
           umma_commit(&empty_bar[stage]);   // frees this smem stage when the MMAs above retire
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
@@ -197,7 +197,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 f[4 * i + 0] += rv.x; f[4 * i + 1] += rv.y; f[4 * i + 2] += rv.z; f[4 * i + 3] += rv.w;
               }
             } else {
-              const uint4* rp = reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(p.residual) +
+              const uint4* rp = reinterpret_cast<const uint4*>(static_cast<const act_t*>(p.residual) +
                                                                 grow * p.ld_res + col);
 #pragma unroll
               for (int i = 0; i < 4; ++i) {
@@ -205,9 +205,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 const uint32_t u[4] = {rv.x, rv.y, rv.z, rv.w};
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
-                  const __nv_bfloat162 h2 = *reinterpret_cast<const __nv_bfloat162*>(&u[j]);
-                  f[8 * i + 2 * j + 0] += __low2float(h2);
-                  f[8 * i + 2 * j + 1] += __high2float(h2);
+                  const float2 t = unpack_act2(u[j]);
+                  f[8 * i + 2 * j + 0] += t.x;
+                  f[8 * i + 2 * j + 1] += t.y;
                 }
               }
             }
@@ -221,11 +221,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
 #pragma unroll
             for (int i = 0; i < 8; ++i) op[i] = make_float4(f[4 * i], f[4 * i + 1], f[4 * i + 2], f[4 * i + 3]);
           } else {
-            uint4* op = reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(p.out) + orow * p.ld_out + col);
+            uint4* op = reinterpret_cast<uint4*>(static_cast<act_t*>(p.out) + orow * p.ld_out + col);
 #pragma unroll
             for (int i = 0; i < 4; ++i)
-              op[i] = make_uint4(pack_bf16x2(f[8 * i], f[8 * i + 1]), pack_bf16x2(f[8 * i + 2], f[8 * i + 3]),
-                                 pack_bf16x2(f[8 * i + 4], f[8 * i + 5]), pack_bf16x2(f[8 * i + 6], f[8 * i + 7]));
+              op[i] = make_uint4(pack_act2(f[8 * i], f[8 * i + 1]), pack_act2(f[8 * i + 2], f[8 * i + 3]),
+                                 pack_act2(f[8 * i + 4], f[8 * i + 5]), pack_act2(f[8 * i + 6], f[8 * i + 7]));
           }
         }
       }

@@ -3,6 +3,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <stdint.h>
 
 namespace rmb {
@@ -10,6 +11,46 @@ namespace rmb {
 #ifndef RMB_MBAR_TIMEOUT_CYCLES
 // A wedged pipeline must not hang the GPU box: every mbarrier wait is bounded (~2 s at 2 GHz) and traps.
 #define RMB_MBAR_TIMEOUT_CYCLES (4000000000ll)
+#endif
+
+// ---------------------------------------------------------------- 16-bit storage / tensor-core operand type
+// All activations and GEMM operands are stored as one 16-bit float type, accumulated in fp32 (TMEM).
+// Default is IEEE fp16: same tcgen05 kind::f16 throughput as bf16 but 3 more mantissa bits, which is what keeps the
+// chunk within 1e-2 of the fp32 reference after ~30 layers; every stored tensor on this path is BN/LayerNorm-bounded,
+// and conversions clamp to the finite range. Build with -DRMB_ACT_BF16 for bf16 storage instead.
+#ifdef RMB_ACT_BF16
+typedef __nv_bfloat16 act_t;
+#define RMB_ACT_DTYPE_NAME "bf16"
+constexpr uint32_t kUmmaABFormat = 1u;      // cute::UMMA::F16F32Format::BF16
+constexpr uint32_t kActNegInf2 = 0xff80ff80u;
+__host__ __device__ __forceinline__ act_t to_act(float x) { return __float2bfloat16_rn(x); }
+__device__ __forceinline__ uint32_t pack_act2(float lo, float hi) {
+  __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+__device__ __forceinline__ float2 unpack_act2(uint32_t u) {
+  return __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&u));
+}
+__device__ __forceinline__ uint32_t act2_max(uint32_t a, uint32_t b) {
+  __nv_bfloat162 r = __hmax2(*reinterpret_cast<__nv_bfloat162*>(&a), *reinterpret_cast<__nv_bfloat162*>(&b));
+  return *reinterpret_cast<uint32_t*>(&r);
+}
+#else
+typedef __half act_t;
+#define RMB_ACT_DTYPE_NAME "fp16"
+constexpr uint32_t kUmmaABFormat = 0u;      // cute::UMMA::F16F32Format::F16
+constexpr uint32_t kActNegInf2 = 0xfc00fc00u;
+__host__ __device__ __forceinline__ float clamp_half(float x) { return fminf(fmaxf(x, -65504.0f), 65504.0f); }
+__host__ __device__ __forceinline__ act_t to_act(float x) { return __float2half_rn(clamp_half(x)); }
+__device__ __forceinline__ uint32_t pack_act2(float lo, float hi) {
+  __half2 v = __floats2half2_rn(clamp_half(lo), clamp_half(hi));
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+__device__ __forceinline__ float2 unpack_act2(uint32_t u) { return __half22float2(*reinterpret_cast<__half2*>(&u)); }
+__device__ __forceinline__ uint32_t act2_max(uint32_t a, uint32_t b) {
+  __half2 r = __hmax2(*reinterpret_cast<__half2*>(&a), *reinterpret_cast<__half2*>(&b));
+  return *reinterpret_cast<uint32_t*>(&r);
+}
 #endif
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
@@ -114,8 +155,8 @@ __device__ __forceinline__ void umma_commit(uint64_t* bar) {
                : "memory");
 }
 
-// D[tmem] (+)= A[smem] * B[smem]; bf16 inputs, fp32 accumulate. Issued by ONE thread.
-__device__ __forceinline__ void umma_bf16_ss(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+// D[tmem] (+)= A[smem] * B[smem]; 16-bit float inputs (act_t), fp32 accumulate. Issued by ONE thread.
+__device__ __forceinline__ void umma_f16_ss(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
                                              uint32_t accumulate) {
   asm volatile(
       "{\n\t.reg .pred p;\n\t"
@@ -125,11 +166,11 @@ __device__ __forceinline__ void umma_bf16_ss(uint32_t tmem_d, uint64_t desc_a, u
       : "memory");
 }
 
-// Instruction descriptor, kind::f16, A/B = bf16, D = fp32 (cute::UMMA::InstrDescriptor bit layout).
-__host__ __device__ constexpr uint32_t make_idesc_bf16(int M, int N, bool a_mn_major, bool b_mn_major) {
+// Instruction descriptor, kind::f16, A/B = act_t, D = fp32 (cute::UMMA::InstrDescriptor bit layout).
+__host__ __device__ constexpr uint32_t make_idesc_f16(int M, int N, bool a_mn_major, bool b_mn_major) {
   return (1u << 4)                                  // c_format = F32
-         | (1u << 7)                                // a_format = BF16
-         | (1u << 10)                               // b_format = BF16
+         | (kUmmaABFormat << 7)                     // a_format
+         | (kUmmaABFormat << 10)                    // b_format
          | ((a_mn_major ? 1u : 0u) << 15)           // a_major
          | ((b_mn_major ? 1u : 0u) << 16)           // b_major
          | (static_cast<uint32_t>(N >> 3) << 17)    // n_dim
@@ -169,10 +210,5 @@ __device__ __forceinline__ void tmem_ld_32x32b_x32(uint32_t taddr, uint32_t (&r)
       : "r"(taddr));
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
-
-__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
-  __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
-  return *reinterpret_cast<uint32_t*>(&v);
-}
 
 }  // namespace rmb

@@ -28,8 +28,8 @@ inline PFN_encodeTiled get_encode_tiled(std::string* err) {
   return fn;
 }
 
-// rank-`rank` bf16 tensor map. dims[0] is the contiguous dimension; strides_bytes[i] is the stride of dims[i+1].
-inline bool make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims,
+// rank-`rank` tensor map over 16-bit (act_t) elements. dims[0] is the contiguous dimension; strides_bytes[i] is the stride of dims[i+1].
+inline bool make_tmap_act(CUtensorMap* out, const void* base, int rank, const uint64_t* dims,
                            const uint64_t* strides_bytes, const uint32_t* box, int swizzle_bytes, std::string* err) {
   PFN_encodeTiled fn = get_encode_tiled(err);
   if (!fn) return false;
@@ -43,7 +43,12 @@ inline bool make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const u
   if (swizzle_bytes == 128) sw = CU_TENSOR_MAP_SWIZZLE_128B;
   else if (swizzle_bytes == 64) sw = CU_TENSOR_MAP_SWIZZLE_64B;
   else if (swizzle_bytes == 32) sw = CU_TENSOR_MAP_SWIZZLE_32B;
-  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, static_cast<cuuint32_t>(rank), const_cast<void*>(base), gdim,
+  #ifdef RMB_ACT_BF16
+  const CUtensorMapDataType dt = CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+#else
+  const CUtensorMapDataType dt = CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+#endif
+  CUresult r = fn(out, dt, static_cast<cuuint32_t>(rank), const_cast<void*>(base), gdim,
                   gstr, gbox, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {

@@ -11,8 +11,13 @@ from robomanipbaselines_b200._lib import check, cur_stream, ptr
 pytestmark = pytest.mark.gpu
 
 
+def _act_dtype():
+    return _lib.act_torch_dtype()
+
+
 def _bf16(t):
-    return t.to(torch.bfloat16)
+    """Round to the library's 16-bit operand type (fp16 by default, bf16 with -DRMB_ACT_BF16)."""
+    return t.to(_act_dtype())
 
 
 def _report(name, got, ref):
@@ -35,8 +40,8 @@ def test_gemm(lib, cuda, M, N, K, flags):
     res = torch.randn(M, N, generator=g).to(cuda)
     if not res_f32:
         res = _bf16(res)
-    out = torch.empty(M, N, device=cuda, dtype=torch.float32 if flags & 2 else torch.bfloat16)
-    check(lib.rmb_gemm_bf16(ptr(A), ptr(W), ptr(bias), ptr(res), ptr(out), M, N, K, flags, cur_stream()), "gemm")
+    out = torch.empty(M, N, device=cuda, dtype=torch.float32 if flags & 2 else _act_dtype())
+    check(lib.rmb_gemm(ptr(A), ptr(W), ptr(bias), ptr(res), ptr(out), M, N, K, flags, cur_stream()), "gemm")
     torch.cuda.synchronize()
     ref = A.float() @ W.float().t() + bias + res.float()
     if flags & 1:
@@ -66,8 +71,8 @@ def test_conv(lib, cuda, B, H, W, Cin, Cout, k, stride, relu, use_res):
     OH, OW = (H + 2 * (k // 2) - k) // stride + 1, (W + 2 * (k // 2) - k) // stride + 1
     res = _bf16(torch.randn(B, OH, OW, Cout, generator=g)).to(cuda) if use_res else None
     wt = w.permute(0, 2, 3, 1).contiguous().reshape(Cout, k * k * Cin)      # [Cout][kh][kw][Cin]
-    out = torch.zeros(B, OH, OW, Cout, device=cuda, dtype=torch.bfloat16)
-    check(lib.rmb_conv2d_nhwc_bf16(ptr(x), ptr(wt), ptr(bias), ptr(res), ptr(out), B, H, W, Cin, Cout, k, stride,
+    out = torch.zeros(B, OH, OW, Cout, device=cuda, dtype=_act_dtype())
+    check(lib.rmb_conv2d_nhwc(ptr(x), ptr(wt), ptr(bias), ptr(res), ptr(out), B, H, W, Cin, Cout, k, stride,
                                    relu, cur_stream()), "conv")
     torch.cuda.synchronize()
     ref = _conv_ref(x, w, bias, res, stride, relu)
@@ -87,7 +92,7 @@ def _stem_weight(w_oihw):
 def test_preprocess_and_stem(lib, cuda, B, H, W):
     g = torch.Generator(device="cpu").manual_seed(H)
     img = torch.randint(0, 256, (B, H, W, 3), generator=g, dtype=torch.uint8).to(cuda)
-    x0 = torch.full((B, H, W + 8, 4), 7.0, device=cuda, dtype=torch.bfloat16)
+    x0 = torch.full((B, H, W + 8, 4), 7.0, device=cuda, dtype=_act_dtype())
     check(lib.rmb_preprocess_images_u8(ptr(img), ptr(x0), B, H, W, cur_stream()), "preprocess_u8")
     mean = torch.tensor([0.485, 0.456, 0.406], device=cuda)
     std = torch.tensor([0.229, 0.224, 0.225], device=cuda)
@@ -105,8 +110,8 @@ def test_preprocess_and_stem(lib, cuda, B, H, W):
 
     w = _bf16(torch.randn(64, 3, 7, 7, generator=g) / 147 ** 0.5).to(cuda)
     bias = torch.randn(64, generator=g).to(cuda)
-    out = torch.zeros(B, H // 2, W // 2, 64, device=cuda, dtype=torch.bfloat16)
-    check(lib.rmb_conv1_stem_bf16(ptr(x0), ptr(_stem_weight(w)), ptr(bias), ptr(out), B, H, W, cur_stream()), "stem")
+    out = torch.zeros(B, H // 2, W // 2, 64, device=cuda, dtype=_act_dtype())
+    check(lib.rmb_conv1_stem(ptr(x0), ptr(_stem_weight(w)), ptr(bias), ptr(out), B, H, W, cur_stream()), "stem")
     torch.cuda.synchronize()
     ref = F.conv2d(x0[:, :, 4:-4, :3].float().permute(0, 3, 1, 2), w.float(), bias, stride=2, padding=3).relu()
     err, scale = _report(f"stem {H}x{W}", out, ref.permute(0, 2, 3, 1))
@@ -115,8 +120,8 @@ def test_preprocess_and_stem(lib, cuda, B, H, W):
 
 def test_maxpool(lib, cuda):
     x = _bf16(torch.randn(3, 24, 32, 64)).to(cuda)
-    out = torch.empty(3, 12, 16, 64, device=cuda, dtype=torch.bfloat16)
-    check(lib.rmb_maxpool3x3s2_nhwc_bf16(ptr(x), ptr(out), 3, 24, 32, 64, cur_stream()), "maxpool")
+    out = torch.empty(3, 12, 16, 64, device=cuda, dtype=_act_dtype())
+    check(lib.rmb_maxpool3x3s2_nhwc(ptr(x), ptr(out), 3, 24, 32, 64, cur_stream()), "maxpool")
     torch.cuda.synchronize()
     ref = F.max_pool2d(x.float().permute(0, 3, 1, 2), 3, 2, 1).permute(0, 2, 3, 1)
     assert torch.equal(out.float(), ref)
@@ -131,13 +136,13 @@ def test_attention(lib, cuda, B, Lq, Lk, shared):
     QK = _bf16(torch.randn(max(qrows, B * Lk), 2 * D, generator=g)).to(cuda)   # q at cols 0.., k at cols 512..
     Qs = _bf16(torch.randn(qrows, D, generator=g)).to(cuda)
     V = _bf16(torch.randn(B * Lk, D, generator=g)).to(cuda)
-    out = torch.zeros(B * Lq, D, device=cuda, dtype=torch.bfloat16)
+    out = torch.zeros(B * Lq, D, device=cuda, dtype=_act_dtype())
     if shared:
-        check(lib.rmb_attention_bf16(ptr(Qs), D, 0, 1, ptr(QK), 2 * D, D, ptr(V), D, 0, ptr(out), D, B, H, Lq, Lk,
+        check(lib.rmb_attention(ptr(Qs), D, 0, 1, ptr(QK), 2 * D, D, ptr(V), D, 0, ptr(out), D, B, H, Lq, Lk,
                                      cur_stream()), "attention")
         q = Qs.float().view(1, Lq, H, 64).expand(B, Lq, H, 64)
     else:
-        check(lib.rmb_attention_bf16(ptr(QK), 2 * D, 0, 0, ptr(QK), 2 * D, D, ptr(V), D, 0, ptr(out), D, B, H, Lq, Lk,
+        check(lib.rmb_attention(ptr(QK), 2 * D, 0, 0, ptr(QK), 2 * D, D, ptr(V), D, 0, ptr(out), D, B, H, Lq, Lk,
                                      cur_stream()), "attention")
         q = QK[:B * Lq, :D].float().view(B, Lq, H, 64)
     torch.cuda.synchronize()
@@ -155,8 +160,8 @@ def test_layernorm(lib, cuda):
     gamma, beta = torch.randn(512).to(cuda), torch.randn(512).to(cuda)
     pos = torch.randn(L, 512).to(cuda)
     y = torch.empty(rows, 512, device=cuda)
-    yb = torch.empty(rows, 512, device=cuda, dtype=torch.bfloat16)
-    ypb = torch.empty(rows, 512, device=cuda, dtype=torch.bfloat16)
+    yb = torch.empty(rows, 512, device=cuda, dtype=_act_dtype())
+    ypb = torch.empty(rows, 512, device=cuda, dtype=_act_dtype())
     check(lib.rmb_layernorm512(ptr(x), ptr(gamma), ptr(beta), ptr(pos), L, ptr(y), ptr(yb), ptr(ypb), rows, 1,
                                cur_stream()), "layernorm")
     torch.cuda.synchronize()
