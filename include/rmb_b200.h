@@ -65,6 +65,18 @@ int rmb_act_finalize(rmb_act_engine_t* e);
  * d_qpos  float32 [batch, state_dim] (already normalised); d_a_hat float32 [batch, chunk_size, action_dim] (normalised). */
 int rmb_act_forward(rmb_act_engine_t* e, const void* d_images, int image_format, const float* d_qpos, float* d_a_hat,
                     int batch, void* stream);
+/* Same forward with a CUDA-event pair recorded around every kernel launch on `stream` (synchronises the stream before
+ * returning). Fills out[0..n) in launch order and returns n (<= cap), <0 on error. flops / bytes are the ALGORITHMIC
+ * figures of that launch: 2*rows*N*K useful FLOPs; operands read once + result written once. */
+typedef struct rmb_launch_prof {
+  char name[48];    /* which layer, e.g. "layer2.0.conv1 3x3" */
+  char kernel[40];  /* __global__ function, e.g. "gemm_tc_kernel" */
+  float ms;         /* device time between the two events */
+  double flops;
+  double bytes;
+} rmb_launch_prof_t;
+int rmb_act_forward_profile(rmb_act_engine_t* e, const void* d_images, int image_format, const float* d_qpos,
+                            float* d_a_hat, int batch, void* stream, rmb_launch_prof_t* out, int cap);
 /* Number of kernels rmb_act_forward launches for one call (for bench.py's gpu_launches). */
 int rmb_act_forward_num_launches(const rmb_act_engine_t* e);
 /* Algorithmic FLOPs of one forward for `batch` episodes (live graph only). */

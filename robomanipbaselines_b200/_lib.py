@@ -26,6 +26,13 @@ class ActConfig(ctypes.Structure):
     ]
 
 
+class LaunchProf(ctypes.Structure):
+    """Mirror of rmb_launch_prof_t."""
+
+    _fields_ = [("name", ctypes.c_char * 48), ("kernel", ctypes.c_char * 40), ("ms", c_float), ("flops", c_double),
+                ("bytes", c_double)]
+
+
 # name -> (restype, argtypes); must list every symbol include/rmb_b200.h declares (tests check this)
 SIGNATURES = {
     "rmb_last_error": (c_char_p, []),
@@ -37,6 +44,8 @@ SIGNATURES = {
     "rmb_act_load_tensor": (c_int, [c_void_p, c_char_p, c_void_p, c_int64]),
     "rmb_act_finalize": (c_int, [c_void_p]),
     "rmb_act_forward": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int, c_void_p]),
+    "rmb_act_forward_profile": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int, c_void_p,
+                                        POINTER(LaunchProf), c_int]),
     "rmb_act_forward_num_launches": (c_int, [c_void_p]),
     "rmb_act_forward_flops": (c_double, [c_void_p, c_int]),
     "rmb_act_debug_read": (c_int64, [c_void_p, c_int, c_void_p, c_int, c_void_p]),

@@ -542,68 +542,164 @@ double rmb_act_forward_flops(const rmb_act_engine_t* e, int batch) {
   return f;
 }
 
-int rmb_act_forward(rmb_act_engine_t* e, const void* d_images, int image_format, const float* d_qpos, float* d_a_hat,
-                    int batch, void* stream_) {
+// One record per kernel launch of a forward (filled by rmb_act_forward_profile).
+struct LaunchProf {
+  std::vector<cudaEvent_t> ev;      // 2 per launch
+  std::vector<rmb_launch_prof_t> rec;
+};
+
+static int forward_impl(rmb_act_engine_t* e, const void* d_images, int image_format, const float* d_qpos, float* d_a_hat,
+                        int batch, cudaStream_t s, LaunchProf* prof) {
   if (!e || !d_images || !d_qpos || !d_a_hat) return fail("rmb_act_forward: null argument");
   if (!e->finalized) return fail("rmb_act_forward: weights not finalized");
   if (batch < 1 || batch > e->cfg.max_batch) return fail("rmb_act_forward: batch out of range");
-  cudaStream_t s = static_cast<cudaStream_t>(stream_);
+  if (image_format != 0 && image_format != 1) return fail("rmb_act_forward: image_format must be 0 (u8 HWC) or 1 (f32 CHW)");
   rmb_act_engine::BatchPlans* bp = nullptr;
   if (int r = build_plans(e, batch, &bp)) return r;
   const rmb_act_config_t& c = e->cfg;
-  const int NI = batch * c.num_cams, H = c.img_h, W = c.img_w, L = e->L, C = c.chunk_size;
+  const int NI = batch * c.num_cams, H = c.img_h, W = c.img_w, L = e->L, C = c.chunk_size, FF = c.dim_feedforward;
   const int sms = e->num_sms;
   const float3 mean = make_float3(0.485f, 0.456f, 0.406f);
   const float3 istd = make_float3(1.0f / 0.229f, 1.0f / 0.224f, 1.0f / 0.225f);
+  const long long BL = (long long)batch * L, BC = (long long)batch * C;
+
+  // begin/end bracket every launch with CUDA events when profiling (no-ops otherwise)
+  auto begin = [&](const char* name, const char* kernel, double flops, double bytes) {
+    if (!prof) return;
+    rmb_launch_prof_t r;
+    memset(&r, 0, sizeof(r));
+    snprintf(r.name, sizeof(r.name), "%s", name);
+    snprintf(r.kernel, sizeof(r.kernel), "%s", kernel);
+    r.flops = flops; r.bytes = bytes;
+    prof->rec.push_back(r);
+    cudaEvent_t a, b;
+    cudaEventCreate(&a); cudaEventCreate(&b);
+    prof->ev.push_back(a); prof->ev.push_back(b);
+    cudaEventRecord(a, s);
+  };
+  auto end = [&]() { if (prof) cudaEventRecord(prof->ev.back(), s); };
+  // algorithmic HBM bytes of an implicit GEMM: A read once, weights once, output written once (+ residual read)
+  auto gemm_bytes = [&](const GemmPlan& g, double a_bytes) {
+    const double rows = (double)g.p.W * g.p.H * g.p.B, N = (double)g.p.n_col_tiles * g.block_n;
+    const double K = (double)g.p.num_taps * g.p.chunks_per_tap * g.block_k;
+    return a_bytes + N * K * 2 + rows * N * (g.p.out_f32 ? 4 : 2) + (g.p.residual ? rows * N * (g.p.res_f32 ? 4 : 2) : 0);
+  };
+  auto run_gemm = [&](const char* name, const GemmPlan& g, double a_bytes) -> int {
+    begin(name, "gemm_tc_kernel", (double)g.flops, gemm_bytes(g, a_bytes));
+    RMB_CUDA(launch_gemm(g, sms, s));
+    end();
+    return 0;
+  };
+#define RMB_RUN(x) do { if (int _r = (x)) return _r; } while (0)
+
   {
     const long long items = (long long)NI * H * (W / 4 + 2);
-    if (image_format == 0)
+    const double out_b = (double)NI * H * (W + 8) * 8;
+    if (image_format == 0) {
+      begin("preprocess_u8", "preprocess_u8_kernel", 0, (double)NI * H * W * 3 + out_b);
       preprocess_u8_kernel<<<grid_for(items, 256, sms), 256, 0, s>>>(static_cast<const uint8_t*>(d_images), e->x0, NI, H, W, mean, istd);
-    else if (image_format == 1)
+    } else {
+      begin("preprocess_f32", "preprocess_f32_kernel", 0, (double)NI * H * W * 12 + out_b);
       preprocess_f32_kernel<<<grid_for(items, 256, sms), 256, 0, s>>>(static_cast<const float*>(d_images), e->x0, NI, H, W, mean, istd);
-    else
-      return fail("rmb_act_forward: image_format must be 0 (u8 HWC) or 1 (f32 CHW)");
+    }
+    end();
   }
-  RMB_CUDA(launch_gemm(bp->stem, sms, s));
+  RMB_RUN(run_gemm("stem conv7x7/2", bp->stem, (double)NI * H * (W + 8) * 8));
   {
     const long long items = (long long)NI * (H / 4) * (W / 4) * 8;
+    begin("maxpool3x3/2", "maxpool3x3s2_kernel", 0, (double)NI * (H / 2) * (W / 2) * 128 + (double)NI * (H / 4) * (W / 4) * 128);
     maxpool3x3s2_kernel<<<grid_for(items, 256, sms), 256, 0, s>>>(e->c1, e->stage[0][2], NI, H / 2, W / 2, 64);
+    end();
   }
+  const int chans[4] = {64, 128, 256, 512};
   for (int li = 0; li < 4; ++li) {
-    if (li > 0) RMB_CUDA(launch_gemm(bp->down[li], sms, s));
-    RMB_CUDA(launch_gemm(bp->conv[li][0][0], sms, s));
-    RMB_CUDA(launch_gemm(bp->conv[li][0][1], sms, s));
-    RMB_CUDA(launch_gemm(bp->conv[li][1][0], sms, s));
-    RMB_CUDA(launch_gemm(bp->conv[li][1][1], sms, s));
+    char nm[48];
+    const double px = (double)NI * (H >> (2 + li)) * (W >> (2 + li));
+    const double cin = li == 0 ? 64 : chans[li - 1];
+    const double in_b = (li == 0 ? px : px * 4) * cin * 2, mid_b = px * chans[li] * 2;
+    if (li > 0) { snprintf(nm, sizeof(nm), "layer%d.0.downsample 1x1/2", li + 1); RMB_RUN(run_gemm(nm, bp->down[li], in_b)); }
+    snprintf(nm, sizeof(nm), "layer%d.0.conv1 3x3", li + 1); RMB_RUN(run_gemm(nm, bp->conv[li][0][0], in_b));
+    snprintf(nm, sizeof(nm), "layer%d.0.conv2 3x3", li + 1); RMB_RUN(run_gemm(nm, bp->conv[li][0][1], mid_b));
+    snprintf(nm, sizeof(nm), "layer%d.1.conv1 3x3", li + 1); RMB_RUN(run_gemm(nm, bp->conv[li][1][0], mid_b));
+    snprintf(nm, sizeof(nm), "layer%d.1.conv2 3x3", li + 1); RMB_RUN(run_gemm(nm, bp->conv[li][1][1], mid_b));
   }
-  RMB_CUDA(launch_gemm(bp->input_proj, sms, s));
+  RMB_RUN(run_gemm("input_proj 1x1 -> tokens", bp->input_proj, (double)NI * e->Hf * e->Wf * 512 * 2));
+  begin("latent+proprio tokens", "act_extra_tokens_kernel", 0, (double)batch * 2 * 512 * 4);
   act_extra_tokens_kernel<<<batch, 256, 0, s>>>(d_qpos, c.state_dim, e->latent_bias, e->w_state, e->b_state, e->tok_f32, L);
-  const long long BL = (long long)batch * L, BC = (long long)batch * C;
+  end();
   const int ln_grid = grid_for(BL * 32, 256, sms);
+  begin("tokens cast(+pos)", "layernorm512_kernel", 0, (double)BL * 512 * (4 + 2 + 2));
   layernorm512_kernel<<<ln_grid, 256, 0, s>>>(e->tok_f32, nullptr, nullptr, e->pos, L, nullptr, e->tok_b, e->tok_pb, BL, 0, 1e-5f);
+  end();
+  const double tokb = (double)BL * 512 * 2;
+  const double attn_flops = 4.0 * batch * (double)L * L * 512, attn_bytes = (double)BL * 512 * 2 * 4;
   for (int l = 0; l < c.enc_layers; ++l) {
     auto& w = e->enc[l];
     auto& pl = bp->enc[l];
-    RMB_CUDA(launch_gemm(pl.qk, sms, s));
-    RMB_CUDA(launch_gemm(pl.v, sms, s));
+    char nm[48];
+    snprintf(nm, sizeof(nm), "enc%d QK proj", l); RMB_RUN(run_gemm(nm, pl.qk, tokb));
+    snprintf(nm, sizeof(nm), "enc%d V proj", l); RMB_RUN(run_gemm(nm, pl.v, tokb));
+    snprintf(nm, sizeof(nm), "enc%d self-attention", l);
+    begin(nm, "attention_tc_kernel", attn_flops, attn_bytes);
     RMB_CUDA(launch_attention(pl.attn, s));
-    RMB_CUDA(launch_gemm(pl.o, sms, s));                       // y = ao Wo^T + bo + x
+    end();
+    snprintf(nm, sizeof(nm), "enc%d out proj +res", l); RMB_RUN(run_gemm(nm, pl.o, tokb));   // y = ao Wo^T + bo + x
+    snprintf(nm, sizeof(nm), "enc%d norm1", l);
+    begin(nm, "layernorm512_kernel", 0, (double)BL * 512 * (4 + 4 + 2));
     layernorm512_kernel<<<ln_grid, 256, 0, s>>>(e->y_f32, w.g1, w.be1, nullptr, L, e->x1_f32, e->x1_b, nullptr, BL, 1, 1e-5f);
-    RMB_CUDA(launch_gemm(pl.ff1, sms, s));
-    RMB_CUDA(launch_gemm(pl.ff2, sms, s));                     // y = relu(.) W2^T + b2 + x1
+    end();
+    snprintf(nm, sizeof(nm), "enc%d linear1+relu", l); RMB_RUN(run_gemm(nm, pl.ff1, tokb));
+    snprintf(nm, sizeof(nm), "enc%d linear2 +res", l); RMB_RUN(run_gemm(nm, pl.ff2, (double)BL * FF * 2));   // y = relu(.) W2^T + b2 + x1
+    snprintf(nm, sizeof(nm), "enc%d norm2", l);
+    begin(nm, "layernorm512_kernel", 0, (double)BL * 512 * (4 + 4 + 2 + 2));
     layernorm512_kernel<<<ln_grid, 256, 0, s>>>(e->y_f32, w.g2, w.be2, e->pos, L, e->tok_f32, e->tok_b, e->tok_pb, BL, 1, 1e-5f);
+    end();
   }
-  RMB_CUDA(launch_gemm(bp->dk, sms, s));
-  RMB_CUDA(launch_gemm(bp->dv, sms, s));
+  RMB_RUN(run_gemm("dec0 K proj", bp->dk, tokb));
+  RMB_RUN(run_gemm("dec0 V proj", bp->dv, tokb));
+  begin("dec0 cross-attention", "attention_tc_kernel", 4.0 * batch * (double)C * L * 512, (double)BL * 512 * 2 * 2 + (double)BC * 512 * 2);
   RMB_CUDA(launch_attention(bp->dattn, s));
-  RMB_CUDA(launch_gemm(bp->dout, sms, s));
+  end();
+  RMB_RUN(run_gemm("dec0 out proj +tgt", bp->dout, (double)BC * 512 * 2));
   const int lnd_grid = grid_for(BC * 32, 256, sms);
+  begin("dec0 norm2", "layernorm512_kernel", 0, (double)BC * 512 * (4 + 4 + 2));
   layernorm512_kernel<<<lnd_grid, 256, 0, s>>>(e->yd, e->dec.g2, e->dec.be2, nullptr, C, e->t_f32, e->t_b, nullptr, BC, 1, 1e-5f);
-  RMB_CUDA(launch_gemm(bp->dff1, sms, s));
-  RMB_CUDA(launch_gemm(bp->dff2, sms, s));
+  end();
+  RMB_RUN(run_gemm("dec0 linear1+relu", bp->dff1, (double)BC * 512 * 2));
+  RMB_RUN(run_gemm("dec0 linear2 +res", bp->dff2, (double)BC * FF * 2));
+  begin("norm3+decoder.norm+action_head", "act_head_kernel", 2.0 * BC * 512 * c.action_dim, (double)BC * 512 * 4 + (double)BC * c.action_dim * 4);
   act_head_kernel<<<lnd_grid, 256, 0, s>>>(e->yd2, e->dec.g3, e->dec.be3, e->dec.gn, e->dec.ben, e->w_head, e->b_head, d_a_hat, BC, c.action_dim, 1e-5f);
+  end();
+#undef RMB_RUN
   RMB_CUDA(cudaGetLastError());
   return 0;
+}
+
+int rmb_act_forward(rmb_act_engine_t* e, const void* d_images, int image_format, const float* d_qpos, float* d_a_hat,
+                    int batch, void* stream_) {
+  return forward_impl(e, d_images, image_format, d_qpos, d_a_hat, batch, static_cast<cudaStream_t>(stream_), nullptr);
+}
+
+int rmb_act_forward_profile(rmb_act_engine_t* e, const void* d_images, int image_format, const float* d_qpos,
+                            float* d_a_hat, int batch, void* stream_, rmb_launch_prof_t* out, int cap) {
+  if (!out || cap < 1) return fail("rmb_act_forward_profile: null output");
+  cudaStream_t s = static_cast<cudaStream_t>(stream_);
+  LaunchProf prof;
+  const int r = forward_impl(e, d_images, image_format, d_qpos, d_a_hat, batch, s, &prof);
+  cudaError_t ce = cudaStreamSynchronize(s);
+  int n = 0;
+  if (r == 0 && ce == cudaSuccess) {
+    for (size_t i = 0; i < prof.rec.size() && n < cap; ++i, ++n) {
+      float ms = 0.f;
+      cudaEventElapsedTime(&ms, prof.ev[2 * i], prof.ev[2 * i + 1]);
+      prof.rec[i].ms = ms;
+      out[n] = prof.rec[i];
+    }
+  }
+  for (cudaEvent_t ev : prof.ev) cudaEventDestroy(ev);
+  if (r != 0) return r;
+  if (ce != cudaSuccess) return fail(std::string("rmb_act_forward_profile: ") + cudaGetErrorString(ce), -2);
+  return n;
 }
 
 int64_t rmb_act_debug_read(rmb_act_engine_t* e, int which, float* d_out, int batch, void* stream_) {

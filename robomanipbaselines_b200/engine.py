@@ -66,6 +66,20 @@ class ActEngine:
               "rmb_act_forward")
         return out
 
+    def forward_profile(self, images, qpos, out=None):
+        """forward() with CUDA events around every launch; returns (a_hat, [dict(name, kernel, ms, flops, bytes)])."""
+        B = qpos.shape[0]
+        c = self.cfg
+        fmt = 0 if images.dtype == torch.uint8 else 1
+        if out is None:
+            out = torch.empty(B, c.chunk_size, c.action_dim, device=self.device, dtype=torch.float32)
+        cap = 256
+        recs = (_lib.LaunchProf * cap)()
+        n = check(self.lib.rmb_act_forward_profile(self._h, ptr(images), fmt, ptr(qpos), ptr(out), B, cur_stream(),
+                                                   recs, cap), "rmb_act_forward_profile")
+        return out, [dict(name=recs[i].name.decode(), kernel=recs[i].kernel.decode(), ms=recs[i].ms,
+                          flops=recs[i].flops, bytes=recs[i].bytes) for i in range(n)]
+
     def debug_read(self, which, batch):
         L = 2 + (self.cfg.img_h // 32) * (self.cfg.img_w // 32) * self.cfg.num_cams
         out = torch.empty(batch, L, 512, device=self.device)
