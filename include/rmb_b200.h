@@ -45,6 +45,10 @@ const char* rmb_version(void);
  * buffer below holds this type; accumulation is always fp32. */
 const char* rmb_act_dtype(void);
 int rmb_check_device(int dev);
+/* Synchronises the current device and returns the kernels' fault flag: 0 = none, 1 = an mbarrier wait inside a
+ * TMA/tcgen05 pipeline timed out (the kernel drained with garbage results instead of hanging), <0 = CUDA error.
+ * clear != 0 resets the flag. Results produced while the flag is set are invalid. */
+int rmb_device_fault(int clear);
 
 /* ---- engine lifetime: replaces ACTPolicy.__init__ (third_party/act/policy.py:10-16) + RolloutBase.load_ckpt
  *      (robo_manip_baselines/common/base/RolloutBase.py:376-385) */

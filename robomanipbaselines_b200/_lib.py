@@ -39,6 +39,7 @@ SIGNATURES = {
     "rmb_version": (c_char_p, []),
     "rmb_act_dtype": (c_char_p, []),
     "rmb_check_device": (c_int, [c_int]),
+    "rmb_device_fault": (c_int, [c_int]),
     "rmb_act_engine_create": (c_int, [POINTER(ActConfig), POINTER(c_void_p)]),
     "rmb_act_engine_destroy": (None, [c_void_p]),
     "rmb_act_load_tensor": (c_int, [c_void_p, c_char_p, c_void_p, c_int64]),

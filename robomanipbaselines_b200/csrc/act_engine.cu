@@ -224,6 +224,18 @@ const char* rmb_last_error(void) { return g_last_error.c_str(); }
 const char* rmb_version(void) { return "rmb_b200 0.1 (sm_100a, " RMB_ACT_DTYPE_NAME " operands, fp32 accumulate)"; }
 const char* rmb_act_dtype(void) { return RMB_ACT_DTYPE_NAME; }
 
+int rmb_device_fault(int clear) {
+  int v = 0;
+  RMB_CUDA(cudaDeviceSynchronize());
+  RMB_CUDA(cudaMemcpyFromSymbol(&v, rmb::g_rmb_fault, sizeof(int)));
+  if (v != 0 && clear) {
+    const int zero = 0;
+    RMB_CUDA(cudaMemcpyToSymbol(rmb::g_rmb_fault, &zero, sizeof(int)));
+  }
+  if (v != 0) g_last_error = "device fault flag set: an mbarrier wait timed out inside a kernel (pipeline wedged)";
+  return v;
+}
+
 int rmb_check_device(int dev) {
   cudaDeviceProp prop;
   RMB_CUDA(cudaGetDeviceProperties(&prop, dev));

@@ -63,7 +63,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
     fence_mbar_init();
     prefetch_tmap(&tmap_q); prefetch_tmap(&tmap_k); prefetch_tmap(&tmap_v);
   }
-  if (warp == 0) { tmem_alloc(tmem_ptr_smem, 256); tmem_relinquish(); }
+  if (warp == 0) { __syncwarp(); tmem_alloc(tmem_ptr_smem, 256); tmem_relinquish(); }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -108,6 +108,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
                      k != 0);
       umma_commit(s_bar);
     }
+    __syncwarp();
     mbar_wait(s_bar, g & 1);
     tc_fence_after();
     const int kv_base = kt * 128;
@@ -162,6 +163,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
       }
       umma_commit(o_bar);
     }
+    __syncwarp();
   }
   mbar_wait(o_bar, (nkt - 1) & 1);
   tc_fence_after();

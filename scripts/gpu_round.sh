@@ -1,0 +1,29 @@
+#!/bin/bash
+# One gpurun call: per-group GPU tests (separate processes so a trapped kernel cannot poison later groups),
+# then smoke + a short bench. Everything is bounded by `timeout`; logs land in gpurun_out/.
+cd "$(dirname "$0")/.." || exit 1
+mkdir -p gpurun_out
+nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,memory.total --format=csv > gpurun_out/gpu.txt 2>&1
+run() { # name, timeout, cmd...
+  local name=$1 t=$2; shift 2
+  echo "=== $name" | tee -a gpurun_out/summary.txt
+  timeout "$t" "$@" > "gpurun_out/$name.log" 2>&1
+  local rc=$?
+  echo "rc=$rc" | tee -a gpurun_out/summary.txt
+  tail -n 6 "gpurun_out/$name.log" | tee -a gpurun_out/summary.txt
+  return $rc
+}
+: > gpurun_out/summary.txt
+PT="python -m pytest -q -s -m gpu -p no:cacheprovider"
+run t_elem 300 $PT tests/test_kernels_gpu.py -k "maxpool or layernorm or ensemble or normalize"
+run t_gemm 300 $PT tests/test_kernels_gpu.py -k "test_gemm"
+run t_conv 300 $PT tests/test_kernels_gpu.py -k "test_conv"
+run t_stem 300 $PT tests/test_kernels_gpu.py -k "preprocess_and_stem"
+run t_attn 300 $PT tests/test_kernels_gpu.py -k "test_attention"
+run t_engine 600 $PT tests/test_act_engine_gpu.py
+ENGINE_RC=$?
+if [ "$1" != "--no-bench" ] && [ $ENGINE_RC -eq 0 ]; then
+  run smoke 300 python -c "import __graft_entry__ as g; g.smoke()"
+  run bench 900 python bench.py --steps 5 --warmup 3
+fi
+exit 0

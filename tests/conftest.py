@@ -29,3 +29,18 @@ def cuda():
 
     _lib.check(_lib.load().rmb_check_device(0), "rmb_check_device")
     return torch.device("cuda:0")
+
+
+@pytest.fixture(autouse=True)
+def _no_device_fault(request):
+    """After every GPU test: the kernels' fault flag (bounded mbarrier waits, see ptx.cuh) must still be clear."""
+    yield
+    if request.node.get_closest_marker("gpu") is None:
+        return
+    import torch
+
+    if not torch.cuda.is_available():
+        return
+    from robomanipbaselines_b200 import _lib
+
+    assert _lib.load().rmb_device_fault(1) == 0, "a TMA/tcgen05 pipeline timed out inside a kernel"
