@@ -45,7 +45,8 @@ struct GemmSmem {
   static constexpr int kBBytes = BLOCK_N * BLOCK_K * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kBarrierBytes = 256;
-  static constexpr int kTotal = STAGES * kStageBytes + kBarrierBytes + 1024;  // +1024: manual alignment slack
+  static constexpr int kStagingBytes = 4 * 4096;   // epilogue: one 32 x 128 B staging tile per warp
+  static constexpr int kTotal = STAGES * kStageBytes + kStagingBytes + kBarrierBytes + 1024;  // +1024: alignment slack
 };
 
 template <int BLOCK_N, int BLOCK_K, int STAGES>
@@ -64,7 +65,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem + STAGES * S::kABytes;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * S::kStageBytes);
+  uint8_t* smem_stage = smem + STAGES * S::kStageBytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_stage + S::kStagingBytes);
   uint64_t* full_bar = bars;                    // [STAGES]
   uint64_t* empty_bar = bars + STAGES;          // [STAGES]
   uint64_t* tmem_full_bar = bars + 2 * STAGES;  // [2]
@@ -92,63 +94,83 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
   const int total_tiles = row_tiles * p.n_col_tiles;
   const uint32_t tx_bytes = static_cast<uint32_t>(rows_per_tile * BLOCK_K * 2 + S::kBBytes);
 
+  // The producer and MMA warps run their loops warp-uniformly (all 32 lanes, identical control flow) and only the
+  // issuing instruction is predicated on one elected lane: loop state stays in uniform registers and the per-k-block
+  // instruction count -- the throughput limit of a single issuing thread -- is a few dozen instead of ~150.
   if (warp == 4) {
     // ------------------------------------------------------------ TMA producer
-    if (lane == 0) {
-      int stage = 0; uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        const int ct = tile % p.n_col_tiles;
-        const int rt = tile / p.n_col_tiles;
-        const int wt = rt % p.tiles_w;
-        const int ht = (rt / p.tiles_w) % p.tiles_h;
-        const int bt = rt / (p.tiles_w * p.tiles_h);
-        const int w0 = wt * p.box_w, h0 = ht * p.box_h, b0 = bt * p.box_b;
-        for (int kb = 0; kb < num_kb; ++kb) {
-          const int tap = kb / p.chunks_per_tap;
-          const int ch = kb - tap * p.chunks_per_tap;
+    const uint32_t a_base = smem_u32(smem_a), b_base = smem_u32(smem_b), full_base = smem_u32(full_bar);
+    int stage = 0; uint32_t phase = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      const int ct = tile % p.n_col_tiles;
+      const int rt = tile / p.n_col_tiles;
+      const int wt = rt % p.tiles_w;
+      const int ht = (rt / p.tiles_w) % p.tiles_h;
+      const int bt = rt / (p.tiles_w * p.tiles_h);
+      const int w0 = wt * p.box_w, h0 = ht * p.box_h, b0 = bt * p.box_b;
+      const int n0 = ct * BLOCK_N;
+      int kcol = 0;                                   // column of the weight matrix = kb * BLOCK_K
+      for (int tap = 0; tap < p.num_taps; ++tap) {
+        const int c0 = p.tap_c0[tap], d1 = w0 + p.tap_d1[tap], d2 = p.tap_d2[tap], d3 = h0 + p.tap_d3[tap];
+        for (int ch = 0; ch < p.chunks_per_tap; ++ch) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
-          mbar_arrive_expect_tx(&full_bar[stage], tx_bytes);
-          tma_load_5d(smem_a + stage * S::kABytes, &tmap_a, &full_bar[stage], p.tap_c0[tap] + ch * BLOCK_K,
-                      w0 + p.tap_d1[tap], p.tap_d2[tap], h0 + p.tap_d3[tap], b0);
-          tma_load_2d(smem_b + stage * S::kBBytes, &tmap_b, &full_bar[stage], kb * BLOCK_K, ct * BLOCK_N);
+          if (elect_one()) {
+            const uint32_t fb = full_base + stage * 8;
+            mbar_arrive_expect_tx_u32(fb, tx_bytes);
+            tma_load_5d_u32(a_base + stage * S::kABytes, &tmap_a, fb, c0 + ch * BLOCK_K, d1, d2, d3, b0);
+            tma_load_2d_u32(b_base + stage * S::kBBytes, &tmap_b, fb, kcol, n0);
+          }
+          __syncwarp();
+          kcol += BLOCK_K;
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
       }
     }
   } else if (warp == 5) {
-    // ------------------------------------------------------------ MMA issuer (single thread)
-    if (lane == 0) {
-      int stage = 0; uint32_t phase = 0;
-      int acc = 0; uint32_t acc_phase = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        mbar_wait(&tmem_empty_bar[acc], acc_phase ^ 1);
+    // ------------------------------------------------------------ MMA issuer (one elected lane issues)
+    const uint64_t a_desc0 = make_smem_desc(smem_u32(smem_a), 0, kSBO, kSwizzleLayout);
+    const uint64_t b_desc0 = make_smem_desc(smem_u32(smem_b), 0, kSBO, kSwizzleLayout);
+    const uint32_t empty_base = smem_u32(empty_bar);
+    int stage = 0; uint32_t phase = 0;
+    int acc = 0; uint32_t acc_phase = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      mbar_wait(&tmem_empty_bar[acc], acc_phase ^ 1);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + acc * BLOCK_N;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait(&full_bar[stage], phase);
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + acc * BLOCK_N;
-        for (int kb = 0; kb < num_kb; ++kb) {
-          mbar_wait(&full_bar[stage], phase);
-          tc_fence_after();
-          const uint32_t a_addr = smem_u32(smem_a + stage * S::kABytes);
-          const uint32_t b_addr = smem_u32(smem_b + stage * S::kBBytes);
+        if (elect_one()) {
+          // the 14-bit start-address field (bytes >> 4) never carries: all of shared memory is < 256 KB
+          const uint64_t da = a_desc0 + static_cast<uint64_t>(stage * (S::kABytes >> 4));
+          const uint64_t db = b_desc0 + static_cast<uint64_t>(stage * (S::kBBytes >> 4));
 #pragma unroll
-          for (int k = 0; k < BLOCK_K / 16; ++k) {
-            const uint64_t da = make_smem_desc(a_addr + k * 32, 0, kSBO, kSwizzleLayout);
-            const uint64_t db = make_smem_desc(b_addr + k * 32, 0, kSBO, kSwizzleLayout);
-            umma_f16_ss(d_tmem, da, db, kIdesc, (kb | k) != 0 ? 1u : 0u);
-          }
-          umma_commit(&empty_bar[stage]);   // frees this smem stage when the MMAs above retire
-          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+          for (int k = 0; k < BLOCK_K / 16; ++k)
+            umma_f16_ss(d_tmem, da + 2 * k, db + 2 * k, kIdesc, (kb | k) != 0 ? 1u : 0u);
+          umma_commit_u32(empty_base + stage * 8);    // frees this smem stage when the MMAs above retire
         }
-        umma_commit(&tmem_full_bar[acc]);   // accumulator complete -> epilogue
-        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        __syncwarp();
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
+      if (elect_one()) umma_commit(&tmem_full_bar[acc]);   // accumulator complete -> epilogue
+      __syncwarp();
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
   } else {
     // ------------------------------------------------------------ epilogue warps 0..3 (TMEM lanes 32*warp..+31)
+    // Two passes per 32-column chunk so that global traffic is coalesced:
+    //   pass 1: thread = accumulator row; tcgen05.ld 32 fp32 columns -> per-warp smem staging tile (32 rows x 128 B,
+    //           16-byte groups XOR-swizzled by row & 7: conflict-free for both passes)
+    //   pass 2: 8 lanes = one row (8 x 16 B = the row's 128 B), 4 rows per instruction; bias / residual / ReLU here,
+    //           so residual loads and output stores are full 64-128 B row segments.
+    // The next chunk's tcgen05.ld is in flight while pass 2 runs.
     int acc = 0; uint32_t acc_phase = 0;
-    const int r = warp * 32 + lane;                 // row of the tile owned by this thread
+    const int r = warp * 32 + lane;                 // row of the tile owned by this thread in pass 1
     const int wl = r % p.box_w;
     const int hl = (r / p.box_w) % p.box_h;
     const int bl = r / (p.box_w * p.box_h);
+    uint8_t* stg = smem_stage + warp * 4096;
+    const int sub = lane & 7, rsel = lane >> 3;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
       const int ct = tile % p.n_col_tiles;
       const int rt = tile / p.n_col_tiles;
@@ -157,81 +179,83 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
       const int bt = rt / (p.tiles_w * p.tiles_h);
       const int w = wt * p.box_w + wl, h = ht * p.box_h + hl, b = bt * p.box_b + bl;
       const bool valid = (r < rows_per_tile) && (w < p.W) && (h < p.H) && (b < p.B);
-      long long grow;                               // source row (residual) in natural pixel order
-      long long orow;                               // destination row
-      grow = (static_cast<long long>(b) * p.H + h) * p.W + w;
-      if (p.remap_ncam > 0) {
-        orow = static_cast<long long>(b / p.remap_ncam) * p.remap_L + p.remap_off +
-               static_cast<long long>(h) * (p.W * p.remap_ncam) + (b % p.remap_ncam) * p.W + w;
-      } else {
-        orow = grow;
+      int my_grow = -1, my_orow = -1;               // source row (residual, natural pixel order) / destination row
+      if (valid) {
+        my_grow = (b * p.H + h) * p.W + w;
+        my_orow = my_grow;
+        if (p.remap_ncam > 0)
+          my_orow = (b / p.remap_ncam) * p.remap_L + p.remap_off + h * (p.W * p.remap_ncam) + (b % p.remap_ncam) * p.W + w;
+      }
+      int grow_it[8], orow_it[8];
+#pragma unroll
+      for (int it = 0; it < 8; ++it) {
+        grow_it[it] = __shfl_sync(0xffffffffu, my_grow, it * 4 + rsel);
+        orow_it[it] = __shfl_sync(0xffffffffu, my_orow, it * 4 + rsel);
       }
       mbar_wait(&tmem_full_bar[acc], acc_phase);
       tc_fence_after();
       const uint32_t t_row = tmem_base + acc * BLOCK_N + (static_cast<uint32_t>(warp * 32) << 16);
+      uint32_t v[32];
+      tmem_ld_32x32b_x32(t_row, v);
 #pragma unroll 1
       for (int c = 0; c < BLOCK_N; c += 32) {
-        uint32_t v[32];
-        tmem_ld_32x32b_x32(t_row + c, v);
         tmem_ld_wait();
-        if (valid) {
-          const int col = ct * BLOCK_N + c;
-          float f[32];
 #pragma unroll
-          for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]);
-          if (p.bias != nullptr) {
-            const float4* bp = reinterpret_cast<const float4*>(p.bias + col);
+        for (int g = 0; g < 8; ++g)
+          *reinterpret_cast<uint4*>(stg + lane * 128 + ((g ^ (lane & 7)) << 4)) =
+              make_uint4(v[4 * g], v[4 * g + 1], v[4 * g + 2], v[4 * g + 3]);
+        const bool last = (c + 32 >= BLOCK_N);
+        if (!last) tmem_ld_32x32b_x32(t_row + c + 32, v);
+        else tc_fence_before();
+        __syncwarp();
+        if (last && lane == 0) mbar_arrive(&tmem_empty_bar[acc]);   // 4 arrivals (one per warp) free the accumulator
+        const int col = ct * BLOCK_N + c + sub * 4;
+        float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (p.bias != nullptr) bv = __ldg(reinterpret_cast<const float4*>(p.bias + col));
+        float4 f[8];
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-              const float4 bv = __ldg(bp + i);
-              f[4 * i + 0] += bv.x; f[4 * i + 1] += bv.y; f[4 * i + 2] += bv.z; f[4 * i + 3] += bv.w;
-            }
-          }
-          if (p.residual != nullptr) {
-            if (p.res_f32) {
-              const float4* rp = reinterpret_cast<const float4*>(static_cast<const float*>(p.residual) +
-                                                                  grow * p.ld_res + col);
+        for (int it = 0; it < 8; ++it) {
+          const int i = it * 4 + rsel;
+          f[it] = *reinterpret_cast<const float4*>(stg + i * 128 + ((sub ^ (i & 7)) << 4));
+        }
+        if (p.residual != nullptr) {
+          if (p.res_f32) {
+            float4 rv[8];
 #pragma unroll
-              for (int i = 0; i < 8; ++i) {
-                const float4 rv = __ldg(rp + i);
-                f[4 * i + 0] += rv.x; f[4 * i + 1] += rv.y; f[4 * i + 2] += rv.z; f[4 * i + 3] += rv.w;
-              }
-            } else {
-              const uint4* rp = reinterpret_cast<const uint4*>(static_cast<const act_t*>(p.residual) +
-                                                                grow * p.ld_res + col);
+            for (int it = 0; it < 8; ++it)
+              rv[it] = (grow_it[it] >= 0)
+                           ? __ldg(reinterpret_cast<const float4*>(static_cast<const float*>(p.residual) +
+                                                                   static_cast<long long>(grow_it[it]) * p.ld_res + col))
+                           : make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-              for (int i = 0; i < 4; ++i) {
-                const uint4 rv = __ldg(rp + i);
-                const uint32_t u[4] = {rv.x, rv.y, rv.z, rv.w};
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                  const float2 t = unpack_act2(u[j]);
-                  f[8 * i + 2 * j + 0] += t.x;
-                  f[8 * i + 2 * j + 1] += t.y;
-                }
-              }
-            }
-          }
-          if (p.relu) {
-#pragma unroll
-            for (int i = 0; i < 32; ++i) f[i] = fmaxf(f[i], 0.0f);
-          }
-          if (p.out_f32) {
-            float4* op = reinterpret_cast<float4*>(static_cast<float*>(p.out) + orow * p.ld_out + col);
-#pragma unroll
-            for (int i = 0; i < 8; ++i) op[i] = make_float4(f[4 * i], f[4 * i + 1], f[4 * i + 2], f[4 * i + 3]);
+            for (int it = 0; it < 8; ++it) { f[it].x += rv[it].x; f[it].y += rv[it].y; f[it].z += rv[it].z; f[it].w += rv[it].w; }
           } else {
-            uint4* op = reinterpret_cast<uint4*>(static_cast<act_t*>(p.out) + orow * p.ld_out + col);
+            uint2 rv[8];
 #pragma unroll
-            for (int i = 0; i < 4; ++i)
-              op[i] = make_uint4(pack_act2(f[8 * i], f[8 * i + 1]), pack_act2(f[8 * i + 2], f[8 * i + 3]),
-                                 pack_act2(f[8 * i + 4], f[8 * i + 5]), pack_act2(f[8 * i + 6], f[8 * i + 7]));
+            for (int it = 0; it < 8; ++it)
+              rv[it] = (grow_it[it] >= 0)
+                           ? __ldg(reinterpret_cast<const uint2*>(static_cast<const act_t*>(p.residual) +
+                                                                  static_cast<long long>(grow_it[it]) * p.ld_res + col))
+                           : make_uint2(0u, 0u);
+#pragma unroll
+            for (int it = 0; it < 8; ++it) {
+              const float2 lo = unpack_act2(rv[it].x), hi = unpack_act2(rv[it].y);
+              f[it].x += lo.x; f[it].y += lo.y; f[it].z += hi.x; f[it].w += hi.y;
+            }
           }
         }
+#pragma unroll
+        for (int it = 0; it < 8; ++it) {
+          float4 o = make_float4(f[it].x + bv.x, f[it].y + bv.y, f[it].z + bv.z, f[it].w + bv.w);
+          if (p.relu) { o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f); }
+          if (orow_it[it] >= 0) {
+            const long long off = static_cast<long long>(orow_it[it]) * p.ld_out + col;
+            if (p.out_f32) *reinterpret_cast<float4*>(static_cast<float*>(p.out) + off) = o;
+            else *reinterpret_cast<uint2*>(static_cast<act_t*>(p.out) + off) = make_uint2(pack_act2(o.x, o.y), pack_act2(o.z, o.w));
+          }
+        }
+        __syncwarp();                                // staging tile is rewritten by the next chunk's pass 1
       }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);   // 4 arrivals (one per epilogue warp) free the accumulator
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
   }
