@@ -128,8 +128,9 @@ struct rmb_act_engine {
   float *yd = nullptr, *t_f32 = nullptr, *yd2 = nullptr;
 
   struct BatchPlans {
-    GemmPlan stem;
+    HaloPlan stem;
     GemmPlan conv[4][2][2];
+    HaloPlan conv_l1[2][2];   // layer1 (Cin = Cout = 64): halo-reuse kernel
     GemmPlan down[4];
     GemmPlan input_proj;
     struct Enc { GemmPlan qk, v, o, ff1, ff2; AttnPlan attn; };
@@ -481,7 +482,7 @@ static int build_plans(rmb_act_engine* e, int nb, rmb_act_engine::BatchPlans** o
   const rmb_act_config_t& c = e->cfg;
   const int NI = nb * c.num_cams, H = c.img_h, W = c.img_w, D = 512, FF = c.dim_feedforward, C = c.chunk_size, L = e->L;
   const int chans[4] = {64, 128, 256, 512};
-  if (!plan_conv1(&bp->stem, e->x0, NI, H, W, e->stem.w, e->stem.b, e->c1, &err)) return fail(err);
+  if (!plan_conv1_halo(&bp->stem, e->x0, NI, H, W, e->stem.w, e->stem.b, e->c1, &err)) return fail(err);
   // stage buffers: [0] = t (mid), [1] = y (block 0 out), [2] = d (downsample) then z (block 1 out)
   for (int li = 0; li < 4; ++li) {
     const int h = H >> (2 + li), w = W >> (2 + li);
@@ -493,6 +494,13 @@ static int build_plans(rmb_act_engine* e, int nb, rmb_act_engine::BatchPlans** o
     if (li > 0) {
       if (!plan_conv(&bp->down[li], x_in, NI, hin, win, cin, 1, 2, e->down[li].w, chans[li], e->down[li].b, nullptr, false, z, chans[li], false, false, &err)) return fail(err);
       identity = z;
+    }
+    if (li == 0) {
+      if (!plan_conv3x3_halo(&bp->conv_l1[0][0], x_in, NI, h, w, e->blk[0][0][0].w, e->blk[0][0][0].b, nullptr, t, true, &err)) return fail(err);
+      if (!plan_conv3x3_halo(&bp->conv_l1[0][1], t, NI, h, w, e->blk[0][0][1].w, e->blk[0][0][1].b, identity, y, true, &err)) return fail(err);
+      if (!plan_conv3x3_halo(&bp->conv_l1[1][0], y, NI, h, w, e->blk[0][1][0].w, e->blk[0][1][0].b, nullptr, t, true, &err)) return fail(err);
+      if (!plan_conv3x3_halo(&bp->conv_l1[1][1], t, NI, h, w, e->blk[0][1][1].w, e->blk[0][1][1].b, y, z, true, &err)) return fail(err);
+      continue;
     }
     if (!plan_conv(&bp->conv[li][0][0], x_in, NI, hin, win, cin, 3, (li == 0) ? 1 : 2, e->blk[li][0][0].w, chans[li], e->blk[li][0][0].b, nullptr, false, t, chans[li], false, true, &err)) return fail(err);
     if (!plan_conv(&bp->conv[li][0][1], t, NI, h, w, chans[li], 3, 1, e->blk[li][0][1].w, chans[li], e->blk[li][0][1].b, identity, false, y, chans[li], false, true, &err)) return fail(err);
@@ -596,6 +604,14 @@ static int forward_impl(rmb_act_engine_t* e, const void* d_images, int image_for
     const double K = (double)g.p.num_taps * g.p.chunks_per_tap * g.block_k;
     return a_bytes + N * K * 2 + rows * N * (g.p.out_f32 ? 4 : 2) + (g.p.residual ? rows * N * (g.p.res_f32 ? 4 : 2) : 0);
   };
+  auto run_halo = [&](const char* name, const HaloPlan& g, double a_bytes) -> int {
+    const double rows = (double)g.hp.g.W * g.hp.g.H * g.hp.g.B;
+    const double K = (double)g.hp.n_taps * g.block_k;
+    begin(name, "conv_halo_kernel", (double)g.flops, a_bytes + 64 * K * 2 + rows * 64 * 2 + (g.hp.g.residual ? rows * 64 * 2 : 0));
+    RMB_CUDA(launch_halo(g, sms, s));
+    end();
+    return 0;
+  };
   auto run_gemm = [&](const char* name, const GemmPlan& g, double a_bytes) -> int {
     begin(name, "gemm_tc_kernel", (double)g.flops, gemm_bytes(g, a_bytes));
     RMB_CUDA(launch_gemm(g, sms, s));
@@ -616,7 +632,7 @@ static int forward_impl(rmb_act_engine_t* e, const void* d_images, int image_for
     }
     end();
   }
-  RMB_RUN(run_gemm("stem conv7x7/2", bp->stem, (double)NI * H * (W + 8) * 8));
+  RMB_RUN(run_halo("stem conv7x7/2", bp->stem, (double)NI * H * (W + 8) * 8));
   {
     const long long items = (long long)NI * (H / 4) * (W / 4) * 8;
     begin("maxpool3x3/2", "maxpool3x3s2_kernel", 0, (double)NI * (H / 2) * (W / 2) * 128 + (double)NI * (H / 4) * (W / 4) * 128);
@@ -630,6 +646,13 @@ static int forward_impl(rmb_act_engine_t* e, const void* d_images, int image_for
     const double cin = li == 0 ? 64 : chans[li - 1];
     const double in_b = (li == 0 ? px : px * 4) * cin * 2, mid_b = px * chans[li] * 2;
     if (li > 0) { snprintf(nm, sizeof(nm), "layer%d.0.downsample 1x1/2", li + 1); RMB_RUN(run_gemm(nm, bp->down[li], in_b)); }
+    if (li == 0) {
+      RMB_RUN(run_halo("layer1.0.conv1 3x3", bp->conv_l1[0][0], in_b));
+      RMB_RUN(run_halo("layer1.0.conv2 3x3", bp->conv_l1[0][1], mid_b));
+      RMB_RUN(run_halo("layer1.1.conv1 3x3", bp->conv_l1[1][0], mid_b));
+      RMB_RUN(run_halo("layer1.1.conv2 3x3", bp->conv_l1[1][1], mid_b));
+      continue;
+    }
     snprintf(nm, sizeof(nm), "layer%d.0.conv1 3x3", li + 1); RMB_RUN(run_gemm(nm, bp->conv[li][0][0], in_b));
     snprintf(nm, sizeof(nm), "layer%d.0.conv2 3x3", li + 1); RMB_RUN(run_gemm(nm, bp->conv[li][0][1], mid_b));
     snprintf(nm, sizeof(nm), "layer%d.1.conv1 3x3", li + 1); RMB_RUN(run_gemm(nm, bp->conv[li][1][0], mid_b));
@@ -801,8 +824,14 @@ int rmb_gemm(const void* d_A, const void* d_Wt, const float* d_bias, const void*
 int rmb_conv2d_nhwc(const void* d_in, const void* d_Wt, const float* d_bias, const void* d_residual, void* d_out,
                          int B, int H, int W, int Cin, int Cout, int ksize, int stride, int relu, void* stream_) {
   if (!d_in || !d_Wt || !d_out) return fail("rmb_conv2d_nhwc: null argument");
-  GemmPlan g;
   std::string err;
+  if (conv3x3_halo_eligible(W, Cin, Cout, ksize, stride)) {
+    HaloPlan hg;
+    if (!plan_conv3x3_halo(&hg, d_in, B, H, W, d_Wt, d_bias, d_residual, d_out, relu != 0, &err)) return fail(err);
+    RMB_CUDA(launch_halo(hg, device_sms(), static_cast<cudaStream_t>(stream_)));
+    return 0;
+  }
+  GemmPlan g;
   if (!plan_conv(&g, d_in, B, H, W, Cin, ksize, stride, d_Wt, Cout, d_bias, d_residual, false, d_out, Cout, false, relu != 0, &err)) return fail(err);
   RMB_CUDA(launch_gemm(g, device_sms(), static_cast<cudaStream_t>(stream_)));
   return 0;
@@ -811,10 +840,10 @@ int rmb_conv2d_nhwc(const void* d_in, const void* d_Wt, const float* d_bias, con
 int rmb_conv1_stem(const void* d_in_padded, const void* d_Wt, const float* d_bias, void* d_out, int B, int H, int W,
                         void* stream_) {
   if (!d_in_padded || !d_Wt || !d_out) return fail("rmb_conv1_stem: null argument");
-  GemmPlan g;
+  HaloPlan g;
   std::string err;
-  if (!plan_conv1(&g, d_in_padded, B, H, W, d_Wt, d_bias, d_out, &err)) return fail(err);
-  RMB_CUDA(launch_gemm(g, device_sms(), static_cast<cudaStream_t>(stream_)));
+  if (!plan_conv1_halo(&g, d_in_padded, B, H, W, d_Wt, d_bias, d_out, &err)) return fail(err);
+  RMB_CUDA(launch_halo(g, device_sms(), static_cast<cudaStream_t>(stream_)));
   return 0;
 }
 

@@ -1,0 +1,162 @@
+// Halo-reuse implicit-GEMM convolution for the two bandwidth-critical stages of the ResNet-18 trunk
+// (reference: torchvision resnet18 conv1 / layer1 via third_party/act/detr/models/backbone.py:86-96), Cout = 64.
+//
+// gemm_tc_kernel fetches one TMA box per filter tap, i.e. it pulls every input pixel kh*kw times from L2 and pays one
+// producer/MMA barrier round trip per tap; with only N = 64 output channels per tile that is >190 B of L2 traffic per
+// tensor-core cycle. Here a tile's input is fetched ONCE per filter COLUMN (3x3 conv) or per input-row PARITY (7x7/2
+// stem) as a box that carries the vertical halo, laid out pixel-major [h][w][K] with w fastest. A filter tap that moves
+// by one input row is then just the same shared-memory buffer advanced by box_w rows of K elements = a whole number of
+// 8-row swizzle atoms, so all taps of a buffer are tcgen05.mma instructions on shifted descriptors -- no extra loads.
+// The 64 x K weight slices of all taps stay resident in shared memory for the lifetime of the (persistent) CTA.
+//   3x3/1 (Cin 64): 3 boxes of (box_h + 2) x box_w pixels per tile instead of 9 of box_h x box_w;  9 x 4 MMAs
+//   7x7/2 stem     : 2 boxes (even / odd input rows) of <= 19 x box_w windows instead of 7;          7 x 2 MMAs
+#pragma once
+#include "gemm_tc.cuh"
+
+namespace rmb {
+
+constexpr int kHaloMaxLoads = 3;
+constexpr int kHaloMaxStages = 8;
+
+struct HaloParams {
+  GemmParams g;                       // tiling (box_w x box_h x 1 pixels, n_col_tiles = 1) and epilogue; g.tap_* unused
+  int n_loads;                        // TMA boxes (= pipeline stages consumed) per tile
+  int ld_c0[kHaloMaxLoads];           // coordinate offsets of each box, as in GemmParams' tap tables
+  int ld_d1[kHaloMaxLoads];
+  int ld_d2[kHaloMaxLoads];
+  int ld_d3[kHaloMaxLoads];
+  int ld_tap0[kHaloMaxLoads];         // taps [ld_tap0, ld_tap0 + ld_ntaps) read this box
+  int ld_ntaps[kHaloMaxLoads];
+  uint32_t box_bytes;                 // bytes one box deposits (expect_tx)
+  uint32_t stage_bytes;               // box_bytes rounded up to 1024
+  int n_stages;
+  int n_taps;
+  uint32_t tap_aoff[kMaxTaps];        // byte offset of the tap's first A row inside its box (multiple of 8 rows)
+  int tap_w[kMaxTaps];                // index of the tap's 64 x BLOCK_K weight slice in the resident weights
+};
+
+template <int BLOCK_K>
+struct HaloSmem {
+  static constexpr int kWTapBytes = 64 * BLOCK_K * 2;
+  static constexpr int kStagingBytes = 8 * 4096;
+  static constexpr int kBarrierBytes = 256;
+  static int total(int n_taps, int n_stages, uint32_t stage_bytes) {
+    return n_taps * kWTapBytes + n_stages * static_cast<int>(stage_bytes) + kStagingBytes + kBarrierBytes + 1024;
+  }
+};
+
+template <int BLOCK_K, int RES>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+conv_halo_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                 const __grid_constant__ HaloParams hp) {
+  using S = HaloSmem<BLOCK_K>;
+  constexpr int BLOCK_N = 64;
+  constexpr uint32_t kSwizzleLayout = (BLOCK_K == 64) ? 2u : 4u;   // SWIZZLE_128B : SWIZZLE_64B
+  constexpr uint32_t kSBO = 8u * BLOCK_K * 2u;
+  constexpr uint32_t kTmemCols = 2 * BLOCK_N;
+  constexpr uint32_t kIdesc = make_idesc_f16(128, BLOCK_N, false, false);
+  const GemmParams& p = hp.g;
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem_w = smem;
+  uint8_t* smem_a = smem_w + hp.n_taps * S::kWTapBytes;
+  uint8_t* smem_stage = smem_a + hp.n_stages * hp.stage_bytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_stage + S::kStagingBytes);
+  uint64_t* full_bar = bars;                              // [kHaloMaxStages]
+  uint64_t* empty_bar = bars + kHaloMaxStages;            // [kHaloMaxStages]
+  uint64_t* tmem_full_bar = bars + 2 * kHaloMaxStages;    // [2]
+  uint64_t* tmem_empty_bar = tmem_full_bar + 2;           // [2]
+  uint64_t* w_bar = tmem_empty_bar + 2;                   // weights resident
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(w_bar + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kHaloMaxStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    for (int a = 0; a < 2; ++a) { mbar_init(&tmem_full_bar[a], 1); mbar_init(&tmem_empty_bar[a], 8); }
+    mbar_init(w_bar, 1);
+    fence_mbar_init();
+  }
+  if (warp == 8 && lane == 0) { prefetch_tmap(&tmap_a); prefetch_tmap(&tmap_b); }
+  if (warp == 9) { tmem_alloc(tmem_ptr_smem, kTmemCols); tmem_relinquish(); }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  const int total_tiles = p.tiles_w * p.tiles_h * p.tiles_b;
+
+  if (warp == 8) {
+    // ------------------------------------------------------------ TMA producer
+    const uint32_t a_base = smem_u32(smem_a), full_base = smem_u32(full_bar);
+    if (elect_one()) {
+      const uint32_t wb = smem_u32(w_bar);
+      mbar_arrive_expect_tx_u32(wb, static_cast<uint32_t>(hp.n_taps * S::kWTapBytes));
+      for (int t = 0; t < hp.n_taps; ++t)
+        tma_load_2d_u32(smem_u32(smem_w) + t * S::kWTapBytes, &tmap_b, wb, t * BLOCK_K, 0);
+    }
+    __syncwarp();
+    int stage = 0; uint32_t phase = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      const int wt = tile % p.tiles_w;
+      const int ht = (tile / p.tiles_w) % p.tiles_h;
+      const int bt = tile / (p.tiles_w * p.tiles_h);
+      const int w0 = wt * p.box_w, h0 = ht * p.box_h;
+      for (int l = 0; l < hp.n_loads; ++l) {
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        if (elect_one()) {
+          const uint32_t fb = full_base + stage * 8;
+          mbar_arrive_expect_tx_u32(fb, hp.box_bytes);
+          tma_load_5d_u32(a_base + stage * hp.stage_bytes, &tmap_a, fb, hp.ld_c0[l], w0 + hp.ld_d1[l], hp.ld_d2[l],
+                          h0 + hp.ld_d3[l], bt);
+        }
+        __syncwarp();
+        if (++stage == hp.n_stages) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 9) {
+    // ------------------------------------------------------------ MMA issuer (one elected lane issues)
+    const uint64_t a_desc0 = make_smem_desc(smem_u32(smem_a), 0, kSBO, kSwizzleLayout);
+    const uint64_t w_desc0 = make_smem_desc(smem_u32(smem_w), 0, kSBO, kSwizzleLayout);
+    const uint32_t empty_base = smem_u32(empty_bar);
+    mbar_wait(w_bar, 0);
+    int stage = 0; uint32_t phase = 0;
+    int acc = 0; uint32_t acc_phase = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      mbar_wait(&tmem_empty_bar[acc], acc_phase ^ 1);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + acc * BLOCK_N;
+      for (int l = 0; l < hp.n_loads; ++l) {
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after();
+        if (elect_one()) {
+          const uint64_t da0 = a_desc0 + static_cast<uint64_t>((stage * hp.stage_bytes) >> 4);
+          const int t0 = hp.ld_tap0[l], t1 = t0 + hp.ld_ntaps[l];
+          for (int t = t0; t < t1; ++t) {
+            const uint64_t da = da0 + static_cast<uint64_t>(hp.tap_aoff[t] >> 4);
+            const uint64_t db = w_desc0 + static_cast<uint64_t>(hp.tap_w[t] * (S::kWTapBytes >> 4));
+#pragma unroll
+            for (int k = 0; k < BLOCK_K / 16; ++k)
+              umma_f16_ss(d_tmem, da + 2 * k, db + 2 * k, kIdesc, (l | (t - t0) | k) != 0 ? 1u : 0u);
+          }
+          umma_commit_u32(empty_base + stage * 8);
+        }
+        __syncwarp();
+        if (++stage == hp.n_stages) { stage = 0; phase ^= 1; }
+      }
+      if (elect_one()) umma_commit(&tmem_full_bar[acc]);
+      __syncwarp();
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+  } else {
+    gemm_epilogue<BLOCK_N, false, RES>(p, smem_stage, tmem_base, tmem_full_bar, tmem_empty_bar, total_tiles, warp, lane);
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 9) { tc_fence_after(); tmem_dealloc(tmem_base, kTmemCols); }
+}
+
+}  // namespace rmb

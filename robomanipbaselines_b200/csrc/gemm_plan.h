@@ -1,8 +1,11 @@
 // Host-side planning of gemm_tc_kernel launches: tensor maps, tap tables, row tiling.
 #pragma once
+#include <string.h>
+
 #include <algorithm>
 #include <string>
 
+#include "conv_halo.cuh"
 #include "gemm_tc.cuh"
 #include "tma_host.h"
 
@@ -171,19 +174,35 @@ inline bool plan_conv1(GemmPlan* g, const void* in_padded, int B, int H, int W, 
   return true;
 }
 
-template <int BN, int BK, int ST>
-inline cudaError_t launch_gemm_variant(const GemmPlan& g, int num_sms, cudaStream_t stream) {
+template <int BN, int BK, int ST, bool OUT_F32, int RES>
+inline cudaError_t launch_gemm_instance(const GemmPlan& g, int num_sms, cudaStream_t stream) {
   using S = GemmSmem<BN, BK, ST>;
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<BN, BK, ST>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal);
+    cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<BN, BK, ST, OUT_F32, RES>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal);
     if (e != cudaSuccess) return e;
     attr_set = true;
   }
   const long long tiles = 1ll * g.p.tiles_w * g.p.tiles_h * g.p.tiles_b * g.p.n_col_tiles;
   const int grid = static_cast<int>(std::min<long long>(tiles, num_sms));
-  gemm_tc_kernel<BN, BK, ST><<<grid, kGemmThreads, S::kTotal, stream>>>(g.ta, g.tb, g.p);
+  gemm_tc_kernel<BN, BK, ST, OUT_F32, RES><<<grid, kGemmThreads, S::kTotal, stream>>>(g.ta, g.tb, g.p);
   return cudaGetLastError();
+}
+
+// epilogue modes in use: act out (+ act residual) for the convs and QKV / FFN-up projections; fp32 out (+ fp32
+// residual) for the transformer's residual stream
+template <int BN, int BK, int ST>
+inline cudaError_t launch_gemm_variant(const GemmPlan& g, int num_sms, cudaStream_t stream) {
+  const bool has_res = g.p.residual != nullptr;
+  if (!g.p.out_f32) {
+    if (!has_res) return launch_gemm_instance<BN, BK, ST, false, 0>(g, num_sms, stream);
+    if (!g.p.res_f32) return launch_gemm_instance<BN, BK, ST, false, 1>(g, num_sms, stream);
+  } else {
+    if (!has_res) return launch_gemm_instance<BN, BK, ST, true, 0>(g, num_sms, stream);
+    if (g.p.res_f32) return launch_gemm_instance<BN, BK, ST, true, 2>(g, num_sms, stream);
+    return launch_gemm_instance<BN, BK, ST, true, 1>(g, num_sms, stream);
+  }
+  return cudaErrorInvalidValue;   // act out + fp32 residual: not needed on this path
 }
 
 inline cudaError_t launch_gemm(const GemmPlan& g, int num_sms, cudaStream_t stream) {
@@ -192,6 +211,151 @@ inline cudaError_t launch_gemm(const GemmPlan& g, int num_sms, cudaStream_t stre
   if (g.block_k == 64 && g.block_n == 128) return launch_gemm_variant<128, 64, 6>(g, num_sms, stream);
   if (g.block_k == 64 && g.block_n == 256) return launch_gemm_variant<256, 64, 4>(g, num_sms, stream);
   return cudaErrorInvalidValue;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Halo-reuse convs (conv_halo.cuh)
+struct HaloPlan {
+  CUtensorMap ta, tb;
+  HaloParams hp;
+  int block_k = 0;
+  int smem = 0;
+  long long flops = 0;
+};
+
+constexpr int kMaxDynSmem = 232448;   // 227 KB per CTA on sm_100
+
+// pixel box for a halo conv: box_w a multiple of 8 (tap shifts must be whole 8-row swizzle atoms), 128 rows per tile
+inline void pick_halo_box(int OW, int OH, int halo_rows, int* bw, int* bh) {
+  double best = -1.0; long long best_bytes = 0;
+  for (int w = 8; w <= 128; w *= 2) {
+    const int h = 128 / w;
+    const long long tw = (OW + w - 1) / w, th = (OH + h - 1) / h;
+    const double eff = static_cast<double>(OW) * OH / (static_cast<double>(tw * th) * 128.0);
+    const long long bytes = static_cast<long long>(h + halo_rows) * w;
+    if (eff > best + 1e-9 || (eff > best - 1e-9 && bytes < best_bytes)) { best = eff; best_bytes = bytes; *bw = w; *bh = h; }
+  }
+}
+
+inline void halo_fill_tiles(GemmParams& p, int OW, int OH, int B, int bw, int bh) {
+  p.box_w = bw; p.box_h = bh; p.box_b = 1;
+  p.W = OW; p.H = OH; p.B = B;
+  p.tiles_w = (OW + bw - 1) / bw; p.tiles_h = (OH + bh - 1) / bh; p.tiles_b = B;
+  p.n_col_tiles = 1; p.num_taps = 0; p.chunks_per_tap = 0;
+  for (int t = 0; t < kMaxTaps; ++t) { p.tap_c0[t] = p.tap_d1[t] = p.tap_d2[t] = p.tap_d3[t] = 0; }
+}
+
+inline bool conv3x3_halo_eligible(int W, int Cin, int Cout, int ksize, int stride) {
+  return Cin == 64 && Cout == 64 && ksize == 3 && stride == 1 && W >= 8;
+}
+
+// 3x3 stride-1 pad-1 conv, Cin = Cout = 64, NHWC act_t; Wt [64, 9*64] tap-major; residual (optional) act_t [rows, 64]
+inline bool plan_conv3x3_halo(HaloPlan* g, const void* in, int B, int H, int W, const void* Wt, const float* bias,
+                              const void* residual, void* out, bool relu, std::string* err) {
+  *g = HaloPlan();
+  g->block_k = 64;
+  HaloParams& hp = g->hp;
+  memset(&hp, 0, sizeof(hp));
+  int bw = 8, bh = 16;
+  pick_halo_box(W, H, 2, &bw, &bh);
+  halo_fill_tiles(hp.g, W, H, B, bw, bh);
+  fill_common(hp.g, bias, residual, 64, false, out, 64, false, relu);
+  hp.n_loads = 3; hp.n_taps = 9;
+  hp.box_bytes = static_cast<uint32_t>((bh + 2) * bw * 128);
+  hp.stage_bytes = hp.box_bytes;                      // bw % 8 == 0 -> already a multiple of 1024
+  for (int kw = 0; kw < 3; ++kw) {
+    hp.ld_c0[kw] = 0; hp.ld_d1[kw] = kw - 1; hp.ld_d2[kw] = 0; hp.ld_d3[kw] = -1;
+    hp.ld_tap0[kw] = 3 * kw; hp.ld_ntaps[kw] = 3;
+    for (int kh = 0; kh < 3; ++kh) {
+      hp.tap_aoff[3 * kw + kh] = static_cast<uint32_t>(kh * bw * 128);
+      hp.tap_w[3 * kw + kh] = kh * 3 + kw;
+    }
+  }
+  const int fixed = 9 * HaloSmem<64>::kWTapBytes + HaloSmem<64>::kStagingBytes + HaloSmem<64>::kBarrierBytes + 1024;
+  hp.n_stages = std::min<int>(kHaloMaxStages, (kMaxDynSmem - fixed) / static_cast<int>(hp.stage_bytes));
+  if (hp.n_stages < 2) { if (err) *err = "plan_conv3x3_halo: tile does not fit shared memory"; return false; }
+  g->smem = HaloSmem<64>::total(9, hp.n_stages, hp.stage_bytes);
+  const uint64_t e = 2, Cin = 64;
+  const uint64_t dims[5] = {Cin, (uint64_t)W, 1, (uint64_t)H, (uint64_t)B};
+  const uint64_t strides[4] = {Cin * e, (uint64_t)W * Cin * e, (uint64_t)W * Cin * e, (uint64_t)H * W * Cin * e};
+  const uint32_t box[5] = {64, (uint32_t)bw, 1, (uint32_t)(bh + 2), 1};
+  if (!make_tmap_act(&g->ta, in, 5, dims, strides, box, 128, err)) return false;
+  const uint64_t wdims[2] = {576, 64};
+  const uint64_t wstr[1] = {576 * e};
+  const uint32_t wbox[2] = {64, 64};
+  if (!make_tmap_act(&g->tb, Wt, 2, wdims, wstr, wbox, 128, err)) return false;
+  g->flops = 2ll * B * H * W * 64 * 576;
+  return true;
+}
+
+// ResNet stem 7x7/2 pad 3 on the padded NHWC4 image (see plan_conv1 for the overlapping-window view):
+// box 0 = odd input rows (filter rows kh = 0,2,4,6), box 1 = even input rows (kh = 1,3,5).
+inline bool plan_conv1_halo(HaloPlan* g, const void* in_padded, int B, int H, int W, const void* Wt, const float* bias,
+                            void* out, std::string* err) {
+  *g = HaloPlan();
+  g->block_k = 32;
+  if (H % 2 != 0 || W % 4 != 0) { if (err) *err = "plan_conv1_halo: H must be even and W a multiple of 4"; return false; }
+  const int OH = H / 2, OW = W / 2, Wp = W + 8;
+  HaloParams& hp = g->hp;
+  memset(&hp, 0, sizeof(hp));
+  int bw = 8, bh = 16;
+  pick_halo_box(OW, OH, 3, &bw, &bh);
+  halo_fill_tiles(hp.g, OW, OH, B, bw, bh);
+  fill_common(hp.g, bias, nullptr, 0, false, out, 64, false, true);
+  hp.n_loads = 2; hp.n_taps = 7;
+  hp.box_bytes = static_cast<uint32_t>((bh + 3) * bw * 64);
+  hp.stage_bytes = (hp.box_bytes + 1023u) & ~1023u;
+  // input row of filter row kh for output row oh: 2*oh + kh - 3 = 2*(oh + h2) + ph
+  int t = 0;
+  for (int ph = 1; ph >= 0; --ph) {
+    const int l = 1 - ph;
+    const int d3 = (ph == 1) ? -2 : -1;               // first H/2-row of the box relative to the tile's first output row
+    hp.ld_c0[l] = 0; hp.ld_d1[l] = 0; hp.ld_d2[l] = ph; hp.ld_d3[l] = d3;
+    hp.ld_tap0[l] = t; hp.ld_ntaps[l] = 0;
+    for (int kh = 0; kh < 7; ++kh) {
+      const int o = kh - 3;
+      const int h2 = (o >= 0) ? o / 2 : -((-o + 1) / 2);
+      if (o - 2 * h2 != ph) continue;
+      hp.tap_aoff[t] = static_cast<uint32_t>((h2 - d3) * bw * 64);
+      hp.tap_w[t] = kh;
+      ++t; ++hp.ld_ntaps[l];
+    }
+  }
+  const int fixed = 7 * HaloSmem<32>::kWTapBytes + HaloSmem<32>::kStagingBytes + HaloSmem<32>::kBarrierBytes + 1024;
+  hp.n_stages = std::min<int>(kHaloMaxStages, (kMaxDynSmem - fixed) / static_cast<int>(hp.stage_bytes));
+  if (hp.n_stages < 2) { if (err) *err = "plan_conv1_halo: tile does not fit shared memory"; return false; }
+  g->smem = HaloSmem<32>::total(7, hp.n_stages, hp.stage_bytes);
+  const uint64_t rowb = (uint64_t)Wp * 8;                    // bytes per padded image row
+  const uint64_t dims[5] = {32, (uint64_t)OW, 2, (uint64_t)H / 2, (uint64_t)B};
+  const uint64_t strides[4] = {16, rowb, 2 * rowb, (uint64_t)H * rowb};
+  const uint32_t box[5] = {32, (uint32_t)bw, 1, (uint32_t)(bh + 3), 1};
+  if (!make_tmap_act(&g->ta, in_padded, 5, dims, strides, box, 64, err)) return false;
+  const uint64_t wdims[2] = {224, 64};
+  const uint64_t wstr[1] = {224 * 2};
+  const uint32_t wbox[2] = {32, 64};
+  if (!make_tmap_act(&g->tb, Wt, 2, wdims, wstr, wbox, 64, err)) return false;
+  g->flops = 2ll * B * OH * OW * 64 * 147;
+  return true;
+}
+
+template <int BK, int RES>
+inline cudaError_t launch_halo_instance(const HaloPlan& g, int num_sms, cudaStream_t stream) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(conv_halo_kernel<BK, RES>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
+    if (e != cudaSuccess) return e;
+    attr_set = true;
+  }
+  const long long tiles = 1ll * g.hp.g.tiles_w * g.hp.g.tiles_h * g.hp.g.tiles_b;
+  const int grid = static_cast<int>(std::min<long long>(tiles, num_sms));
+  conv_halo_kernel<BK, RES><<<grid, kGemmThreads, g.smem, stream>>>(g.ta, g.tb, g.hp);
+  return cudaGetLastError();
+}
+
+inline cudaError_t launch_halo(const HaloPlan& g, int num_sms, cudaStream_t stream) {
+  if (g.block_k == 32) return launch_halo_instance<32, 0>(g, num_sms, stream);
+  if (g.hp.g.residual != nullptr) return launch_halo_instance<64, 1>(g, num_sms, stream);
+  return launch_halo_instance<64, 0>(g, num_sms, stream);
 }
 
 }  // namespace rmb

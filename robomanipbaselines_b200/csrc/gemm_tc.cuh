@@ -14,7 +14,7 @@
 namespace rmb {
 
 constexpr int kMaxTaps = 9;
-constexpr int kGemmThreads = 192;  // warps 0-3: epilogue, warp 4: TMA producer, warp 5: MMA issuer + TMEM owner
+constexpr int kGemmThreads = 320;  // warps 0-7: epilogue, warp 8: TMA producer, warp 9: MMA issuer + TMEM owner
 
 struct GemmParams {
   // row (pixel) tiling
@@ -45,11 +45,131 @@ struct GemmSmem {
   static constexpr int kBBytes = BLOCK_N * BLOCK_K * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kBarrierBytes = 256;
-  static constexpr int kStagingBytes = 4 * 4096;   // epilogue: one 32 x 128 B staging tile per warp
+  static constexpr int kStagingBytes = 8 * 4096;   // epilogue: one 32 x 128 B staging tile per warp
   static constexpr int kTotal = STAGES * kStageBytes + kStagingBytes + kBarrierBytes + 1024;  // +1024: alignment slack
 };
 
-template <int BLOCK_N, int BLOCK_K, int STAGES>
+// ---------------------------------------------------------------------------------------------------------------------
+// Epilogue shared by the GEMM / conv kernels (warps 0..7 of the CTA).
+template <int BLOCK_N, bool OUT_F32, int RES>
+__device__ __forceinline__ void gemm_epilogue(const GemmParams& p, uint8_t* smem_stage, uint32_t tmem_base,
+                                              uint64_t* tmem_full_bar, uint64_t* tmem_empty_bar, int total_tiles,
+                                              int warp, int lane) {
+  const int rows_per_tile = p.box_w * p.box_h * p.box_b;
+  // ------------------------------------------------------------ epilogue warps 0..7
+  // Warp e reads TMEM lanes 32*(e%4)..+31 (hardware rule: lane quarter = warp id % 4) and the 32-column chunks
+  // ci with ci % 2 == e/4. Two passes per chunk so that global traffic is coalesced:
+  //   pass 1: thread = accumulator row; tcgen05.ld 32 fp32 columns -> per-warp smem staging tile (32 rows x 128 B,
+  //           16-byte groups XOR-swizzled by row & 7: conflict-free for both passes)
+  //   pass 2: 8 lanes = one row (8 x 16 B = the row's 128 B), 4 rows per instruction; bias / residual / ReLU here,
+  //           so residual loads and output stores are full 64-128 B row segments.
+  // The next chunk's tcgen05.ld is in flight while pass 2 runs. Output / residual modes are template parameters and
+  // row pointers are built once per tile: a single warp per scheduler is instruction-latency bound, so the
+  // per-chunk instruction count is what sets the epilogue rate.
+  constexpr int kChunksPerWarp = BLOCK_N / 64;
+  constexpr int kOutEsz = OUT_F32 ? 4 : 2;
+  constexpr int kResEsz = (RES == 2) ? 4 : 2;
+  int acc = 0; uint32_t acc_phase = 0;
+  const int q = warp & 3, half = warp >> 2;
+  const int r = q * 32 + lane;                    // row of the tile owned by this thread in pass 1
+  const int wl = r % p.box_w;
+  const int hl = (r / p.box_w) % p.box_h;
+  const int bl = r / (p.box_w * p.box_h);
+  const int sub = lane & 7, rsel = lane >> 3;
+  const uint32_t stg = smem_u32(smem_stage + warp * 4096);
+  uint32_t st_addr[8];
+  #pragma unroll
+  for (int g = 0; g < 8; ++g) st_addr[g] = stg + lane * 128 + ((g ^ (lane & 7)) << 4);
+  const uint32_t ld_even = stg + rsel * 128 + ((sub ^ rsel) << 4);
+  const uint32_t ld_odd = stg + (rsel + 4) * 128 + ((sub ^ (rsel + 4)) << 4);
+  const float relu_floor = p.relu ? 0.0f : -INFINITY;
+  const int col_in_tile = half * 32 + sub * 4;    // first of this lane's 4 columns inside chunk 0 of this warp
+  for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+    const int ct = tile % p.n_col_tiles;
+    const int rt = tile / p.n_col_tiles;
+    const int wt = rt % p.tiles_w;
+    const int ht = (rt / p.tiles_w) % p.tiles_h;
+    const int bt = rt / (p.tiles_w * p.tiles_h);
+    const int w = wt * p.box_w + wl, h = ht * p.box_h + hl, b = bt * p.box_b + bl;
+    const bool valid = (r < rows_per_tile) && (w < p.W) && (h < p.H) && (b < p.B);
+    int my_grow = -1, my_orow = -1;               // source row (residual, natural pixel order) / destination row
+    if (valid) {
+      my_grow = (b * p.H + h) * p.W + w;
+      my_orow = my_grow;
+      if (p.remap_ncam > 0)
+        my_orow = (b / p.remap_ncam) * p.remap_L + p.remap_off + h * (p.W * p.remap_ncam) + (b % p.remap_ncam) * p.W + w;
+    }
+    const int col0 = ct * BLOCK_N + col_in_tile;
+    char* optr[8];
+    const char* rptr[8];
+  #pragma unroll
+    for (int it = 0; it < 8; ++it) {
+      const int orow = __shfl_sync(0xffffffffu, my_orow, it * 4 + rsel);
+      optr[it] = (orow >= 0) ? static_cast<char*>(p.out) + (static_cast<long long>(orow) * p.ld_out + col0) * kOutEsz : nullptr;
+      if (RES != 0) {
+        const int grow = __shfl_sync(0xffffffffu, my_grow, it * 4 + rsel);
+        rptr[it] = static_cast<const char*>(p.residual) + (static_cast<long long>(grow < 0 ? 0 : grow) * p.ld_res + col0) * kResEsz;
+      } else {
+        rptr[it] = nullptr;
+      }
+    }
+    const float* bias_ptr = (p.bias != nullptr) ? p.bias + col0 : nullptr;
+    mbar_wait(&tmem_full_bar[acc], acc_phase);
+    tc_fence_after();
+    const uint32_t t_row = tmem_base + acc * BLOCK_N + half * 32 + (static_cast<uint32_t>(q * 32) << 16);
+    uint32_t v[32];
+    tmem_ld_32x32b_x32(t_row, v);
+  #pragma unroll
+    for (int j = 0; j < kChunksPerWarp; ++j) {      // this warp's chunk j = columns half*32 + j*64 .. +31 of the tile
+      tmem_ld_wait();
+  #pragma unroll
+      for (int g = 0; g < 8; ++g) st_shared_v4(st_addr[g], v[4 * g], v[4 * g + 1], v[4 * g + 2], v[4 * g + 3]);
+      if (j + 1 < kChunksPerWarp) tmem_ld_32x32b_x32(t_row + (j + 1) * 64, v);
+      else tc_fence_before();
+      __syncwarp();
+      if (j + 1 == kChunksPerWarp && lane == 0) mbar_arrive(&tmem_empty_bar[acc]);   // 8 arrivals free the accumulator
+      float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (bias_ptr != nullptr) bv = __ldg(reinterpret_cast<const float4*>(bias_ptr + j * 64));
+      float4 f[8];
+  #pragma unroll
+      for (int it = 0; it < 8; ++it) f[it] = ld_shared_v4f(((it & 1) ? ld_odd : ld_even) + (it >> 1) * 1024);
+      if (RES == 2) {
+        float4 rv[8];
+  #pragma unroll
+        for (int it = 0; it < 8; ++it)
+          rv[it] = (optr[it] != nullptr) ? __ldg(reinterpret_cast<const float4*>(rptr[it] + j * 64 * kResEsz))
+                                         : make_float4(0.f, 0.f, 0.f, 0.f);
+  #pragma unroll
+        for (int it = 0; it < 8; ++it) { f[it].x += rv[it].x; f[it].y += rv[it].y; f[it].z += rv[it].z; f[it].w += rv[it].w; }
+      } else if (RES == 1) {
+        uint2 rv[8];
+  #pragma unroll
+        for (int it = 0; it < 8; ++it)
+          rv[it] = (optr[it] != nullptr) ? __ldg(reinterpret_cast<const uint2*>(rptr[it] + j * 64 * kResEsz))
+                                         : make_uint2(0u, 0u);
+  #pragma unroll
+        for (int it = 0; it < 8; ++it) {
+          const float2 lo = unpack_act2(rv[it].x), hi = unpack_act2(rv[it].y);
+          f[it].x += lo.x; f[it].y += lo.y; f[it].z += hi.x; f[it].w += hi.y;
+        }
+      }
+  #pragma unroll
+      for (int it = 0; it < 8; ++it) {
+        const float ox = fmaxf(f[it].x + bv.x, relu_floor), oy = fmaxf(f[it].y + bv.y, relu_floor);
+        const float oz = fmaxf(f[it].z + bv.z, relu_floor), ow = fmaxf(f[it].w + bv.w, relu_floor);
+        if (optr[it] != nullptr) {
+          if (OUT_F32) *reinterpret_cast<float4*>(optr[it] + j * 64 * kOutEsz) = make_float4(ox, oy, oz, ow);
+          else *reinterpret_cast<uint2*>(optr[it] + j * 64 * kOutEsz) = make_uint2(pack_act2(ox, oy), pack_act2(oz, ow));
+        }
+      }
+      __syncwarp();                                // staging tile is rewritten by the next chunk's pass 1
+    }
+    if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+  }
+}
+
+// OUT_F32: fp32 output (else act_t). RES: 0 no residual, 1 act_t residual, 2 fp32 residual.
+template <int BLOCK_N, int BLOCK_K, int STAGES, bool OUT_F32, int RES>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                const __grid_constant__ GemmParams p) {
@@ -78,11 +198,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-    for (int a = 0; a < 2; ++a) { mbar_init(&tmem_full_bar[a], 1); mbar_init(&tmem_empty_bar[a], 4); }
+    for (int a = 0; a < 2; ++a) { mbar_init(&tmem_full_bar[a], 1); mbar_init(&tmem_empty_bar[a], 8); }
     fence_mbar_init();
   }
-  if (warp == 4 && lane == 0) { prefetch_tmap(&tmap_a); prefetch_tmap(&tmap_b); }
-  if (warp == 5) { tmem_alloc(tmem_ptr_smem, kTmemCols); tmem_relinquish(); }
+  if (warp == 8 && lane == 0) { prefetch_tmap(&tmap_a); prefetch_tmap(&tmap_b); }
+  if (warp == 9) { tmem_alloc(tmem_ptr_smem, kTmemCols); tmem_relinquish(); }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -97,7 +217,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
   // The producer and MMA warps run their loops warp-uniformly (all 32 lanes, identical control flow) and only the
   // issuing instruction is predicated on one elected lane: loop state stays in uniform registers and the per-k-block
   // instruction count -- the throughput limit of a single issuing thread -- is a few dozen instead of ~150.
-  if (warp == 4) {
+  if (warp == 8) {
     // ------------------------------------------------------------ TMA producer
     const uint32_t a_base = smem_u32(smem_a), b_base = smem_u32(smem_b), full_base = smem_u32(full_bar);
     int stage = 0; uint32_t phase = 0;
@@ -126,7 +246,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         }
       }
     }
-  } else if (warp == 5) {
+  } else if (warp == 9) {
     // ------------------------------------------------------------ MMA issuer (one elected lane issues)
     const uint64_t a_desc0 = make_smem_desc(smem_u32(smem_a), 0, kSBO, kSwizzleLayout);
     const uint64_t b_desc0 = make_smem_desc(smem_u32(smem_b), 0, kSBO, kSwizzleLayout);
@@ -157,112 +277,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
   } else {
-    // ------------------------------------------------------------ epilogue warps 0..3 (TMEM lanes 32*warp..+31)
-    // Two passes per 32-column chunk so that global traffic is coalesced:
-    //   pass 1: thread = accumulator row; tcgen05.ld 32 fp32 columns -> per-warp smem staging tile (32 rows x 128 B,
-    //           16-byte groups XOR-swizzled by row & 7: conflict-free for both passes)
-    //   pass 2: 8 lanes = one row (8 x 16 B = the row's 128 B), 4 rows per instruction; bias / residual / ReLU here,
-    //           so residual loads and output stores are full 64-128 B row segments.
-    // The next chunk's tcgen05.ld is in flight while pass 2 runs.
-    int acc = 0; uint32_t acc_phase = 0;
-    const int r = warp * 32 + lane;                 // row of the tile owned by this thread in pass 1
-    const int wl = r % p.box_w;
-    const int hl = (r / p.box_w) % p.box_h;
-    const int bl = r / (p.box_w * p.box_h);
-    uint8_t* stg = smem_stage + warp * 4096;
-    const int sub = lane & 7, rsel = lane >> 3;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-      const int ct = tile % p.n_col_tiles;
-      const int rt = tile / p.n_col_tiles;
-      const int wt = rt % p.tiles_w;
-      const int ht = (rt / p.tiles_w) % p.tiles_h;
-      const int bt = rt / (p.tiles_w * p.tiles_h);
-      const int w = wt * p.box_w + wl, h = ht * p.box_h + hl, b = bt * p.box_b + bl;
-      const bool valid = (r < rows_per_tile) && (w < p.W) && (h < p.H) && (b < p.B);
-      int my_grow = -1, my_orow = -1;               // source row (residual, natural pixel order) / destination row
-      if (valid) {
-        my_grow = (b * p.H + h) * p.W + w;
-        my_orow = my_grow;
-        if (p.remap_ncam > 0)
-          my_orow = (b / p.remap_ncam) * p.remap_L + p.remap_off + h * (p.W * p.remap_ncam) + (b % p.remap_ncam) * p.W + w;
-      }
-      int grow_it[8], orow_it[8];
-#pragma unroll
-      for (int it = 0; it < 8; ++it) {
-        grow_it[it] = __shfl_sync(0xffffffffu, my_grow, it * 4 + rsel);
-        orow_it[it] = __shfl_sync(0xffffffffu, my_orow, it * 4 + rsel);
-      }
-      mbar_wait(&tmem_full_bar[acc], acc_phase);
-      tc_fence_after();
-      const uint32_t t_row = tmem_base + acc * BLOCK_N + (static_cast<uint32_t>(warp * 32) << 16);
-      uint32_t v[32];
-      tmem_ld_32x32b_x32(t_row, v);
-#pragma unroll 1
-      for (int c = 0; c < BLOCK_N; c += 32) {
-        tmem_ld_wait();
-#pragma unroll
-        for (int g = 0; g < 8; ++g)
-          *reinterpret_cast<uint4*>(stg + lane * 128 + ((g ^ (lane & 7)) << 4)) =
-              make_uint4(v[4 * g], v[4 * g + 1], v[4 * g + 2], v[4 * g + 3]);
-        const bool last = (c + 32 >= BLOCK_N);
-        if (!last) tmem_ld_32x32b_x32(t_row + c + 32, v);
-        else tc_fence_before();
-        __syncwarp();
-        if (last && lane == 0) mbar_arrive(&tmem_empty_bar[acc]);   // 4 arrivals (one per warp) free the accumulator
-        const int col = ct * BLOCK_N + c + sub * 4;
-        float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (p.bias != nullptr) bv = __ldg(reinterpret_cast<const float4*>(p.bias + col));
-        float4 f[8];
-#pragma unroll
-        for (int it = 0; it < 8; ++it) {
-          const int i = it * 4 + rsel;
-          f[it] = *reinterpret_cast<const float4*>(stg + i * 128 + ((sub ^ (i & 7)) << 4));
-        }
-        if (p.residual != nullptr) {
-          if (p.res_f32) {
-            float4 rv[8];
-#pragma unroll
-            for (int it = 0; it < 8; ++it)
-              rv[it] = (grow_it[it] >= 0)
-                           ? __ldg(reinterpret_cast<const float4*>(static_cast<const float*>(p.residual) +
-                                                                   static_cast<long long>(grow_it[it]) * p.ld_res + col))
-                           : make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-            for (int it = 0; it < 8; ++it) { f[it].x += rv[it].x; f[it].y += rv[it].y; f[it].z += rv[it].z; f[it].w += rv[it].w; }
-          } else {
-            uint2 rv[8];
-#pragma unroll
-            for (int it = 0; it < 8; ++it)
-              rv[it] = (grow_it[it] >= 0)
-                           ? __ldg(reinterpret_cast<const uint2*>(static_cast<const act_t*>(p.residual) +
-                                                                  static_cast<long long>(grow_it[it]) * p.ld_res + col))
-                           : make_uint2(0u, 0u);
-#pragma unroll
-            for (int it = 0; it < 8; ++it) {
-              const float2 lo = unpack_act2(rv[it].x), hi = unpack_act2(rv[it].y);
-              f[it].x += lo.x; f[it].y += lo.y; f[it].z += hi.x; f[it].w += hi.y;
-            }
-          }
-        }
-#pragma unroll
-        for (int it = 0; it < 8; ++it) {
-          float4 o = make_float4(f[it].x + bv.x, f[it].y + bv.y, f[it].z + bv.z, f[it].w + bv.w);
-          if (p.relu) { o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f); }
-          if (orow_it[it] >= 0) {
-            const long long off = static_cast<long long>(orow_it[it]) * p.ld_out + col;
-            if (p.out_f32) *reinterpret_cast<float4*>(static_cast<float*>(p.out) + off) = o;
-            else *reinterpret_cast<uint2*>(static_cast<act_t*>(p.out) + off) = make_uint2(pack_act2(o.x, o.y), pack_act2(o.z, o.w));
-          }
-        }
-        __syncwarp();                                // staging tile is rewritten by the next chunk's pass 1
-      }
-      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
-    }
+    gemm_epilogue<BLOCK_N, OUT_F32, RES>(p, smem_stage, tmem_base, tmem_full_bar, tmem_empty_bar, total_tiles, warp, lane);
   }
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 5) { tc_fence_after(); tmem_dealloc(tmem_base, kTmemCols); }
+  if (warp == 9) { tc_fence_after(); tmem_dealloc(tmem_base, kTmemCols); }
 }
 
 }  // namespace rmb
