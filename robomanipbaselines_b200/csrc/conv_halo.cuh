@@ -38,16 +38,110 @@ struct HaloParams {
 template <int BLOCK_K>
 struct HaloSmem {
   static constexpr int kWTapBytes = 64 * BLOCK_K * 2;
-  static constexpr int kStagingBytes = 8 * 4096;
+  static constexpr int kStagingBytes = 2 * 16384;   // epilogue: output tile + residual tile (128 px x 64 ch act_t each)
   static constexpr int kBarrierBytes = 256;
   static int total(int n_taps, int n_stages, uint32_t stage_bytes) {
     return n_taps * kWTapBytes + n_stages * static_cast<int>(stage_bytes) + kStagingBytes + kBarrierBytes + 1024;
   }
 };
 
+// Epilogue of the halo conv (warps 0..7): TMEM -> registers (+bias, +residual, ReLU) -> 16-bit tile in shared memory in
+// the TMA layout -> ONE cp.async.bulk.tensor store per tile (coalesced by hardware, clipped at the image border).
+// Thread = accumulator row (TMEM lane quarter = warp % 4) x 32 of the 64 output channels (warp / 4). The residual tile
+// (identity branch of the BasicBlock) arrives by TMA as well, issued one tile ahead by the store-issuing thread.
+template <int RES>
+__device__ __forceinline__ void halo_epilogue(const CUtensorMap* tmap_out, const CUtensorMap* tmap_res,
+                                              const GemmParams& p, uint8_t* out_stage, uint8_t* res_stage,
+                                              uint64_t* res_full, uint32_t tmem_base, uint64_t* tmem_full_bar,
+                                              uint64_t* tmem_empty_bar, int total_tiles, int warp, int lane) {
+  const int q = warp & 3, half = warp >> 2;
+  const int r = q * 32 + lane;
+  const bool issuer = (threadIdx.x == 0);
+  float bias[32];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const float4 b4 = (p.bias != nullptr) ? __ldg(reinterpret_cast<const float4*>(p.bias + half * 32) + i)
+                                          : make_float4(0.f, 0.f, 0.f, 0.f);
+    bias[4 * i] = b4.x; bias[4 * i + 1] = b4.y; bias[4 * i + 2] = b4.z; bias[4 * i + 3] = b4.w;
+  }
+  const float relu_floor = p.relu ? 0.0f : -INFINITY;
+  const uint32_t out_base = smem_u32(out_stage), res_base = smem_u32(res_stage);
+  uint32_t off[4];                                   // this thread's four 16-byte chunks inside its 128-byte row
+#pragma unroll
+  for (int c = 0; c < 4; ++c) off[c] = r * 128 + (((half * 4 + c) ^ (r & 7)) << 4);
+  const uint32_t res_bar = smem_u32(res_full);
+  const uint32_t tile_bytes = 128u * 128u;
+  auto tile_origin = [&](int tile, int* w0, int* h0, int* bt) {
+    *w0 = (tile % p.tiles_w) * p.box_w;
+    *h0 = ((tile / p.tiles_w) % p.tiles_h) * p.box_h;
+    *bt = tile / (p.tiles_w * p.tiles_h);
+  };
+  if (RES != 0 && issuer && static_cast<int>(blockIdx.x) < total_tiles) {
+    int w0, h0, bt;
+    tile_origin(blockIdx.x, &w0, &h0, &bt);
+    mbar_arrive_expect_tx_u32(res_bar, tile_bytes);
+    tma_load_5d_u32(res_base, tmap_res, res_bar, 0, w0, 0, h0, bt);
+  }
+  int acc = 0; uint32_t acc_phase = 0, res_phase = 0;
+  for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+    mbar_wait(&tmem_full_bar[acc], acc_phase);
+    tc_fence_after();
+    uint32_t v[32];
+    tmem_ld_32x32b_x32(tmem_base + acc * 64 + half * 32 + (static_cast<uint32_t>(q * 32) << 16), v);
+    tmem_ld_wait();
+    tc_fence_before();
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);          // 8 arrivals free the accumulator for the next tile
+    float f[32];
+#pragma unroll
+    for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]) + bias[i];
+    if (RES != 0) {
+      mbar_wait(res_full, res_phase);
+      res_phase ^= 1;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        const uint4 rv = ld_shared_v4u(res_base + off[c]);
+        const uint32_t u[4] = {rv.x, rv.y, rv.z, rv.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float2 t = unpack_act2(u[j]);
+          f[8 * c + 2 * j] += t.x; f[8 * c + 2 * j + 1] += t.y;
+        }
+      }
+    }
+    if (issuer) bulk_wait_group_read0();                        // the previous tile's store has read out_stage
+    named_bar_sync(1, 256);
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      uint32_t w[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        w[j] = pack_act2(fmaxf(f[8 * c + 2 * j], relu_floor), fmaxf(f[8 * c + 2 * j + 1], relu_floor));
+      st_shared_v4(out_base + off[c], w[0], w[1], w[2], w[3]);
+    }
+    fence_proxy_async_smem();                                   // generic-proxy writes -> visible to the TMA store
+    named_bar_sync(1, 256);                                     // tile complete; residual tile consumed by everyone
+    if (issuer) {
+      int w0, h0, bt;
+      tile_origin(tile, &w0, &h0, &bt);
+      tma_store_5d(tmap_out, out_base, 0, w0, 0, h0, bt);
+      bulk_commit_group();
+      const int next = tile + gridDim.x;
+      if (RES != 0 && next < total_tiles) {
+        tile_origin(next, &w0, &h0, &bt);
+        mbar_arrive_expect_tx_u32(res_bar, tile_bytes);
+        tma_load_5d_u32(res_base, tmap_res, res_bar, 0, w0, 0, h0, bt);
+      }
+    }
+    if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+  }
+  if (issuer) bulk_wait_group0();
+}
+
 template <int BLOCK_K, int RES>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 conv_halo_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                 const __grid_constant__ CUtensorMap tmap_out, const __grid_constant__ CUtensorMap tmap_res,
                  const __grid_constant__ HaloParams hp) {
   using S = HaloSmem<BLOCK_K>;
   constexpr int BLOCK_N = 64;
@@ -68,7 +162,8 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   uint64_t* tmem_full_bar = bars + 2 * kHaloMaxStages;    // [2]
   uint64_t* tmem_empty_bar = tmem_full_bar + 2;           // [2]
   uint64_t* w_bar = tmem_empty_bar + 2;                   // weights resident
-  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(w_bar + 1);
+  uint64_t* res_full = w_bar + 1;                         // residual tile landed
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(res_full + 1);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -77,9 +172,10 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     for (int s = 0; s < kHaloMaxStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
     for (int a = 0; a < 2; ++a) { mbar_init(&tmem_full_bar[a], 1); mbar_init(&tmem_empty_bar[a], 8); }
     mbar_init(w_bar, 1);
+    mbar_init(res_full, 1);
     fence_mbar_init();
   }
-  if (warp == 8 && lane == 0) { prefetch_tmap(&tmap_a); prefetch_tmap(&tmap_b); }
+  if (warp == 8 && lane == 0) { prefetch_tmap(&tmap_a); prefetch_tmap(&tmap_b); prefetch_tmap(&tmap_out); prefetch_tmap(&tmap_res); }
   if (warp == 9) { tmem_alloc(tmem_ptr_smem, kTmemCols); tmem_relinquish(); }
   tc_fence_before();
   __syncthreads();
@@ -151,7 +247,8 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
   } else {
-    gemm_epilogue<BLOCK_N, false, RES>(p, smem_stage, tmem_base, tmem_full_bar, tmem_empty_bar, total_tiles, warp, lane);
+    halo_epilogue<RES>(&tmap_out, &tmap_res, p, smem_stage, smem_stage + 16384, res_full, tmem_base, tmem_full_bar,
+                       tmem_empty_bar, total_tiles, warp, lane);
   }
 
   tc_fence_before();

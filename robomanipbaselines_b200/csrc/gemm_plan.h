@@ -216,7 +216,7 @@ inline cudaError_t launch_gemm(const GemmPlan& g, int num_sms, cudaStream_t stre
 // ---------------------------------------------------------------------------------------------------------------------
 // Halo-reuse convs (conv_halo.cuh)
 struct HaloPlan {
-  CUtensorMap ta, tb;
+  CUtensorMap ta, tb, tout, tres;   // input boxes, weights, output tile store, residual tile load
   HaloParams hp;
   int block_k = 0;
   int smem = 0;
@@ -284,6 +284,9 @@ inline bool plan_conv3x3_halo(HaloPlan* g, const void* in, int B, int H, int W, 
   const uint64_t wstr[1] = {576 * e};
   const uint32_t wbox[2] = {64, 64};
   if (!make_tmap_act(&g->tb, Wt, 2, wdims, wstr, wbox, 128, err)) return false;
+  const uint32_t obox[5] = {64, (uint32_t)bw, 1, (uint32_t)bh, 1};
+  if (!make_tmap_act(&g->tout, out, 5, dims, strides, obox, 128, err)) return false;
+  if (!make_tmap_act(&g->tres, residual ? residual : out, 5, dims, strides, obox, 128, err)) return false;
   g->flops = 2ll * B * H * W * 64 * 576;
   return true;
 }
@@ -334,6 +337,11 @@ inline bool plan_conv1_halo(HaloPlan* g, const void* in_padded, int B, int H, in
   const uint64_t wstr[1] = {224 * 2};
   const uint32_t wbox[2] = {32, 64};
   if (!make_tmap_act(&g->tb, Wt, 2, wdims, wstr, wbox, 64, err)) return false;
+  const uint64_t odims[5] = {64, (uint64_t)OW, 1, (uint64_t)OH, (uint64_t)B};
+  const uint64_t ostr[4] = {128, (uint64_t)OW * 128, (uint64_t)OW * 128, (uint64_t)OH * OW * 128};
+  const uint32_t obox[5] = {64, (uint32_t)bw, 1, (uint32_t)bh, 1};
+  if (!make_tmap_act(&g->tout, out, 5, odims, ostr, obox, 128, err)) return false;
+  g->tres = g->tout;
   g->flops = 2ll * B * OH * OW * 64 * 147;
   return true;
 }
@@ -348,7 +356,7 @@ inline cudaError_t launch_halo_instance(const HaloPlan& g, int num_sms, cudaStre
   }
   const long long tiles = 1ll * g.hp.g.tiles_w * g.hp.g.tiles_h * g.hp.g.tiles_b;
   const int grid = static_cast<int>(std::min<long long>(tiles, num_sms));
-  conv_halo_kernel<BK, RES><<<grid, kGemmThreads, g.smem, stream>>>(g.ta, g.tb, g.hp);
+  conv_halo_kernel<BK, RES><<<grid, kGemmThreads, g.smem, stream>>>(g.ta, g.tb, g.tout, g.tres, g.hp);
   return cudaGetLastError();
 }
 

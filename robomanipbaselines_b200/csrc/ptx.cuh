@@ -46,9 +46,10 @@ constexpr uint32_t kUmmaABFormat = 0u;      // cute::UMMA::F16F32Format::F16
 constexpr uint32_t kActNegInf2 = 0xfc00fc00u;
 __host__ __device__ __forceinline__ float clamp_half(float x) { return fminf(fmaxf(x, -65504.0f), 65504.0f); }
 __host__ __device__ __forceinline__ act_t to_act(float x) { return __float2half_rn(clamp_half(x)); }
-__device__ __forceinline__ uint32_t pack_act2(float lo, float hi) {
-  __half2 v = __floats2half2_rn(clamp_half(lo), clamp_half(hi));
-  return *reinterpret_cast<uint32_t*>(&v);
+__device__ __forceinline__ uint32_t pack_act2(float lo, float hi) {   // one F2FP.SATFINITE: clamps to +-65504
+  uint32_t r;
+  asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
 }
 __device__ __forceinline__ float2 unpack_act2(uint32_t u) { return __half22float2(*reinterpret_cast<__half2*>(&u)); }
 __device__ __forceinline__ uint32_t act2_max(uint32_t a, uint32_t b) {
@@ -168,6 +169,25 @@ __device__ __forceinline__ void tma_load_5d(void* smem_dst, const void* tmap, ui
       "%7}], [%2];" ::"r"(smem_u32(smem_dst)),
       "l"(reinterpret_cast<uint64_t>(tmap)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4)
       : "memory");
+}
+
+// TMA store (shared -> global), bulk-group completion
+__device__ __forceinline__ void tma_store_5d(const void* tmap, uint32_t smem_src, int c0, int c1, int c2, int c3, int c4) {
+  asm volatile("cp.async.bulk.tensor.5d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5, %6}], [%1];"
+               ::"l"(reinterpret_cast<uint64_t>(tmap)), "r"(smem_src), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit_group() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_group_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_group0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+// named barrier over `nthreads` threads (a multiple of 32) of the CTA
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+__device__ __forceinline__ uint4 ld_shared_v4u(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr) : "memory");
+  return v;
 }
 
 // ---------------------------------------------------------------- tcgen05 / TMEM
