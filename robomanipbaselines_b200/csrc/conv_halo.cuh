@@ -224,18 +224,29 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       mbar_wait(&tmem_empty_bar[acc], acc_phase ^ 1);
       tc_fence_after();
       const uint32_t d_tmem = tmem_base + acc * BLOCK_N;
-      for (int l = 0; l < hp.n_loads; ++l) {
+      // The tap structure is compile-time (BLOCK_K 64: 3x3 conv, box l = filter column, taps = filter rows;
+      // BLOCK_K 32: stem, box 0 = odd input rows with kh = 0,2,4,6, box 1 = even rows with kh = 1,3,5), so each
+      // tcgen05.mma costs the single issuing thread only its descriptor adds. A tap's A operand starts
+      // kh * (box_w rows) into the box; its weights are slice `w` of the resident array.
+      constexpr int kLoads = (BLOCK_K == 64) ? 3 : 2;
+      const uint32_t rb16 = static_cast<uint32_t>(p.box_w * BLOCK_K * 2) >> 4;   // one box row of pixels, in 16-byte units
+#pragma unroll
+      for (int l = 0; l < kLoads; ++l) {
         mbar_wait(&full_bar[stage], phase);
         tc_fence_after();
         if (elect_one()) {
           const uint64_t da0 = a_desc0 + static_cast<uint64_t>((stage * hp.stage_bytes) >> 4);
-          const int t0 = hp.ld_tap0[l], t1 = t0 + hp.ld_ntaps[l];
-          for (int t = t0; t < t1; ++t) {
-            const uint64_t da = da0 + static_cast<uint64_t>(hp.tap_aoff[t] >> 4);
-            const uint64_t db = w_desc0 + static_cast<uint64_t>(hp.tap_w[t] * (S::kWTapBytes >> 4));
+          const int kTaps = (BLOCK_K == 64) ? 3 : (4 - l);
 #pragma unroll
-            for (int k = 0; k < BLOCK_K / 16; ++k)
-              umma_f16_ss(d_tmem, da + 2 * k, db + 2 * k, kIdesc, (l | (t - t0) | k) != 0 ? 1u : 0u);
+          for (int i = 0; i < 4; ++i) {
+            if (i < kTaps) {
+              const int wslice = (BLOCK_K == 64) ? (i * 3 + l) : (2 * i + l);
+              const uint64_t da = da0 + static_cast<uint64_t>(i * rb16);
+              const uint64_t db = w_desc0 + static_cast<uint64_t>(wslice * (S::kWTapBytes >> 4));
+#pragma unroll
+              for (int k = 0; k < BLOCK_K / 16; ++k)
+                umma_f16_ss(d_tmem, da + 2 * k, db + 2 * k, kIdesc, (l | i | k) != 0 ? 1u : 0u);
+            }
           }
           umma_commit_u32(empty_base + stage * 8);
         }
