@@ -138,6 +138,92 @@ int rmb_attention(const void* d_Q, int ldq, int q_col0, int q_shared, const void
 int rmb_layernorm512(const float* d_x, const float* d_gamma, const float* d_beta, const float* d_pos, int L,
                      float* d_y_f32, void* d_y_act, void* d_ypos_act, int64_t rows, int do_norm, void* stream);
 
+/* =====================================================================================================================
+ * Diffusion Policy / DP3 denoising path.
+ * The arithmetic of this path lives in sources that are NOT part of the reference mount (un-vendored submodules
+ * third_party/diffusion_policy @ 7e8fea7, third_party/3D-Diffusion-Policy @ 95ad86a, and diffusers == 0.11.1); the
+ * entry points below replace what the reference calls at
+ *   policy/diffusion_policy/RolloutDiffusionPolicy.py:37-43,74      DDPMScheduler + policy.predict_action
+ *   policy/diffusion_policy_3d/RolloutDiffusionPolicy3d.py:50-56,90 DDIMScheduler + DP3.predict_action
+ * with the hyper-parameters of TrainDiffusionPolicy.py:114-138 / TrainDiffusionPolicy3d.py:185-218. */
+typedef struct rmb_unet_engine rmb_unet_engine_t;
+
+/* ConditionalUnet1D(input_dim, global_cond_dim, diffusion_step_embed_dim, down_dims, kernel_size, n_groups,
+ * cond_predict_scale=True) as built from model_meta_info["policy"]["args"]. */
+typedef struct rmb_unet_config {
+  int32_t max_batch;           /* trajectories per call (workspace is sized for this) */
+  int32_t horizon;             /* T (16): power of two, divisible by 2^(n_levels-1) */
+  int32_t input_dim;           /* action_dim; kernel_size * input_dim <= 64 */
+  int32_t global_cond_dim;     /* obs feature dim * n_obs_steps */
+  int32_t dsed;                /* diffusion_step_embed_dim (128) */
+  int32_t n_levels;            /* len(down_dims), 2..4 */
+  int32_t down_dims[4];        /* multiples of 64 */
+  int32_t kernel_size;         /* 5 (odd) */
+  int32_t n_groups;            /* 8 (only value supported) */
+  int32_t num_train_timesteps; /* 100: size of the per-timestep FiLM table */
+  int32_t device;
+} rmb_unet_config_t;
+
+/* One scheduler step, made on the host with the scheduler's own fp32 arithmetic (diffusers 0.11.1):
+ *   x0 = pred_sample ? out : (x - s_beta*out) / s_alpha;  if clip: x0 = clamp(x0, -1, 1)
+ *   kind 0 (DDPMScheduler.step, fixed_small): x' = c_x0*x0 + c_xt*x (+ sigma*noise when sigma > 0)
+ *   kind 1 (DDIMScheduler.step, eta 0):       x' = c_x0*x0 + c_xt*(derive_eps ? (x - s_alpha*x0)/s_beta : out) */
+typedef struct rmb_sched_step {
+  int32_t t;            /* timestep fed to the UNet (0 <= t < num_train_timesteps) */
+  int32_t kind;         /* 0 DDPM, 1 DDIM */
+  int32_t pred_sample;  /* prediction_type: 0 "epsilon", 1 "sample" */
+  int32_t clip;         /* clip_sample */
+  int32_t derive_eps;
+  float s_beta;         /* sqrt(1 - alphas_cumprod[t]) */
+  float s_alpha;        /* sqrt(alphas_cumprod[t]) */
+  float c_x0;           /* DDPM pred_original_sample_coeff | DDIM sqrt(alpha_prod_t_prev) */
+  float c_xt;           /* DDPM current_sample_coeff       | DDIM sqrt(1 - alpha_prod_t_prev) */
+  float sigma;          /* DDPM sqrt(variance) (0 at t = 0) */
+} rmb_sched_step_t;
+
+int rmb_unet_engine_create(const rmb_unet_config_t* cfg, rmb_unet_engine_t** out);
+void rmb_unet_engine_destroy(rmb_unet_engine_t* e);
+/* ConditionalUnet1D state-dict tensor (key relative to the module, e.g. "down_modules.0.0.blocks.0.block.0.weight"),
+ * fp32 host memory. */
+int rmb_unet_load_tensor(rmb_unet_engine_t* e, const char* name, const float* host_data, int64_t numel);
+int rmb_unet_finalize(rmb_unet_engine_t* e);
+/* The whole conditional_sample loop (DiffusionUnetHybridImagePolicy / DP3 .conditional_sample, obs_as_global_cond):
+ * d_global_cond float32 [batch, global_cond_dim]; d_x_init float32 [batch, T, input_dim] (the torch.randn trajectory);
+ * d_noise float32 [n_steps, batch, T, input_dim] (DDPM variance noise of loop iteration i; may be NULL when every
+ * sigma is 0); steps: HOST array of n_steps entries; d_x_out float32 [batch, T, input_dim] (may alias d_x_init).
+ * n_steps * launches_per_step + 3 kernels are enqueued on `stream`; no synchronisation. */
+int rmb_unet1d_denoise(rmb_unet_engine_t* e, const float* d_global_cond, const float* d_x_init, const float* d_noise,
+                       const rmb_sched_step_t* steps, int n_steps, float* d_x_out, int batch, void* stream);
+/* One ConditionalUnet1D.forward(sample, timestep, global_cond): d_sample / d_out float32 [batch, T, input_dim]. */
+int rmb_unet1d_forward(rmb_unet_engine_t* e, const float* d_sample, int timestep, const float* d_global_cond,
+                       float* d_out, int batch, void* stream);
+/* Kernel launches per UNet evaluation, and algorithmic FLOPs of one evaluation for `batch` trajectories. */
+int rmb_unet_launches_per_step(const rmb_unet_engine_t* e);
+double rmb_unet_step_flops(const rmb_unet_engine_t* e, int batch);
+/* rmb_unet1d_forward with CUDA events around every launch (see rmb_act_forward_profile). */
+int rmb_unet1d_forward_profile(rmb_unet_engine_t* e, const float* d_sample, int timestep, const float* d_global_cond,
+                               float* d_out, int batch, void* stream, rmb_launch_prof_t* out, int cap);
+
+/* ---- DP3Encoder (PointNetEncoderXYZ with LayerNorm + state MLP): obs -> per-obs-step feature */
+typedef struct rmb_pointnet_engine rmb_pointnet_engine_t;
+typedef struct rmb_pointnet_config {
+  int32_t max_clouds;    /* batch * n_obs_steps */
+  int32_t num_points;    /* 1024 */
+  int32_t in_channels;   /* 3 (xyz) or 6 (use_pc_color) */
+  int32_t out_channels;  /* encoder_output_dim (64), <= 64 */
+  int32_t state_dim;     /* 0 = no state MLP */
+  int32_t device;
+} rmb_pointnet_config_t;
+int rmb_pointnet_engine_create(const rmb_pointnet_config_t* cfg, rmb_pointnet_engine_t** out);
+void rmb_pointnet_engine_destroy(rmb_pointnet_engine_t* e);
+/* DP3Encoder state-dict tensor ("extractor.mlp.0.weight", "extractor.final_projection.0.weight", "state_mlp.0.weight", ...). */
+int rmb_pointnet_load_tensor(rmb_pointnet_engine_t* e, const char* name, const float* host_data, int64_t numel);
+int rmb_pointnet_finalize(rmb_pointnet_engine_t* e);
+/* d_points float32 [n_clouds, num_points, point_stride] (first in_channels of each point are used);
+ * d_state float32 [n_clouds, state_dim] or NULL; d_out float32 [n_clouds, out_channels (+ 64 with state)]. */
+int rmb_pointnet_encode(rmb_pointnet_engine_t* e, const float* d_points, int point_stride, const float* d_state,
+                        float* d_out, int n_clouds, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

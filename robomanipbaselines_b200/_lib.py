@@ -33,6 +33,34 @@ class LaunchProf(ctypes.Structure):
                 ("bytes", c_double)]
 
 
+class UnetConfig(ctypes.Structure):
+    """Mirror of rmb_unet_config_t."""
+
+    _fields_ = [
+        ("max_batch", c_int32), ("horizon", c_int32), ("input_dim", c_int32), ("global_cond_dim", c_int32),
+        ("dsed", c_int32), ("n_levels", c_int32), ("down_dims", c_int32 * 4), ("kernel_size", c_int32),
+        ("n_groups", c_int32), ("num_train_timesteps", c_int32), ("device", c_int32),
+    ]
+
+
+class SchedStep(ctypes.Structure):
+    """Mirror of rmb_sched_step_t."""
+
+    _fields_ = [
+        ("t", c_int32), ("kind", c_int32), ("pred_sample", c_int32), ("clip", c_int32), ("derive_eps", c_int32),
+        ("s_beta", c_float), ("s_alpha", c_float), ("c_x0", c_float), ("c_xt", c_float), ("sigma", c_float),
+    ]
+
+
+class PointNetConfig(ctypes.Structure):
+    """Mirror of rmb_pointnet_config_t."""
+
+    _fields_ = [
+        ("max_clouds", c_int32), ("num_points", c_int32), ("in_channels", c_int32), ("out_channels", c_int32),
+        ("state_dim", c_int32), ("device", c_int32),
+    ]
+
+
 # name -> (restype, argtypes); must list every symbol include/rmb_b200.h declares (tests check this)
 SIGNATURES = {
     "rmb_last_error": (c_char_p, []),
@@ -66,6 +94,22 @@ SIGNATURES = {
                                    c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p]),
     "rmb_layernorm512": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p,
                                  c_int64, c_int, c_void_p]),
+    "rmb_unet_engine_create": (c_int, [POINTER(UnetConfig), POINTER(c_void_p)]),
+    "rmb_unet_engine_destroy": (None, [c_void_p]),
+    "rmb_unet_load_tensor": (c_int, [c_void_p, c_char_p, c_void_p, c_int64]),
+    "rmb_unet_finalize": (c_int, [c_void_p]),
+    "rmb_unet1d_denoise": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, POINTER(SchedStep), c_int, c_void_p, c_int,
+                                   c_void_p]),
+    "rmb_unet1d_forward": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int, c_void_p]),
+    "rmb_unet_launches_per_step": (c_int, [c_void_p]),
+    "rmb_unet_step_flops": (c_double, [c_void_p, c_int]),
+    "rmb_unet1d_forward_profile": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int, c_void_p,
+                                           POINTER(LaunchProf), c_int]),
+    "rmb_pointnet_engine_create": (c_int, [POINTER(PointNetConfig), POINTER(c_void_p)]),
+    "rmb_pointnet_engine_destroy": (None, [c_void_p]),
+    "rmb_pointnet_load_tensor": (c_int, [c_void_p, c_char_p, c_void_p, c_int64]),
+    "rmb_pointnet_finalize": (c_int, [c_void_p]),
+    "rmb_pointnet_encode": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int, c_void_p]),
 }
 
 _lib = None

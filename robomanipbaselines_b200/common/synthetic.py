@@ -38,6 +38,12 @@ def synthetic_tensor(key, shape, seed=0):
         return torch.randn(shape, generator=g) * 0.1
     if ".norm" in key and key.endswith(".weight"):
         return 1.0 + 0.1 * torch.randn(shape, generator=g)
+    is_diffusion = key.split(".")[0] in ("model", "obs_encoder") and (".block." in key or "_modules." in key or "extractor." in key or "final_conv" in key) \
+        or key.split(".")[0] in ("down_modules", "up_modules", "mid_modules", "final_conv", "extractor")
+    if is_diffusion and len(shape) == 3:     # Conv1d / ConvTranspose1d of ConditionalUnet1D
+        return torch.randn(shape, generator=g) * (1.0 / (shape[1] * shape[2])) ** 0.5
+    if is_diffusion and len(shape) == 1 and key.endswith(".weight"):   # GroupNorm / LayerNorm gains of the diffusion policies
+        return 1.0 + 0.1 * torch.randn(shape, generator=g)
     if len(shape) == 4:
         fan_in = shape[1] * shape[2] * shape[3]
         return torch.randn(shape, generator=g) * (2.0 / fan_in) ** 0.5

@@ -96,3 +96,148 @@ class ActEngine:
             self.close()
         except Exception:
             pass
+
+
+def _load_tensors(lib, handle, fn, state_dict, what):
+    for name, t in state_dict.items():
+        a = np.ascontiguousarray(t.detach().to("cpu", torch.float32).numpy())
+        check(fn(handle, name.encode(), a.ctypes.data_as(ctypes.c_void_p), a.size), f"{what}({name})")
+
+
+class UnetEngine:
+    """Handle around rmb_unet_engine_t: ConditionalUnet1D + the scheduler loop (include/rmb_b200.h)."""
+
+    def __init__(self, *, max_batch, horizon, input_dim, global_cond_dim, diffusion_step_embed_dim=128,
+                 down_dims=(512, 1024, 2048), kernel_size=5, n_groups=8, num_train_timesteps=100, device=0):
+        if not torch.cuda.is_available():
+            raise _lib.RmbError("UnetEngine needs a CUDA device (sm_100a); there is no CPU fallback")
+        self.lib = _lib.load()
+        dd = (ctypes.c_int32 * 4)(*(list(down_dims) + [0] * (4 - len(down_dims))))
+        self.cfg = _lib.UnetConfig(max_batch, horizon, input_dim, global_cond_dim, diffusion_step_embed_dim,
+                                   len(down_dims), dd, kernel_size, n_groups, num_train_timesteps, device)
+        self.device = torch.device("cuda", device)
+        self._h = ctypes.c_void_p()
+        check(self.lib.rmb_unet_engine_create(ctypes.byref(self.cfg), ctypes.byref(self._h)), "rmb_unet_engine_create")
+
+    def load_state_dict(self, state_dict):
+        """state_dict of the ConditionalUnet1D module (keys relative to it)."""
+        _load_tensors(self.lib, self._h, self.lib.rmb_unet_load_tensor, state_dict, "rmb_unet_load_tensor")
+        check(self.lib.rmb_unet_finalize(self._h), "rmb_unet_finalize")
+
+    @property
+    def max_batch(self):
+        return self.cfg.max_batch
+
+    @property
+    def launches_per_step(self):
+        return self.lib.rmb_unet_launches_per_step(self._h)
+
+    def step_flops(self, batch):
+        return self.lib.rmb_unet_step_flops(self._h, batch)
+
+    def _check(self, x, global_cond):
+        B = x.shape[0]
+        c = self.cfg
+        if tuple(x.shape) != (B, c.horizon, c.input_dim) or x.dtype != torch.float32:
+            raise ValueError(f"trajectory must be float32 (B, {c.horizon}, {c.input_dim})")
+        if tuple(global_cond.shape) != (B, c.global_cond_dim) or global_cond.dtype != torch.float32:
+            raise ValueError(f"global_cond must be float32 (B, {c.global_cond_dim})")
+        if not (x.is_cuda and global_cond.is_cuda and x.is_contiguous() and global_cond.is_contiguous()):
+            raise ValueError("inputs must be contiguous CUDA tensors")
+        return B
+
+    def forward(self, sample, timestep, global_cond, out=None):
+        """ConditionalUnet1D.forward(sample (B,T,Da), timestep int, global_cond (B,G)) -> (B,T,Da)."""
+        B = self._check(sample, global_cond)
+        if out is None:
+            out = torch.empty_like(sample)
+        check(self.lib.rmb_unet1d_forward(self._h, ptr(sample), int(timestep), ptr(global_cond), ptr(out), B,
+                                          cur_stream()), "rmb_unet1d_forward")
+        return out
+
+    def forward_profile(self, sample, timestep, global_cond):
+        B = self._check(sample, global_cond)
+        out = torch.empty_like(sample)
+        cap = 256
+        recs = (_lib.LaunchProf * cap)()
+        n = check(self.lib.rmb_unet1d_forward_profile(self._h, ptr(sample), int(timestep), ptr(global_cond), ptr(out),
+                                                      B, cur_stream(), recs, cap), "rmb_unet1d_forward_profile")
+        return out, [dict(name=recs[i].name.decode(), kernel=recs[i].kernel.decode(), ms=recs[i].ms,
+                          flops=recs[i].flops, bytes=recs[i].bytes) for i in range(n)]
+
+    def denoise(self, global_cond, x_init, steps, noise=None, out=None):
+        """The conditional_sample loop. steps: ctypes array of _lib.SchedStep (see common/schedulers.py);
+        noise float32 (n_steps, B, T, Da) or None."""
+        B = self._check(x_init, global_cond)
+        n = len(steps)
+        if noise is not None and (tuple(noise.shape) != (n,) + tuple(x_init.shape) or noise.dtype != torch.float32
+                                  or not noise.is_cuda or not noise.is_contiguous()):
+            raise ValueError("noise must be a contiguous float32 CUDA tensor (n_steps, B, T, Da)")
+        if out is None:
+            out = torch.empty_like(x_init)
+        check(self.lib.rmb_unet1d_denoise(self._h, ptr(global_cond), ptr(x_init), ptr(noise), steps, n, ptr(out), B,
+                                          cur_stream()), "rmb_unet1d_denoise")
+        return out
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h.value:
+            self.lib.rmb_unet_engine_destroy(self._h)
+            self._h = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class PointNetEngine:
+    """Handle around rmb_pointnet_engine_t: DP3Encoder (PointNetEncoderXYZ + state MLP)."""
+
+    def __init__(self, *, max_clouds, num_points, in_channels=3, out_channels=64, state_dim=0, device=0):
+        if not torch.cuda.is_available():
+            raise _lib.RmbError("PointNetEngine needs a CUDA device (sm_100a); there is no CPU fallback")
+        self.lib = _lib.load()
+        self.cfg = _lib.PointNetConfig(max_clouds, num_points, in_channels, out_channels, state_dim, device)
+        self.device = torch.device("cuda", device)
+        self._h = ctypes.c_void_p()
+        check(self.lib.rmb_pointnet_engine_create(ctypes.byref(self.cfg), ctypes.byref(self._h)),
+              "rmb_pointnet_engine_create")
+
+    def load_state_dict(self, state_dict):
+        _load_tensors(self.lib, self._h, self.lib.rmb_pointnet_load_tensor, state_dict, "rmb_pointnet_load_tensor")
+        check(self.lib.rmb_pointnet_finalize(self._h), "rmb_pointnet_finalize")
+
+    @property
+    def max_clouds(self):
+        return self.cfg.max_clouds
+
+    @property
+    def out_dim(self):
+        return self.cfg.out_channels + (64 if self.cfg.state_dim > 0 else 0)
+
+    def encode(self, points, state=None, out=None):
+        """points float32 (n, Np, >= in_channels), state float32 (n, Ds) -> (n, out_channels [+ 64])."""
+        n, c = points.shape[0], self.cfg
+        if points.dtype != torch.float32 or points.dim() != 3 or points.shape[1] != c.num_points or not points.is_cuda \
+                or not points.is_contiguous():
+            raise ValueError(f"points must be a contiguous float32 CUDA tensor (n, {c.num_points}, >= {c.in_channels})")
+        if c.state_dim > 0 and (state is None or tuple(state.shape) != (n, c.state_dim) or state.dtype != torch.float32
+                                or not state.is_contiguous()):
+            raise ValueError(f"state must be contiguous float32 (n, {c.state_dim})")
+        if out is None:
+            out = torch.empty(n, self.out_dim, device=self.device, dtype=torch.float32)
+        check(self.lib.rmb_pointnet_encode(self._h, ptr(points), points.shape[2], ptr(state), ptr(out), n,
+                                           cur_stream()), "rmb_pointnet_encode")
+        return out
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h.value:
+            self.lib.rmb_pointnet_engine_destroy(self._h)
+            self._h = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -1,0 +1,141 @@
+"""GPU parity of the Diffusion Policy / DP3 path against oracle/diffusion_oracle.py (PARITY UNPINNED: the oracle restates
+sources that are not in the reference mount). Tolerance: max-abs <= 1e-2 in normalised action space (north_star), on the
+final trajectory of the whole scheduler loop with shared initial noise and shared per-step noise."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import diffusion_oracle as dor
+from robomanipbaselines_b200.common.schedulers import DDIMScheduler, DDPMScheduler
+from robomanipbaselines_b200.common.synthetic import synthetic_state_dict
+
+pytestmark = pytest.mark.gpu
+
+SCHED = dict(beta_end=0.02, beta_schedule="squaredcos_cap_v2", beta_start=0.0001, clip_sample=True,
+             num_train_timesteps=100)
+UNET_CASES = {
+    "small": dict(B=3, T=8, Da=4, G=24, dsed=64, down_dims=(128, 256), k=3),
+    "mid3": dict(B=5, T=16, Da=7, G=142, dsed=128, down_dims=(64, 128, 256), k=5),
+    "full_dp": dict(B=2, T=16, Da=7, G=142, dsed=128, down_dims=(512, 1024, 2048), k=5),
+    "full_dp3": dict(B=9, T=16, Da=7, G=256, dsed=128, down_dims=(512, 1024, 2048), k=5),
+}
+
+
+def _unet_pair(case, cuda, seed=0):
+    from robomanipbaselines_b200.engine import UnetEngine
+
+    c = UNET_CASES[case]
+    ref = dor.ConditionalUnet1D(c["Da"], c["G"], c["dsed"], c["down_dims"], c["k"]).eval()
+    sd = synthetic_state_dict({k: tuple(v.shape) for k, v in ref.state_dict().items()}, seed=seed)
+    ref.load_state_dict(sd)
+    eng = UnetEngine(max_batch=c["B"], horizon=c["T"], input_dim=c["Da"], global_cond_dim=c["G"],
+                     diffusion_step_embed_dim=c["dsed"], down_dims=c["down_dims"], kernel_size=c["k"],
+                     device=cuda.index or 0)
+    eng.load_state_dict(sd)
+    g = torch.Generator().manual_seed(2)
+    x = torch.randn(c["B"], c["T"], c["Da"], generator=g)
+    gc = torch.randn(c["B"], c["G"], generator=g)
+    return c, ref, eng, x, gc, g
+
+
+@pytest.mark.parametrize("case", list(UNET_CASES))
+def test_unet_forward(cuda, case):
+    c, ref, eng, x, gc, _ = _unet_pair(case, cuda)
+    for t in (0, 37, 99):
+        with torch.no_grad():
+            want = ref(x, t, gc)
+        got = eng.forward(x.to(cuda), t, gc.to(cuda)).cpu()
+        err = (got - want).abs().max().item()
+        print(f"[unet {case} t={t}] max-abs err {err:.3e} (ref max {want.abs().max().item():.3e})")
+        assert torch.isfinite(got).all() and err <= 1e-2
+    assert eng.launches_per_step > 0 and eng.step_flops(1) > 0
+
+
+@pytest.mark.parametrize("case,kind,n_steps", [("small", "ddpm", 100), ("mid3", "ddim", 10), ("full_dp", "ddpm", 100),
+                                               ("full_dp3", "ddim", 10), ("full_dp3", "ddim", 16)])
+def test_denoise_loop(cuda, case, kind, n_steps):
+    c, ref, eng, x, gc, g = _unet_pair(case, cuda)
+    if kind == "ddpm":
+        mine, orc = DDPMScheduler(**SCHED, prediction_type="epsilon", variance_type="fixed_small"), \
+            dor.DDPMSchedulerOracle(**SCHED, prediction_type="epsilon")
+        noise = torch.randn(n_steps, *x.shape, generator=g)
+    else:
+        mine, orc = DDIMScheduler(**SCHED, prediction_type="sample", set_alpha_to_one=True, steps_offset=0), \
+            dor.DDIMSchedulerOracle(**SCHED, prediction_type="sample")
+        noise = None
+    steps = mine.step_table(n_steps)
+    orc.set_timesteps(n_steps)
+    assert [s.t for s in steps] == [int(t) for t in orc.timesteps]          # timestep indices bit-exact
+    want = dor.conditional_sample(ref, orc, gc, x, noise, n_steps)
+    got = eng.denoise(gc.to(cuda), x.to(cuda), steps, noise=None if noise is None else noise.to(cuda)).cpu()
+    err = (got - want).abs().max().item()
+    print(f"[denoise {case} {kind}-{n_steps}] max-abs err {err:.3e} (ref max {want.abs().max().item():.3e})")
+    assert torch.isfinite(got).all() and err <= 1e-2
+
+
+def test_scheduler_step_alone_is_bit_exact(cuda):
+    """With a UNet whose output is forced to zero weights... instead: compare the host step tables with the oracle's
+    scalars (the device applies them with the same op order, no FMA)."""
+    mine, orc = DDPMScheduler(**SCHED), dor.DDPMSchedulerOracle(**SCHED)
+    for s in mine.step_table(100):
+        t = s.t
+        a, ap = orc.alphas_cumprod[t], (orc.alphas_cumprod[t - 1] if t > 0 else orc.one)
+        assert s.s_alpha == float(a ** 0.5) and s.s_beta == float((1 - a) ** 0.5)
+        assert s.c_x0 == float((ap ** 0.5 * orc.betas[t]) / (1 - a))
+
+
+@pytest.mark.parametrize("n,Np,cin,Ds", [(3, 1024, 3, 7), (4, 512, 6, 5), (2, 100, 3, 0)])
+def test_pointnet_encode(cuda, n, Np, cin, Ds):
+    from robomanipbaselines_b200.engine import PointNetEngine
+
+    ref = dor.DP3Encoder(max(Ds, 1), 64, use_pc_color=(cin == 6)).eval()
+    sd = synthetic_state_dict({k: tuple(v.shape) for k, v in ref.state_dict().items()}, seed=3)
+    ref.load_state_dict(sd)
+    if Ds == 0:
+        sd = {k: v for k, v in sd.items() if not k.startswith("state_mlp")}
+    eng = PointNetEngine(max_clouds=n, num_points=Np, in_channels=cin, out_channels=64, state_dim=Ds)
+    eng.load_state_dict(sd)
+    g = torch.Generator().manual_seed(5)
+    pts = torch.rand(n, Np, 6, generator=g) * 2 - 1
+    st = torch.randn(n, max(Ds, 1), generator=g)
+    with torch.no_grad():
+        want = ref({"point_cloud": pts, "agent_pos": st})
+    got = eng.encode(pts.to(cuda), st.to(cuda) if Ds > 0 else None).cpu()
+    if Ds == 0:
+        want = want[:, :64]
+    err = (got - want).abs().max().item()
+    print(f"[pointnet n{n} Np{Np} cin{cin} Ds{Ds}] max-abs err {err:.3e} (ref max {want.abs().max().item():.3e})")
+    assert got.shape == want.shape and err <= 1e-2
+
+
+def test_dp3_predict_action(cuda):
+    """DP3.predict_action end to end (TrainDiffusionPolicy3d.py:185-218 arguments) against the oracle modules."""
+    from robomanipbaselines_b200.policy.diffusion_policy_3d import DP3
+
+    B, To, Np, Ds, Da = 4, 2, 1024, 7, 7
+    sched_args = dict(SCHED, set_alpha_to_one=True, prediction_type="sample", steps_offset=0)
+    pol = DP3(noise_scheduler=DDIMScheduler(**sched_args),
+              shape_meta={"obs": {"state": {"shape": [Ds], "type": "low_dim"},
+                                  "point_cloud": {"shape": (Np, 6), "type": "point_cloud"}}, "action": {"shape": [Da]}},
+              horizon=16, n_action_steps=8, n_obs_steps=To, num_inference_steps=10, obs_as_global_cond=True,
+              diffusion_step_embed_dim=128, down_dims=[512, 1024, 2048], kernel_size=5, n_groups=8,
+              pointcloud_encoder_cfg={"in_channels": 6, "out_channels": 64, "use_layernorm": True,
+                                      "final_norm": "layernorm", "normal_channel": False},
+              use_pc_color=False, encoder_output_dim=64)
+    sd = synthetic_state_dict({k: tuple(v.shape) for k, v in pol.state_dict().items()}, seed=4)
+    pol.load_state_dict(sd, strict=True)
+    enc, unet = dor.DP3Encoder(Ds, 64).eval(), dor.ConditionalUnet1D(Da, To * 128).eval()
+    enc.load_state_dict({k[len("obs_encoder."):]: v for k, v in sd.items() if k.startswith("obs_encoder.")})
+    unet.load_state_dict({k[len("model."):]: v for k, v in sd.items() if k.startswith("model.")})
+    g = torch.Generator().manual_seed(6)
+    pc = torch.rand(B, To, Np, 6, generator=g) * 2 - 1
+    st = torch.randn(B, To, Ds, generator=g)
+    x0 = torch.randn(B, 16, Da, generator=g)
+    with torch.no_grad():
+        feat = enc({"point_cloud": pc.reshape(B * To, Np, 6), "agent_pos": st.reshape(B * To, Ds)}).reshape(B, -1)
+    orc = dor.DDIMSchedulerOracle(**sched_args)
+    want = dor.conditional_sample(unet, orc, feat, x0, None, 10)[:, To - 1:To - 1 + 8]
+    got = pol.predict_action({"state": st.to(cuda), "point_cloud": pc.to(cuda)}, x_init=x0.to(cuda))["action"].cpu()
+    err = (got - want).abs().max().item()
+    print(f"[dp3 predict_action] max-abs err {err:.3e} (ref max {want.abs().max().item():.3e})")
+    assert got.shape == (B, 8, Da) and err <= 1e-2
