@@ -106,3 +106,44 @@ def get_images(rgb_images):
     images = np.moveaxis(images, -1, -3)
     # v2.ToDtype(float32, scale=True) multiplies by 1/255 in float32 (RolloutBase.py:353,488)
     return (images.astype(np.float32) * np.float32(1.0 / 255.0))[np.newaxis]
+
+
+class DiffusionRolloutOracle:
+    """One episode of RolloutDiffusionPolicy(3d).infer_policy with the policy call factored out
+    (policy/diffusion_policy/RolloutDiffusionPolicy.py:60-108, policy/diffusion_policy_3d/RolloutDiffusionPolicy3d.py:73-123).
+
+    Observation ring buffers are pushed ONLY when the policy is called (get_state / get_images / get_pointcloud sit
+    inside the `if len(policy_action_buf) == 0` branch): the first call fills all n_obs_steps slots with the same
+    observation, later calls pop the oldest and append. The action FIFO holds the n_action_steps actions of one
+    inference as float64 and pops one per policy step; each popped action is denormalised.
+    """
+
+    def __init__(self, n_obs_steps, state_stats, action_stats):
+        self.n_obs_steps = n_obs_steps
+        self.state_stats, self.action_stats = state_stats, action_stats
+        self.reset()
+
+    def reset(self):
+        self.obs_buf = None              # dict name -> list of n_obs_steps arrays
+        self.policy_action_buf = None
+
+    def needs_inference(self):
+        return self.policy_action_buf is None or len(self.policy_action_buf) == 0
+
+    def push_obs(self, raw_state, **others):
+        """-> dict of stacked (n_obs_steps, ...) arrays, state normalised and cast to float32 (get_state :87-108)."""
+        new = {"state": normalize_data(np.asarray(raw_state, np.float64), self.state_stats).astype(np.float32)}
+        new.update({k: np.asarray(v) for k, v in others.items()})
+        if self.obs_buf is None:
+            self.obs_buf = {k: [v for _ in range(self.n_obs_steps)] for k, v in new.items()}
+        else:
+            for k, v in new.items():
+                self.obs_buf[k].pop(0)
+                self.obs_buf[k].append(v)
+        return {k: np.stack(v, axis=0) for k, v in self.obs_buf.items()}
+
+    def step(self, actions=None):
+        """actions: (n_action_steps, Da) float32 from predict_action when needs_inference() was True."""
+        if self.needs_inference():
+            self.policy_action_buf = list(np.asarray(actions).astype(np.float64))
+        return denormalize_data(self.policy_action_buf.pop(0), self.action_stats)

@@ -139,3 +139,48 @@ def test_dp3_predict_action(cuda):
     err = (got - want).abs().max().item()
     print(f"[dp3 predict_action] max-abs err {err:.3e} (ref max {want.abs().max().item():.3e})")
     assert got.shape == (B, 8, Da) and err <= 1e-2
+
+
+def test_batched_dp3_rollout_matches_reference_glue(cuda):
+    """BatchedDiffusionRollout vs the restated RolloutDiffusionPolicy3d.infer_policy glue: obs ring buffers and FIFO
+    positions bit-exact (with staggered per-episode resets), denormalised float64 actions bit-exact given the same
+    predicted chunk."""
+    from oracle import rollout_oracle as ror
+    from robomanipbaselines_b200.common.batched_diffusion_rollout import BatchedDiffusionRollout
+    from robomanipbaselines_b200.common.synthetic import synthetic_norm_stats
+    from robomanipbaselines_b200.policy.diffusion_policy_3d import DP3
+
+    B, To, Np, Ds, Da, Na = 3, 2, 128, 7, 7, 8
+    sched_args = dict(SCHED, set_alpha_to_one=True, prediction_type="sample", steps_offset=0)
+    pol = DP3(noise_scheduler=DDIMScheduler(**sched_args),
+              shape_meta={"obs": {"state": {"shape": [Ds]}, "point_cloud": {"shape": (Np, 6)}}, "action": {"shape": [Da]}},
+              horizon=16, n_action_steps=Na, n_obs_steps=To, num_inference_steps=4, diffusion_step_embed_dim=64,
+              down_dims=[64, 128], kernel_size=5, n_groups=8, pointcloud_encoder_cfg={"out_channels": 64},
+              encoder_output_dim=64)
+    pol.load_state_dict(synthetic_state_dict({k: tuple(v.shape) for k, v in pol.state_dict().items()}, seed=7))
+    meta = {"data": {"n_obs_steps": To, "n_action_steps": Na, "horizon": 16},
+            "state": synthetic_norm_stats(Ds, 1, "limits"), "action": synthetic_norm_stats(Da, 2)}
+    br = BatchedDiffusionRollout(pol, B, meta, device=str(cuda), obs_keys=("point_cloud",))
+    orcs = [ror.DiffusionRolloutOracle(To, meta["state"], meta["action"]) for _ in range(B)]
+    rng = np.random.default_rng(0)
+    br.reset()
+    for step in range(21):
+        if step == 5:                       # episode 1 restarts mid-FIFO
+            br.reset(torch.tensor([False, True, False]))
+            orcs[1].reset()
+        if step == 12:
+            br.reset(torch.tensor([True, False, False]))
+            orcs[0].reset()
+        raw = rng.standard_normal((B, Ds))
+        pc = rng.uniform(-1, 1, (B, Np, 6)).astype(np.float32)
+        need = [o.needs_inference() for o in orcs]
+        want_obs = [o.push_obs(raw[b], point_cloud=pc[b]) if need[b] else None for b, o in enumerate(orcs)]
+        act = br.infer(torch.from_numpy(raw).to(cuda), point_cloud=torch.from_numpy(pc).to(cuda)).cpu().numpy()
+        for b in range(B):
+            if need[b]:
+                assert np.array_equal(br.obs_buf["state"][b].cpu().numpy(), want_obs[b]["state"]), (step, b)
+                assert np.array_equal(br.obs_buf["point_cloud"][b].cpu().numpy(), want_obs[b]["point_cloud"]), (step, b)
+            chunk = br.fifo[b].cpu().numpy().astype(np.float32) if need[b] else None
+            assert np.array_equal(act[b], orcs[b].step(chunk)), (step, b)
+            assert br._host_pos[b] == Na - len(orcs[b].policy_action_buf)
+    assert br.n_inferences == 7
