@@ -224,6 +224,32 @@ int rmb_pointnet_finalize(rmb_pointnet_engine_t* e);
 int rmb_pointnet_encode(rmb_pointnet_engine_t* e, const float* d_points, int point_stride, const float* d_state,
                         float* d_out, int n_clouds, void* stream);
 
+/* ---- Diffusion Policy image observation encoder of one camera key (robomimic VisualCore as diffusion_policy builds it:
+ * CropRandomizer (centre crop at eval) -> ResNet18Conv with BatchNorm replaced by GroupNorm(C/16, C) ->
+ * SpatialSoftmax(num_kp) -> Flatten -> Linear(2*num_kp, feat)); source not in the reference mount (robomimic 0.2.0). */
+typedef struct rmb_imgenc_engine rmb_imgenc_engine_t;
+typedef struct rmb_imgenc_config {
+  int32_t max_images;      /* batch * n_obs_steps */
+  int32_t in_h, in_w;      /* image the rollout feeds: model_meta_info["data"]["image_size"] (240 x 320) */
+  int32_t crop_h, crop_w;  /* crop_shape (216 x 288) */
+  int32_t num_kp;          /* 32 */
+  int32_t feat_dim;        /* 64 */
+  int32_t device;
+} rmb_imgenc_config_t;
+int rmb_imgenc_engine_create(const rmb_imgenc_config_t* cfg, rmb_imgenc_engine_t** out);
+void rmb_imgenc_engine_destroy(rmb_imgenc_engine_t* e);
+/* keys relative to obs_encoder.obs_nets.<rgb key>: "backbone.nets.0.weight", "backbone.nets.4.0.bn1.weight",
+ * "pool.nets.weight", "nets.3.weight", ... */
+int rmb_imgenc_load_tensor(rmb_imgenc_engine_t* e, const char* name, const float* host_data, int64_t numel);
+int rmb_imgenc_finalize(rmb_imgenc_engine_t* e);
+/* d_images float32 [n_images, 3, in_h, in_w] (already scaled by the caller, RolloutDiffusionPolicy.py:117-123);
+ * feature j of image i is written to d_out[i * ld_out + j], j < feat_dim. */
+int rmb_imgenc_encode(rmb_imgenc_engine_t* e, const float* d_images, float* d_out, int64_t ld_out, int n_images,
+                      void* stream);
+/* debug tap: layer4 output after the last GroupNorm + ReLU as float32 [n_images, Hf, Wf, 512]; returns floats written */
+int64_t rmb_imgenc_debug_read(rmb_imgenc_engine_t* e, float* d_out, int n_images, void* stream);
+double rmb_imgenc_flops(const rmb_imgenc_engine_t* e, int n_images);
+
 #ifdef __cplusplus
 }
 #endif

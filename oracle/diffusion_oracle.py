@@ -314,3 +314,64 @@ class DP3Encoder(nn.Module):
         pn_feat = self.extractor(points)
         state_feat = self.state_mlp(observations["agent_pos"])
         return torch.cat([pn_feat, state_feat], dim=-1)
+
+
+# ------------------------------------------------------------------------------------------------ DP image encoder
+class SpatialSoftmax(nn.Module):
+    """robomimic 0.2.0 `SpatialSoftmax` (num_kp keypoints, temperature 1, no noise): 1x1 conv to num_kp maps, softmax
+    over H*W, expected (x, y) with x, y in linspace(-1, 1)."""
+
+    def __init__(self, in_c, in_h, in_w, num_kp=32):
+        super().__init__()
+        self.nets = nn.Conv2d(in_c, num_kp, kernel_size=1)
+        pos_x, pos_y = np.meshgrid(np.linspace(-1.0, 1.0, in_w), np.linspace(-1.0, 1.0, in_h))
+        self.register_buffer("pos_x", torch.from_numpy(pos_x.reshape(1, in_h * in_w)).float(), persistent=False)
+        self.register_buffer("pos_y", torch.from_numpy(pos_y.reshape(1, in_h * in_w)).float(), persistent=False)
+        self.num_kp, self.in_h, self.in_w = num_kp, in_h, in_w
+
+    def forward(self, feature):
+        feature = self.nets(feature).reshape(-1, self.in_h * self.in_w)
+        attention = F.softmax(feature, dim=-1)
+        expected_x = torch.sum(self.pos_x * attention, dim=1, keepdim=True)
+        expected_y = torch.sum(self.pos_y * attention, dim=1, keepdim=True)
+        return torch.cat([expected_x, expected_y], 1).view(-1, self.num_kp, 2)
+
+
+class _ResNet18Conv(nn.Module):
+    def __init__(self):
+        super().__init__()
+        import torchvision
+
+        net = torchvision.models.resnet18(weights=None)
+        self.nets = nn.Sequential(*(list(net.children())[:-2]))
+
+    def forward(self, x):
+        return self.nets(x)
+
+
+def _bn_to_gn(module):
+    """diffusion_policy `replace_submodules(BatchNorm2d -> GroupNorm(num_features // 16, num_features))`."""
+    for name, child in list(module.named_children()):
+        if isinstance(child, nn.BatchNorm2d):
+            setattr(module, name, nn.GroupNorm(child.num_features // 16, child.num_features))
+        else:
+            _bn_to_gn(child)
+    return module
+
+
+class DpImageEncoder(nn.Module):
+    """robomimic VisualCore for one rgb key as DiffusionUnetHybridImagePolicy builds it: centre crop (CropRandomizer in
+    eval mode) -> ResNet18Conv with GroupNorm -> SpatialSoftmax(32) -> Flatten -> Linear(64, 64)."""
+
+    def __init__(self, crop_h, crop_w, num_kp=32, feat_dim=64):
+        super().__init__()
+        self.crop_h, self.crop_w = crop_h, crop_w
+        self.backbone = _bn_to_gn(_ResNet18Conv())
+        fh, fw = int(math.ceil(crop_h / 32.0)), int(math.ceil(crop_w / 32.0))
+        self.pool = SpatialSoftmax(512, fh, fw, num_kp)
+        self.nets = nn.Sequential(self.backbone, self.pool, nn.Flatten(start_dim=1), nn.Linear(num_kp * 2, feat_dim))
+
+    def forward(self, x):
+        h, w = x.shape[-2:]
+        t, l = (h - self.crop_h) // 2, (w - self.crop_w) // 2
+        return self.nets(x[..., t:t + self.crop_h, l:l + self.crop_w])

@@ -61,6 +61,15 @@ class PointNetConfig(ctypes.Structure):
     ]
 
 
+class ImgEncConfig(ctypes.Structure):
+    """Mirror of rmb_imgenc_config_t."""
+
+    _fields_ = [
+        ("max_images", c_int32), ("in_h", c_int32), ("in_w", c_int32), ("crop_h", c_int32), ("crop_w", c_int32),
+        ("num_kp", c_int32), ("feat_dim", c_int32), ("device", c_int32),
+    ]
+
+
 # name -> (restype, argtypes); must list every symbol include/rmb_b200.h declares (tests check this)
 SIGNATURES = {
     "rmb_last_error": (c_char_p, []),
@@ -110,6 +119,13 @@ SIGNATURES = {
     "rmb_pointnet_load_tensor": (c_int, [c_void_p, c_char_p, c_void_p, c_int64]),
     "rmb_pointnet_finalize": (c_int, [c_void_p]),
     "rmb_pointnet_encode": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int, c_void_p]),
+    "rmb_imgenc_engine_create": (c_int, [POINTER(ImgEncConfig), POINTER(c_void_p)]),
+    "rmb_imgenc_engine_destroy": (None, [c_void_p]),
+    "rmb_imgenc_load_tensor": (c_int, [c_void_p, c_char_p, c_void_p, c_int64]),
+    "rmb_imgenc_finalize": (c_int, [c_void_p]),
+    "rmb_imgenc_encode": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p]),
+    "rmb_imgenc_debug_read": (c_int64, [c_void_p, c_void_p, c_int, c_void_p]),
+    "rmb_imgenc_flops": (c_double, [c_void_p, c_int]),
 }
 
 _lib = None

@@ -26,6 +26,8 @@ def synthetic_tensor(key, shape, seed=0):
     shape = tuple(int(s) for s in shape)
     g = _gen(key, seed)
     is_bn = (".bn" in key) or (".downsample.1." in key)
+    if key.endswith("nets.1.weight") and len(shape) == 1:        # GroupNorm gain after the stem of robomimic's ResNet18Conv
+        return torch.rand(shape, generator=g) + 0.5
     if key.endswith("running_var"):
         return torch.rand(shape, generator=g) + 0.5
     if key.endswith("bn2.weight"):

@@ -883,3 +883,4 @@ int rmb_layernorm512(const float* d_x, const float* d_gamma, const float* d_beta
 }  // extern "C"
 
 #include "diffusion_engine.cuh"
+#include "imgenc_engine.cuh"

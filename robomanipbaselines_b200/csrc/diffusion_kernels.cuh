@@ -406,4 +406,159 @@ __global__ void __launch_bounds__(128) pointnet_final_kernel(const float* __rest
   }
 }
 
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Diffusion Policy image encoder (robomimic ResNet18Conv with BatchNorm -> GroupNorm(C/16, C), SpatialSoftmax(32)):
+// GroupNorm over (16 channels x H x W) per image on NHWC act_t maps. A map may be allocated one row / column larger
+// than its valid extent (Hv, Wv) so that the next stride-2 conv sees even sizes; the extra row / column is kept at
+// zero (= the conv's own zero padding) by gn2d_apply and excluded from the statistics.
+//   gn2d_stats : partial[img][chunk][group] = (sum, sum of squares) over the chunk's valid pixels (deterministic)
+//   gn2d_apply : y = relu?((x - mean) * rstd * gamma + beta (+ residual)), zero outside the valid extent
+__global__ void __launch_bounds__(256) gn2d_stats_kernel(const act_t* __restrict__ in, float2* __restrict__ partial,
+                                                         int H, int W, int Hv, int Wv, int C, int nchunk) {
+  __shared__ float2 red[256];
+  const int img = blockIdx.y, chunk = blockIdx.x, tid = threadIdx.x;
+  const int octs = C >> 3, ppp = 256 / octs, oct = tid % octs, pslot = tid / octs;
+  const int npix = Hv * Wv, per = (npix + nchunk - 1) / nchunk;
+  const int p0 = chunk * per, p1 = min(p0 + per, npix);
+  float s = 0.f, q = 0.f;
+  if (pslot < ppp) {
+    for (int pi = p0 + pslot; pi < p1; pi += ppp) {
+      const int y = pi / Wv, x = pi - y * Wv;
+      const uint4 v = __ldg(reinterpret_cast<const uint4*>(in + ((static_cast<long long>(img) * H + y) * W + x) * C) + oct);
+      const uint32_t u[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const float2 f = unpack_act2(u[k]);
+        s += f.x + f.y;
+        q += f.x * f.x + f.y * f.y;
+      }
+    }
+  }
+  red[tid] = make_float2(s, q);
+  __syncthreads();
+  const int G = C >> 4;
+  if (tid < G) {
+    float ss = 0.f, qq = 0.f;
+    for (int ps = 0; ps < ppp; ++ps) {
+      const float2 a = red[ps * octs + 2 * tid], b = red[ps * octs + 2 * tid + 1];
+      ss += a.x + b.x; qq += a.y + b.y;
+    }
+    partial[(static_cast<long long>(img) * nchunk + chunk) * G + tid] = make_float2(ss, qq);
+  }
+}
+
+__global__ void __launch_bounds__(256) gn2d_apply_kernel(const act_t* __restrict__ in, const float2* __restrict__ partial,
+                                                         int nchunk, const float* __restrict__ gamma,
+                                                         const float* __restrict__ beta, const act_t* __restrict__ res,
+                                                         act_t* __restrict__ out, int H, int W, int Hv, int Wv, int C,
+                                                         int relu, int napply) {
+  __shared__ float2 st[32];                       // (mean, rstd) per group, G = C/16 <= 32
+  const int img = blockIdx.y, tid = threadIdx.x, G = C >> 4;
+  if (tid < G) {
+    double s = 0, q = 0;
+    for (int c = 0; c < nchunk; ++c) {
+      const float2 a = partial[(static_cast<long long>(img) * nchunk + c) * G + tid];
+      s += a.x; q += a.y;
+    }
+    const double n = static_cast<double>(Hv) * Wv * 16.0, mean = s / n;
+    const double var = fmax(q / n - mean * mean, 0.0);
+    st[tid] = make_float2(static_cast<float>(mean), static_cast<float>(1.0 / sqrt(var + 1e-5)));
+  }
+  __syncthreads();
+  const int octs = C >> 3, total = H * W * octs, per = (total + napply - 1) / napply;
+  const int i1 = min((blockIdx.x + 1) * per, total);
+  const float floor_v = relu ? 0.0f : -INFINITY;
+  for (int i = blockIdx.x * per + tid; i < i1; i += 256) {
+    const int oct = i % octs, pix = i / octs, y = pix / W, x = pix - y * W;
+    const long long off = ((static_cast<long long>(img) * H + y) * W + x) * C + oct * 8;
+    uint4 o = make_uint4(0u, 0u, 0u, 0u);
+    if (y < Hv && x < Wv) {
+      const uint4 v = __ldg(reinterpret_cast<const uint4*>(in + off));
+      const float2 ms = st[oct >> 1];
+      const float4 g0 = __ldg(reinterpret_cast<const float4*>(gamma + oct * 8)), g1 = __ldg(reinterpret_cast<const float4*>(gamma + oct * 8 + 4));
+      const float4 b0 = __ldg(reinterpret_cast<const float4*>(beta + oct * 8)), b1 = __ldg(reinterpret_cast<const float4*>(beta + oct * 8 + 4));
+      const float ga[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w}, be[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+      const uint32_t u[4] = {v.x, v.y, v.z, v.w};
+      uint32_t r[4] = {0u, 0u, 0u, 0u};
+      if (res != nullptr) {
+        const uint4 rv = __ldg(reinterpret_cast<const uint4*>(res + off));
+        r[0] = rv.x; r[1] = rv.y; r[2] = rv.z; r[3] = rv.w;
+      }
+      uint32_t w[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const float2 f = unpack_act2(u[k]), rr = unpack_act2(r[k]);
+        const float a = fmaxf((f.x - ms.x) * ms.y * ga[2 * k] + be[2 * k] + rr.x, floor_v);
+        const float b = fmaxf((f.y - ms.x) * ms.y * ga[2 * k + 1] + be[2 * k + 1] + rr.y, floor_v);
+        w[k] = pack_act2(a, b);
+      }
+      o = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+    *reinterpret_cast<uint4*>(out + off) = o;
+  }
+}
+
+// float32 CHW image [n_img, 3, in_H, in_W] -> centre crop (off_y, off_x, Hv x Wv) -> padded NHWC4 act_t [H, W + 8] for the
+// stem, zero outside the crop (H, W = crop rounded up to multiples of 32)
+// (values copied as they are: the reference already scaled them to [-1, 1], RolloutDiffusionPolicy.py:121-123).
+__global__ void preprocess_crop_f32_kernel(const float* __restrict__ in, act_t* __restrict__ out, int n_img, int in_H,
+                                           int in_W, int off_y, int off_x, int Hv, int Wv, int H, int W) {
+  const int quads_per_row = W / 4 + 2;
+  const long long total = static_cast<long long>(n_img) * H * quads_per_row;
+  const long long plane = static_cast<long long>(in_H) * in_W;
+  for (long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; idx < total;
+       idx += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int q = static_cast<int>(idx % quads_per_row);
+    const long long row = idx / quads_per_row;
+    const long long img = row / H;
+    const int y = static_cast<int>(row % H);
+    uint32_t w[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
+    if (q >= 1 && q <= W / 4 && y < Hv) {
+      const float* base = in + img * 3 * plane + static_cast<long long>(y + off_y) * in_W + off_x + (q - 1) * 4;
+#pragma unroll
+      for (int p = 0; p < 4; ++p) {
+        if ((q - 1) * 4 + p < Wv) {
+          w[2 * p] = pack_act2(__ldg(base + p), __ldg(base + plane + p));
+          w[2 * p + 1] = pack_act2(__ldg(base + 2 * plane + p), 0.0f);
+        }
+      }
+    }
+    uint4* dst = reinterpret_cast<uint4*>(out + (row * (W + 2 * 4) + q * 4) * 4);
+    dst[0] = make_uint4(w[0], w[1], w[2], w[3]);
+    dst[1] = make_uint4(w[4], w[5], w[6], w[7]);
+  }
+}
+
+// robomimic SpatialSoftmax (num_kp K <= 32, temperature 1) on the 1x1-conv logits [img*H*W, ld] (fp32, first K columns),
+// then Flatten + Linear(2K -> F): one CTA (64 threads) per image. Keypoint k = (E[x], E[y]) over softmax(H*W) with
+// x, y in linspace(-1, 1). out[img * ld_out + j], j < F <= 64.
+__global__ void __launch_bounds__(64) spatial_softmax_linear_kernel(const float* __restrict__ logits, int ld, int H, int W,
+                                                                    int K, const float* __restrict__ Wl,
+                                                                    const float* __restrict__ bl, int F,
+                                                                    float* __restrict__ out, long long ld_out) {
+  __shared__ float kp[64];
+  const int img = blockIdx.x, t = threadIdx.x, HW = H * W;
+  if (t < K) {
+    const float* lg = logits + static_cast<long long>(img) * HW * ld + t;
+    float m = -INFINITY;
+    for (int i = 0; i < HW; ++i) m = fmaxf(m, lg[static_cast<long long>(i) * ld]);
+    float s = 0.f, ex = 0.f, ey = 0.f;
+    for (int i = 0; i < HW; ++i) {
+      const float e = __expf(lg[static_cast<long long>(i) * ld] - m);
+      const int y = i / W, x = i - y * W;
+      const float px = (W > 1) ? -1.0f + 2.0f * x / (W - 1) : 0.f, py = (H > 1) ? -1.0f + 2.0f * y / (H - 1) : 0.f;
+      s += e; ex += e * px; ey += e * py;
+    }
+    kp[2 * t] = ex / s;
+    kp[2 * t + 1] = ey / s;
+  }
+  __syncthreads();
+  if (t < F) {
+    float a = __ldg(bl + t);
+    for (int i = 0; i < 2 * K; ++i) a = fmaf(kp[i], __ldg(Wl + t * 2 * K + i), a);
+    out[static_cast<long long>(img) * ld_out + t] = a;
+  }
+}
+
 }  // namespace rmb

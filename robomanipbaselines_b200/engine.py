@@ -241,3 +241,63 @@ class PointNetEngine:
             self.close()
         except Exception:
             pass
+
+
+class ImgEncEngine:
+    """Handle around rmb_imgenc_engine_t: Diffusion Policy's per-camera image encoder (ResNet-18 + GroupNorm +
+    SpatialSoftmax + Linear) with the centre crop fused into the input pass."""
+
+    def __init__(self, *, max_images, in_h, in_w, crop_h, crop_w, num_kp=32, feat_dim=64, device=0):
+        if not torch.cuda.is_available():
+            raise _lib.RmbError("ImgEncEngine needs a CUDA device (sm_100a); there is no CPU fallback")
+        self.lib = _lib.load()
+        self.cfg = _lib.ImgEncConfig(max_images, in_h, in_w, crop_h, crop_w, num_kp, feat_dim, device)
+        self.device = torch.device("cuda", device)
+        self._h = ctypes.c_void_p()
+        check(self.lib.rmb_imgenc_engine_create(ctypes.byref(self.cfg), ctypes.byref(self._h)), "rmb_imgenc_engine_create")
+
+    def load_state_dict(self, state_dict):
+        """keys relative to obs_encoder.obs_nets.<rgb key> (the duplicated `nets.0/1.*` aliases are ignored)."""
+        sd = {k: v for k, v in state_dict.items() if not (k.startswith("nets.0.") or k.startswith("nets.1."))}
+        _load_tensors(self.lib, self._h, self.lib.rmb_imgenc_load_tensor, sd, "rmb_imgenc_load_tensor")
+        check(self.lib.rmb_imgenc_finalize(self._h), "rmb_imgenc_finalize")
+
+    @property
+    def max_images(self):
+        return self.cfg.max_images
+
+    def flops(self, n):
+        return self.lib.rmb_imgenc_flops(self._h, n)
+
+    def encode(self, images, out=None):
+        """images float32 (n, 3, in_h, in_w) -> features (n, feat_dim); `out` may be a strided view (n, feat_dim) of a
+        wider row-major buffer (the global_cond matrix)."""
+        n, c = images.shape[0], self.cfg
+        if tuple(images.shape) != (n, 3, c.in_h, c.in_w) or images.dtype != torch.float32 or not images.is_cuda \
+                or not images.is_contiguous():
+            raise ValueError(f"images must be a contiguous float32 CUDA tensor (n, 3, {c.in_h}, {c.in_w})")
+        if out is None:
+            out = torch.empty(n, c.feat_dim, device=self.device, dtype=torch.float32)
+        if out.dtype != torch.float32 or out.shape != (n, c.feat_dim) or out.stride(1) != 1:
+            raise ValueError("out must be float32 (n, feat_dim) with unit inner stride")
+        check(self.lib.rmb_imgenc_encode(self._h, ptr(images), ptr(out), out.stride(0), n, cur_stream()),
+              "rmb_imgenc_encode")
+        return out
+
+    def debug_layer4(self, n):
+        c = self.cfg
+        hp, wp = (c.crop_h + 31) // 32 * 32, (c.crop_w + 31) // 32 * 32
+        out = torch.empty(n, hp // 32, wp // 32, 512, device=self.device)
+        check(self.lib.rmb_imgenc_debug_read(self._h, ptr(out), n, cur_stream()), "rmb_imgenc_debug_read")
+        return out
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h.value:
+            self.lib.rmb_imgenc_engine_destroy(self._h)
+            self._h = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -184,3 +184,82 @@ def test_batched_dp3_rollout_matches_reference_glue(cuda):
             assert np.array_equal(act[b], orcs[b].step(chunk)), (step, b)
             assert br._host_pos[b] == Na - len(orcs[b].policy_action_buf)
     assert br.n_inferences == 7
+
+
+def _visual_core_state(seed):
+    """Synthetic weights for one VisualCore; the `nets.0 / nets.1` aliases carry the same tensors as backbone / pool."""
+    from robomanipbaselines_b200.policy.diffusion_policy.policy import visual_core_param_shapes
+
+    shapes = visual_core_param_shapes()
+    uniq = {k: v for k, v in shapes.items() if not (k.startswith("nets.0.") or k.startswith("nets.1."))}
+    sd = synthetic_state_dict(uniq, seed=seed)
+    for k in shapes:
+        if k.startswith("nets.0."):
+            sd[k] = sd["backbone." + k[len("nets.0."):]]
+        elif k.startswith("nets.1."):
+            sd[k] = sd["pool." + k[len("nets.1."):]]
+    return sd
+
+
+@pytest.mark.parametrize("n,in_hw,crop_hw", [(2, (240, 320), (216, 288)), (3, (96, 128), (64, 96))])
+def test_dp_image_encoder(cuda, n, in_hw, crop_hw):
+    from robomanipbaselines_b200.engine import ImgEncEngine
+
+    ref = dor.DpImageEncoder(*crop_hw).eval()
+    sd = _visual_core_state(11)
+    ref.load_state_dict(sd, strict=True)
+    eng = ImgEncEngine(max_images=n, in_h=in_hw[0], in_w=in_hw[1], crop_h=crop_hw[0], crop_w=crop_hw[1])
+    eng.load_state_dict(sd)
+    g = torch.Generator().manual_seed(12)
+    img = torch.rand(n, 3, *in_hw, generator=g) * 2 - 1
+    with torch.no_grad():
+        want = ref(img)
+        t, l = (in_hw[0] - crop_hw[0]) // 2, (in_hw[1] - crop_hw[1]) // 2
+        want_l4 = ref.backbone(img[..., t:t + crop_hw[0], l:l + crop_hw[1]]).permute(0, 2, 3, 1)
+    got = eng.encode(img.to(cuda)).cpu()
+    got_l4 = eng.debug_layer4(n).cpu()[:, :want_l4.shape[1], :want_l4.shape[2]]
+    e4 = (got_l4 - want_l4).abs().max().item()
+    err = (got - want).abs().max().item()
+    print(f"[dp imgenc n{n} {in_hw}->{crop_hw}] layer4 max-abs err {e4:.3e} (ref max {want_l4.abs().max().item():.3e}); "
+          f"feature err {err:.3e} (ref max {want.abs().max().item():.3e})")
+    assert err <= 1e-2 and e4 <= 5e-2
+
+
+def test_dp_predict_action(cuda):
+    """DiffusionUnetHybridImagePolicy.predict_action (TrainDiffusionPolicy.py:100-138 arguments, DDPM-100, one camera +
+    7-d state) against the oracle modules with shared x_T and per-step noise."""
+    from robomanipbaselines_b200.policy.diffusion_policy import DiffusionUnetHybridImagePolicy
+
+    B, To, Ds, Da, H, W = 2, 2, 7, 7, 240, 320
+    sched_args = dict(SCHED, prediction_type="epsilon", variance_type="fixed_small")
+    pol = DiffusionUnetHybridImagePolicy(
+        noise_scheduler=DDPMScheduler(**sched_args),
+        shape_meta={"obs": {"state": {"shape": [Ds], "type": "low_dim"},
+                            "front_rgb_image": {"shape": [3, H, W], "type": "rgb"}}, "action": {"shape": [Da]}},
+        horizon=16, n_action_steps=8, n_obs_steps=To, num_inference_steps=100, obs_as_global_cond=True,
+        crop_shape=(216, 288), diffusion_step_embed_dim=128, down_dims=[512, 1024, 2048], kernel_size=5, n_groups=8,
+        cond_predict_scale=True, obs_encoder_group_norm=True, eval_fixed_crop=True)
+    shapes = {k: tuple(v.shape) for k, v in pol.state_dict().items()}
+    sd = synthetic_state_dict({k: v for k, v in shapes.items() if k.startswith("model.")}, seed=13)
+    vc = _visual_core_state(14)
+    sd.update({"obs_encoder.obs_nets.front_rgb_image." + k: v for k, v in vc.items()})
+    assert set(sd) == set(shapes)
+    pol.load_state_dict(sd, strict=True)
+    enc, unet = dor.DpImageEncoder(216, 288).eval(), dor.ConditionalUnet1D(Da, To * (64 + Ds)).eval()
+    enc.load_state_dict(vc)
+    unet.load_state_dict({k[len("model."):]: v for k, v in sd.items() if k.startswith("model.")})
+    g = torch.Generator().manual_seed(15)
+    img = torch.rand(B, To, 3, H, W, generator=g) * 2 - 1
+    st = torch.randn(B, To, Ds, generator=g)
+    x0 = torch.randn(B, 16, Da, generator=g)
+    noise = torch.randn(100, B, 16, Da, generator=g)
+    with torch.no_grad():
+        f = enc(img.reshape(B * To, 3, H, W))
+    cond = torch.cat([st.reshape(B * To, Ds), f], dim=-1).reshape(B, -1)
+    orc = dor.DDPMSchedulerOracle(**SCHED, prediction_type="epsilon")
+    want = dor.conditional_sample(unet, orc, cond, x0, noise, 100)[:, To - 1:To - 1 + 8]
+    got = pol.predict_action({"state": st.to(cuda), "front_rgb_image": img.to(cuda)}, x_init=x0.to(cuda),
+                             step_noise=noise.to(cuda))["action"].cpu()
+    err = (got - want).abs().max().item()
+    print(f"[dp predict_action ddpm-100] max-abs err {err:.3e} (ref max {want.abs().max().item():.3e})")
+    assert got.shape == (B, 8, Da) and err <= 1e-2
