@@ -106,6 +106,92 @@ def build_rollout(device, batch):
     return pol, meta, BatchedRollout(pol, batch, meta, device=str(device))
 
 
+def bench_diffusion(device, reps=2):
+    """Secondary workloads of BASELINE.json (configs[2] and the per-GPU share of configs[4]): one predict_action =
+    obs encoder + the whole scheduler loop, synthetic observations resident in HBM, CUDA events. Reported as
+    inferences/s and policy steps/s (one inference is amortised over n_action_steps = 8 policy steps)."""
+    from robomanipbaselines_b200.common.schedulers import DDIMScheduler, DDPMScheduler
+    from robomanipbaselines_b200.common.synthetic import synthetic_state_dict
+    from robomanipbaselines_b200.policy.diffusion_policy import DiffusionUnetHybridImagePolicy
+    from robomanipbaselines_b200.policy.diffusion_policy.policy import visual_core_param_shapes
+    from robomanipbaselines_b200.policy.diffusion_policy_3d import DP3
+
+    sched = dict(beta_end=0.02, beta_schedule="squaredcos_cap_v2", beta_start=0.0001, clip_sample=True,
+                 num_train_timesteps=100)
+    out = {}
+    gen = torch.Generator(device=device).manual_seed(3)
+
+    def timed(fn):
+        fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / reps
+
+    # ---- configs[2]: Diffusion Policy, batch 1024, DDPM 100 and DDIM-like 16 steps, one 240x320 camera + 7-d state
+    B, To = 1024, 2
+    pol = DiffusionUnetHybridImagePolicy(
+        noise_scheduler=DDPMScheduler(**sched, prediction_type="epsilon", variance_type="fixed_small"),
+        shape_meta={"obs": {"state": {"shape": [DS], "type": "low_dim"},
+                            "front_rgb_image": {"shape": [3, 240, 320], "type": "rgb"}}, "action": {"shape": [DA]}},
+        horizon=16, n_action_steps=8, n_obs_steps=To, num_inference_steps=100, obs_as_global_cond=True,
+        crop_shape=(216, 288), diffusion_step_embed_dim=128, down_dims=[512, 1024, 2048], kernel_size=5, n_groups=8,
+        cond_predict_scale=True, obs_encoder_group_norm=True, eval_fixed_crop=True, max_batch=B)
+    shapes = {k: tuple(v.shape) for k, v in pol.state_dict().items()}
+    sd = synthetic_state_dict({k: v for k, v in shapes.items() if k.startswith("model.")}, seed=0)
+    vc_shapes = visual_core_param_shapes()
+    vc = synthetic_state_dict({k: v for k, v in vc_shapes.items() if not k.startswith(("nets.0.", "nets.1."))}, seed=0)
+    for k in vc_shapes:
+        if k.startswith("nets.0."):
+            vc[k] = vc["backbone." + k[7:]]
+        elif k.startswith("nets.1."):
+            vc[k] = vc["pool." + k[7:]]
+    sd.update({"obs_encoder.obs_nets.front_rgb_image." + k: v for k, v in vc.items()})
+    pol.load_state_dict(sd, strict=True)
+    obs = {"state": torch.randn(B, To, DS, device=device, generator=gen),
+           "front_rgb_image": torch.rand(B, To, 3, 240, 320, device=device, generator=gen) * 2 - 1}
+    ms_enc = timed(lambda: pol.encode_obs(obs))
+    ms = timed(lambda: pol.predict_action(obs))
+    unet = pol.unet_for(B, device)
+    enc = pol.encoder_for("front_rgb_image", B * To, device)
+    flops = unet.step_flops(B) * 100 + enc.flops(B * To)
+    out["diffusion_policy_c3"] = {
+        "workload": "DiffusionUnetHybridImagePolicy.predict_action, batch 1024, horizon 16, DDPM 100 steps, ResNet-18 "
+                    "(GroupNorm) obs encoder on one 240x320 camera (crop 216x288) x 2 obs steps + 7-d state",
+        "ms_per_inference_batch": ms, "ms_obs_encoder": ms_enc, "inferences_per_s": B / ms * 1e3,
+        "policy_steps_per_s": 8 * B / ms * 1e3, "model_tflops": flops / ms / 1e9,
+        "gpu_launches": unet.launches_per_step * 100 + 3 + 70}
+    del pol, obs, unet, enc
+    torch.cuda.empty_cache()
+
+    # ---- configs[4] per-GPU share: DP3, batch 512 (= 4096 / 8), 1024-point clouds, DDIM 10 and 16
+    B = 512
+    for n_steps in (10, 16):
+        pol = DP3(noise_scheduler=DDIMScheduler(**sched, set_alpha_to_one=True, prediction_type="sample", steps_offset=0),
+                  shape_meta={"obs": {"state": {"shape": [DS]}, "point_cloud": {"shape": (1024, 6)}}, "action": {"shape": [DA]}},
+                  horizon=16, n_action_steps=8, n_obs_steps=To, num_inference_steps=n_steps, diffusion_step_embed_dim=128,
+                  down_dims=[512, 1024, 2048], kernel_size=5, n_groups=8, pointcloud_encoder_cfg={"out_channels": 64},
+                  use_pc_color=False, encoder_output_dim=64, max_batch=B)
+        pol.load_state_dict(synthetic_state_dict({k: tuple(v.shape) for k, v in pol.state_dict().items()}, seed=0))
+        obs = {"state": torch.randn(B, To, DS, device=device, generator=gen),
+               "point_cloud": torch.rand(B, To, 1024, 6, device=device, generator=gen) * 2 - 1}
+        ms_enc = timed(lambda: pol.encode_obs(obs))
+        ms = timed(lambda: pol.predict_action(obs))
+        unet = pol.unet_for(B, device)
+        out[f"dp3_c5_ddim{n_steps}"] = {
+            "workload": f"DP3.predict_action, batch 512 per GPU (4096 / 8), 2 x 1024-point clouds + 7-d state, DDIM {n_steps} steps",
+            "ms_per_inference_batch": ms, "ms_obs_encoder": ms_enc, "inferences_per_s": B / ms * 1e3,
+            "policy_steps_per_s": 8 * B / ms * 1e3, "model_tflops": unet.step_flops(B) * n_steps / ms / 1e9,
+            "gpu_launches": unet.launches_per_step * n_steps + 3 + 7}
+        del pol, obs, unet
+        torch.cuda.empty_cache()
+    return out
+
+
 def cpu_reference_step(sd, meta, oracles, images_u8, raw_state, live_only):
     """One policy step of the reference path for len(oracles) episodes on the CPU (oracle port, fp32 PyTorch + numpy)."""
     from oracle import act_oracle, rollout_oracle
@@ -171,6 +257,7 @@ def main():
     ap.add_argument("--batch", type=int, default=256, help="episodes per GPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-latency", action="store_true")
+    ap.add_argument("--no-diffusion", action="store_true", help="skip the Diffusion Policy / DP3 side measurements")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -333,6 +420,11 @@ def main():
         }
         if latency:
             line["latency"] = latency
+        if world == 1 and not args.no_diffusion:
+            del imgs, d_imgs, h_imgs
+            pol._invalidate()
+            torch.cuda.empty_cache()
+            line["other_configs"] = bench_diffusion(device)
         if world == 1 and not args.no_cpu_baseline:
             sample = 4
             times, cores = time_cpu_baseline(sample, 4, 1, live_only=False)
