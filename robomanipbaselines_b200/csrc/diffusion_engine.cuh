@@ -12,8 +12,39 @@
 // global_cond share of all 12 FiLM projections is ONE GEMM per inference.
 #pragma once
 #include "diffusion_kernels.cuh"
+#include "gemm_gn.cuh"
 
 namespace {
+
+// gemm_tc_kernel with the fused GroupNorm + Mish + FiLM + residual epilogue (gemm_gn.cuh)
+template <int BN, int ST>
+cudaError_t launch_gemm_gn_instance(const GemmPlan& g, int num_sms, cudaStream_t stream) {
+  using S = GemmSmem<BN, 64, ST>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<BN, 64, ST, false, 0, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal);
+    if (e != cudaSuccess) return e;
+    attr_set = true;
+  }
+  const long long tiles = 1ll * g.p.tiles_w * g.p.tiles_h * g.p.tiles_b * g.p.n_col_tiles;
+  const int grid = static_cast<int>(std::min<long long>(tiles, num_sms));
+  gemm_tc_kernel<BN, 64, ST, false, 0, 1><<<grid, kGemmThreads, S::kTotal, stream>>>(g.ta, g.tb, g.p);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_gemm_gn(const GemmPlan& g, int num_sms, cudaStream_t stream) {
+  if (g.block_n == 64) return launch_gemm_gn_instance<64, 6>(g, num_sms, stream);
+  if (g.block_n == 128) return launch_gemm_gn_instance<128, 6>(g, num_sms, stream);
+  if (g.block_n == 256) return launch_gemm_gn_instance<256, 4>(g, num_sms, stream);
+  return cudaErrorInvalidValue;
+}
+
+// can this conv plan normalise its own output? (whole samples per row tile, whole groups per column tile)
+bool gn_fusable(const GemmPlan& g, int T, int C) {
+  const int cg = C / 8;
+  return g.p.tiles_w == 1 && g.p.tiles_h == 1 && g.p.box_w == T && g.p.box_h == 1 && 128 % T == 0 && cg % 32 == 0 &&
+         g.block_n % cg == 0 && g.p.bias != nullptr && g.block_k == 64;
+}
 
 // Conv1d-style implicit GEMM over a [B, W_view, c_extent] view (row stride / batch stride in elements).
 bool plan_conv1d(GemmPlan* g, const void* in, int c_extent, long long row_stride, int W_view, long long batch_stride,
@@ -63,6 +94,7 @@ struct rmb_unet_engine {
   std::vector<void*> allocs;
 
   int L = 0, d[4] = {}, Tl[4] = {};
+  bool fuse_gn = true;                      // RMB_UNET_NO_FUSE=1 keeps GroupNorm in its own kernel (A/B measurements)
   struct Crb {
     std::string name;
     int cin = 0, cout = 0, T = 0, film_off = 0;
@@ -86,7 +118,7 @@ struct rmb_unet_engine {
   float *film_gc = nullptr, *conv_out = nullptr, *x_state = nullptr;
 
   struct Op {
-    int kind = 0;                           // 0 GEMM, 1 GroupNorm(+Mish+FiLM+residual)
+    int kind = 0;                           // 0 GEMM, 1 GroupNorm(+Mish+FiLM+residual), 2 GEMM with that fused in
     GemmPlan g;
     GnParams gn;
     std::string name;
@@ -162,6 +194,7 @@ int rmb_unet_engine_create(const rmb_unet_config_t* cfg, rmb_unet_engine_t** out
   cudaGetDeviceProperties(&prop, cfg->device);
   e->num_sms = prop.multiProcessorCount;
   e->L = cfg->n_levels;
+  { const char* nf = getenv("RMB_UNET_NO_FUSE"); e->fuse_gn = !(nf && nf[0] == '1'); }
   for (int i = 0; i < e->L; ++i) { e->d[i] = cfg->down_dims[i]; e->Tl[i] = cfg->horizon >> i; }
   *out = e;
   return 0;
@@ -382,26 +415,39 @@ static int unet_build_plans(rmb_unet_engine* e, int nb, rmb_unet_engine::Plans**
     op.bytes = (double)nb * T * C * (4 + 2 + (res ? 2 : 0)) + (film_off >= 0 ? (double)nb * 2 * C * 4 : 0);
     pl->ops.push_back(op);
   };
+  // conv + GroupNorm + Mish (+ FiLM) (+ residual): one launch when the tile holds whole (sample, group)s, else two
+  auto conv_gn = [&](const std::string& name, const act_t* in, int ld_in, int Cin, int T, int ntaps, const act_t* W,
+                     int Cout, const float* bias, const float* gamma, const float* beta, int film_off, const act_t* res,
+                     int ld_res, act_t* outp, int ld_out) -> bool {
+    if (!conv_s1(name, in, ld_in, Cin, T, ntaps, W, Cout, bias, e->conv_out, Cout, true)) return false;
+    Op& op = pl->ops.back();
+    if (e->fuse_gn && gn_fusable(op.g, T, Cout)) {
+      GemmParams& p = op.g.p;
+      op.kind = 2;
+      op.name += film_off >= 0 ? "+gn+mish+film" : (res ? "+gn+mish+res" : "+gn+mish");
+      p.out = outp; p.ld_out = ld_out; p.out_f32 = 0;
+      p.gn_gamma = gamma; p.gn_beta = beta; p.gn_cg = Cout / 8;
+      p.gn_film_gc = film_off >= 0 ? e->film_gc : nullptr; p.gn_film_t = e->film_t; p.gn_film_ld = e->film_total;
+      p.gn_film_off = film_off >= 0 ? film_off : 0;
+      p.gn_res = res; p.gn_ld_res = ld_res;
+      op.bytes = (double)nb * T * Cin * 2 + (double)Cout * ntaps * Cin * 2 + (double)nb * T * Cout * (2 + (res ? 2 : 0)) +
+                 (film_off >= 0 ? (double)nb * 2 * Cout * 4 : 0);
+      return true;
+    }
+    gn(name + " gn+mish", Cout, T, gamma, beta, film_off, res, ld_res, outp, ld_out);
+    return true;
+  };
   // ConditionalResidualBlock1D: x_in [nb, T, cin] (ld_x) -> x_out (ld_o)
   auto crb = [&](const rmb_unet_engine::Crb& b, const act_t* x_in, int ld_x, act_t* x_out, int ld_o) -> bool {
     const act_t* res = x_in; int ld_res = ld_x;
-    if (b.first) {
-      if (!conv_s1(b.name + " conv0", e->xcol, kXcolWidth, kXcolWidth, b.T, 1, b.w0, b.cout, b.b0, e->conv_out, b.cout, true)) return false;
-    } else {
-      if (!conv_s1(b.name + " conv0", x_in, ld_x, b.cin, b.T, K, b.w0, b.cout, b.b0, e->conv_out, b.cout, true)) return false;
-    }
-    gn(b.name + " gn0+mish+film", b.cout, b.T, b.g0, b.be0, b.film_off, nullptr, 0, e->h1, b.cout);
+    const act_t* in0 = b.first ? e->xcol : x_in;
+    const int ld0 = b.first ? kXcolWidth : ld_x, cin0 = b.first ? kXcolWidth : b.cin, taps0 = b.first ? 1 : K;
+    if (!conv_gn(b.name + " conv0", in0, ld0, cin0, b.T, taps0, b.w0, b.cout, b.b0, b.g0, b.be0, b.film_off, nullptr, 0, e->h1, b.cout)) return false;
     if (b.has_res) {
-      if (b.first) {
-        if (!conv_s1(b.name + " res1x1", e->xcol, kXcolWidth, kXcolWidth, b.T, 1, b.wres, b.cout, b.bres, e->resb, b.cout, false)) return false;
-      } else {
-        if (!conv_s1(b.name + " res1x1", x_in, ld_x, b.cin, b.T, 1, b.wres, b.cout, b.bres, e->resb, b.cout, false)) return false;
-      }
+      if (!conv_s1(b.name + " res1x1", in0, ld0, cin0, b.T, 1, b.wres, b.cout, b.bres, e->resb, b.cout, false)) return false;
       res = e->resb; ld_res = b.cout;
     }
-    if (!conv_s1(b.name + " conv1", e->h1, b.cout, b.cout, b.T, K, b.w1, b.cout, b.b1, e->conv_out, b.cout, true)) return false;
-    gn(b.name + " gn1+mish+res", b.cout, b.T, b.g1, b.be1, -1, res, ld_res, x_out, ld_o);
-    return true;
+    return conv_gn(b.name + " conv1", e->h1, b.cout, b.cout, b.T, K, b.w1, b.cout, b.b1, b.g1, b.be1, -1, res, ld_res, x_out, ld_o);
   };
 
   // once per inference: FiLM(global_cond) for all blocks
@@ -493,6 +539,12 @@ static int unet_run_eval(rmb_unet_engine* e, rmb_unet_engine::Plans* pl, int nb,
       begin(op.name, "gemm_tc_kernel", (double)op.g.flops, op.bytes);
       RMB_CUDA(launch_gemm(op.g, e->num_sms, s));
       end();
+    } else if (op.kind == 2) {
+      GemmPlan g = op.g;
+      g.p.gn_film_t = film_t_row;
+      begin(op.name, "gemm_tc_kernel<gn>", (double)op.g.flops, op.bytes);
+      RMB_CUDA(launch_gemm_gn(g, e->num_sms, s));
+      end();
     } else {
       GnParams g = op.gn;
       g.film_t = film_t_row;
@@ -532,8 +584,9 @@ extern "C" {
 
 int rmb_unet_launches_per_step(const rmb_unet_engine_t* e) {
   if (!e) return -1;
+  if (!e->plans.empty()) return (int)e->plans.begin()->second->ops.size() + 1;   // as planned (+ the final kernel)
   int n = 1 + 1;                                  // final conv + final kernel
-  for (auto& b : e->crbs) n += 4 + (b.has_res ? 1 : 0);
+  for (auto& b : e->crbs) n += (e->fuse_gn ? 2 : 4) + (b.has_res ? 1 : 0);
   n += (e->L - 1) * 3;                            // down conv + 2 convT phases per level
   return n;
 }

@@ -1,0 +1,132 @@
+// Fused epilogue of the ConditionalUnet1D convs: conv bias -> GroupNorm(8) -> Mish -> FiLM (scale * y + bias) ->
+// + residual -> 16-bit store, computed on the TMEM accumulator of gemm_tc_kernel<..., EPI = 1>, so the Conv1dBlock
+// output never makes a round trip through HBM before it is normalised
+// (upstream diffusion_policy Conv1dBlock / ConditionalResidualBlock1D; oracle/diffusion_oracle.py:57-94).
+//
+// Why it fits one tile: rows of a tile are box_b whole samples x T time steps (128 % T == 0) and a group is
+// C/8 channels wide, a multiple of 32 that divides BLOCK_N, so every (sample, group) the tile touches is complete
+// inside it. Two sweeps over the accumulator (tcgen05.ld is cheap): sweep 1 leaves per-(row, 32-column chunk) sums
+// in shared memory, a 256-thread named barrier, each thread reduces the T rows x Cg/32 chunks of its own sample's
+// groups, sweep 2 normalises and stores. The MMA warp is already working on the next tile (double-buffered TMEM).
+#pragma once
+#include "diffusion_kernels.cuh"
+#include "gemm_tc.cuh"
+
+namespace rmb {
+
+template <int BLOCK_N>
+__device__ __forceinline__ void gemm_gn_epilogue(const GemmParams& p, uint8_t* smem_stage, uint32_t tmem_base,
+                                                 uint64_t* tmem_full_bar, uint64_t* tmem_empty_bar, int total_tiles,
+                                                 int warp, int lane) {
+  constexpr int kChunks = BLOCK_N / 32;   // 32-column chunks of a tile
+  constexpr int kMine = kChunks / 2;      // chunks handled by this warp: columns half * BLOCK_N/2 .. +BLOCK_N/2
+  float2* stat = reinterpret_cast<float2*>(smem_stage);          // [128 rows][kChunks] (sum, sum of squares)
+  const int q = warp & 3, half = warp >> 2;
+  const int r = q * 32 + lane;
+  const int T = p.box_w, rows_per_tile = p.box_w * p.box_b;
+  const int wl = r % T, bl = r / T;
+  const int cpg = p.gn_cg >> 5;                                  // chunks per group
+  const float inv_n = 1.0f / static_cast<float>(T * p.gn_cg);
+  const int N = p.n_col_tiles * BLOCK_N;
+  int acc = 0; uint32_t acc_phase = 0;
+  for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+    const int ct = tile % p.n_col_tiles, bt = tile / p.n_col_tiles;
+    const int b = bt * p.box_b + bl;
+    const bool valid = (r < rows_per_tile) && (b < p.B);
+    const long long grow = static_cast<long long>(b) * T + wl;
+    const int n0 = ct * BLOCK_N;
+    mbar_wait(&tmem_full_bar[acc], acc_phase);
+    tc_fence_after();
+    const uint32_t t_row = tmem_base + acc * BLOCK_N + (static_cast<uint32_t>(q * 32) << 16);
+    uint32_t v[32];
+    // ---- sweep 1: per-row partial sums of (acc + bias) per 32-column chunk
+#pragma unroll
+    for (int j = 0; j < kMine; ++j) {
+      const int c = half * kMine + j;
+      tmem_ld_32x32b_x32(t_row + c * 32, v);
+      tmem_ld_wait();
+      const float4* bp = reinterpret_cast<const float4*>(p.bias + n0 + c * 32);
+      float s = 0.f, qq = 0.f;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const float4 b4 = __ldg(bp + i);
+        const float x0 = __uint_as_float(v[4 * i]) + b4.x, x1 = __uint_as_float(v[4 * i + 1]) + b4.y;
+        const float x2 = __uint_as_float(v[4 * i + 2]) + b4.z, x3 = __uint_as_float(v[4 * i + 3]) + b4.w;
+        s += (x0 + x1) + (x2 + x3);
+        qq += (x0 * x0 + x1 * x1) + (x2 * x2 + x3 * x3);
+      }
+      stat[r * kChunks + c] = make_float2(s, qq);
+    }
+    named_bar_sync(1, 256);
+    // ---- statistics of the groups this warp's columns belong to (<= kMine distinct groups)
+    float g_mean[kMine], g_rstd[kMine];
+#pragma unroll
+    for (int j = 0; j < kMine; ++j) {
+      const int c = half * kMine + j, gi = c / cpg;
+      if (j > 0 && gi == (c - 1) / cpg) { g_mean[j] = g_mean[j - 1]; g_rstd[j] = g_rstd[j - 1]; continue; }
+      float s = 0.f, qq = 0.f;
+      for (int rr = bl * T; rr < bl * T + T; ++rr)
+        for (int cc = gi * cpg; cc < gi * cpg + cpg; ++cc) {
+          const float2 a = stat[rr * kChunks + cc];
+          s += a.x; qq += a.y;
+        }
+      const float mean = s * inv_n;
+      g_mean[j] = mean;
+      g_rstd[j] = rsqrtf(fmaxf(qq * inv_n - mean * mean, 0.0f) + 1e-5f);
+    }
+    named_bar_sync(1, 256);                                       // stat[] may be overwritten by the next tile
+    // ---- sweep 2: normalise, Mish, FiLM, residual, store
+    const float* fg = (p.gn_film_gc != nullptr && valid) ? p.gn_film_gc + static_cast<long long>(b) * p.gn_film_ld + p.gn_film_off + n0 : nullptr;
+    const float* ft = p.gn_film_t + p.gn_film_off + n0;
+    const act_t* rp = (p.gn_res != nullptr && valid) ? static_cast<const act_t*>(p.gn_res) + grow * p.gn_ld_res + n0 : nullptr;
+    act_t* op = static_cast<act_t*>(p.out) + grow * p.ld_out + n0;
+#pragma unroll
+    for (int j = 0; j < kMine; ++j) {
+      const int c = half * kMine + j;
+      tmem_ld_32x32b_x32(t_row + c * 32, v);
+      tmem_ld_wait();
+      if (j + 1 == kMine) {
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);         // 8 arrivals free the accumulator
+      }
+      const float mean = g_mean[j], rstd = g_rstd[j];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {                               // 8 columns per iteration
+        const int col = c * 32 + i * 8;
+        float x[8];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bias + n0 + col) + h);
+          const float4 g4 = __ldg(reinterpret_cast<const float4*>(p.gn_gamma + n0 + col) + h);
+          const float4 e4 = __ldg(reinterpret_cast<const float4*>(p.gn_beta + n0 + col) + h);
+          x[4 * h + 0] = mish_f((__uint_as_float(v[8 * i + 4 * h + 0]) + b4.x - mean) * rstd * g4.x + e4.x);
+          x[4 * h + 1] = mish_f((__uint_as_float(v[8 * i + 4 * h + 1]) + b4.y - mean) * rstd * g4.y + e4.y);
+          x[4 * h + 2] = mish_f((__uint_as_float(v[8 * i + 4 * h + 2]) + b4.z - mean) * rstd * g4.z + e4.z);
+          x[4 * h + 3] = mish_f((__uint_as_float(v[8 * i + 4 * h + 3]) + b4.w - mean) * rstd * g4.w + e4.w);
+        }
+        if (fg != nullptr) {
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            const float4 s1 = __ldg(reinterpret_cast<const float4*>(fg + col) + h), s2 = __ldg(reinterpret_cast<const float4*>(ft + col) + h);
+            const float4 b1 = __ldg(reinterpret_cast<const float4*>(fg + N + col) + h), b2 = __ldg(reinterpret_cast<const float4*>(ft + N + col) + h);
+            x[4 * h + 0] = (s1.x + s2.x) * x[4 * h + 0] + (b1.x + b2.x);
+            x[4 * h + 1] = (s1.y + s2.y) * x[4 * h + 1] + (b1.y + b2.y);
+            x[4 * h + 2] = (s1.z + s2.z) * x[4 * h + 2] + (b1.z + b2.z);
+            x[4 * h + 3] = (s1.w + s2.w) * x[4 * h + 3] + (b1.w + b2.w);
+          }
+        }
+        if (rp != nullptr) {
+          const uint4 rv = __ldg(reinterpret_cast<const uint4*>(rp + col));
+          const float2 r0 = unpack_act2(rv.x), r1 = unpack_act2(rv.y), r2 = unpack_act2(rv.z), r3 = unpack_act2(rv.w);
+          x[0] += r0.x; x[1] += r0.y; x[2] += r1.x; x[3] += r1.y; x[4] += r2.x; x[5] += r2.y; x[6] += r3.x; x[7] += r3.y;
+        }
+        if (valid)
+          *reinterpret_cast<uint4*>(op + col) = make_uint4(pack_act2(x[0], x[1]), pack_act2(x[2], x[3]), pack_act2(x[4], x[5]), pack_act2(x[6], x[7]));
+      }
+    }
+    if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+  }
+}
+
+}  // namespace rmb

@@ -37,6 +37,16 @@ struct GemmParams {
   // optional output-row remap: rows (img, h, w) -> token rows of DETRVAE's flattened multi-camera feature map
   //   out_row = (img / remap_ncam) * remap_L + remap_off + h * (W * remap_ncam) + (img % remap_ncam) * W + w
   int remap_ncam, remap_L, remap_off;
+  // fused GroupNorm(8) + Mish (+ FiLM) (+ residual) epilogue of the ConditionalUnet1D convs (EPI == 1, gemm_gn.cuh):
+  // rows of a tile are whole samples (box_w = T rows each), `bias` is the conv bias, `out` is act_t
+  const float* gn_gamma;     // [N]
+  const float* gn_beta;      // [N]
+  const float* gn_film_gc;   // [B, gn_film_ld] or nullptr: scale at gn_film_off + c, bias at gn_film_off + N + c
+  const float* gn_film_t;    // the diffusion step's row of the FiLM table (same indexing); set per launch
+  int gn_film_ld, gn_film_off;
+  const void* gn_res;        // act_t [rows, gn_ld_res] or nullptr
+  int gn_ld_res;
+  int gn_cg;                 // channels per group = N / 8
 };
 
 template <int BLOCK_N, int BLOCK_K, int STAGES>
@@ -168,8 +178,14 @@ __device__ __forceinline__ void gemm_epilogue(const GemmParams& p, uint8_t* smem
   }
 }
 
+template <int BLOCK_N>
+__device__ __forceinline__ void gemm_gn_epilogue(const GemmParams& p, uint8_t* smem_stage, uint32_t tmem_base,
+                                                 uint64_t* tmem_full_bar, uint64_t* tmem_empty_bar, int total_tiles,
+                                                 int warp, int lane);
+
 // OUT_F32: fp32 output (else act_t). RES: 0 no residual, 1 act_t residual, 2 fp32 residual.
-template <int BLOCK_N, int BLOCK_K, int STAGES, bool OUT_F32, int RES>
+// EPI: 0 plain epilogue (bias / residual / ReLU), 1 fused GroupNorm + Mish + FiLM + residual (gemm_gn.cuh).
+template <int BLOCK_N, int BLOCK_K, int STAGES, bool OUT_F32, int RES, int EPI = 0>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                const __grid_constant__ GemmParams p) {
@@ -277,7 +293,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
   } else {
-    gemm_epilogue<BLOCK_N, OUT_F32, RES>(p, smem_stage, tmem_base, tmem_full_bar, tmem_empty_bar, total_tiles, warp, lane);
+    if constexpr (EPI == 1)
+      gemm_gn_epilogue<BLOCK_N>(p, smem_stage, tmem_base, tmem_full_bar, tmem_empty_bar, total_tiles, warp, lane);
+    else
+      gemm_epilogue<BLOCK_N, OUT_F32, RES>(p, smem_stage, tmem_base, tmem_full_bar, tmem_empty_bar, total_tiles, warp, lane);
   }
 
   tc_fence_before();

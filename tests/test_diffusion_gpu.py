@@ -263,3 +263,18 @@ def test_dp_predict_action(cuda):
     err = (got - want).abs().max().item()
     print(f"[dp predict_action ddpm-100] max-abs err {err:.3e} (ref max {want.abs().max().item():.3e})")
     assert got.shape == (B, 8, Da) and err <= 1e-2
+
+
+def test_unet_forward_unfused_groupnorm(cuda, monkeypatch):
+    """RMB_UNET_NO_FUSE=1 keeps GroupNorm + Mish + FiLM in unet_gn_mish_kernel: same results as the fused epilogue."""
+    c, ref, eng_fused, x, gc, _ = _unet_pair("full_dp3", cuda)
+    monkeypatch.setenv("RMB_UNET_NO_FUSE", "1")
+    _, _, eng_plain, _, _, _ = _unet_pair("full_dp3", cuda)
+    a = eng_fused.forward(x.to(cuda), 42, gc.to(cuda)).cpu()
+    b = eng_plain.forward(x.to(cuda), 42, gc.to(cuda)).cpu()
+    with torch.no_grad():
+        want = ref(x, 42, gc)
+    print(f"[unet fused vs plain] fused err {(a - want).abs().max().item():.3e}, plain err {(b - want).abs().max().item():.3e}, "
+          f"launches {eng_fused.launches_per_step} vs {eng_plain.launches_per_step}")
+    assert eng_fused.launches_per_step < eng_plain.launches_per_step
+    assert (a - want).abs().max().item() <= 1e-2 and (b - want).abs().max().item() <= 1e-2
