@@ -17,32 +17,33 @@
 namespace {
 
 // gemm_tc_kernel with the fused GroupNorm + Mish + FiLM + residual epilogue (gemm_gn.cuh)
-template <int BN, int ST>
+template <int BN, int ST, int EPI>
 cudaError_t launch_gemm_gn_instance(const GemmPlan& g, int num_sms, cudaStream_t stream) {
   using S = GemmSmem<BN, 64, ST>;
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<BN, 64, ST, false, 0, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal);
+    cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<BN, 64, ST, false, 0, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal);
     if (e != cudaSuccess) return e;
     attr_set = true;
   }
   const long long tiles = 1ll * g.p.tiles_w * g.p.tiles_h * g.p.tiles_b * g.p.n_col_tiles;
   const int grid = static_cast<int>(std::min<long long>(tiles, num_sms));
-  gemm_tc_kernel<BN, 64, ST, false, 0, 1><<<grid, kGemmThreads, S::kTotal, stream>>>(g.ta, g.tb, g.p);
+  gemm_tc_kernel<BN, 64, ST, false, 0, EPI><<<grid, kGemmThreads, S::kTotal, stream>>>(g.ta, g.tb, g.p);
   return cudaGetLastError();
 }
 
 cudaError_t launch_gemm_gn(const GemmPlan& g, int num_sms, cudaStream_t stream) {
-  if (g.block_n == 64) return launch_gemm_gn_instance<64, 6>(g, num_sms, stream);
-  if (g.block_n == 128) return launch_gemm_gn_instance<128, 6>(g, num_sms, stream);
-  if (g.block_n == 256) return launch_gemm_gn_instance<256, 4>(g, num_sms, stream);
+  const bool film = g.p.gn_film_gc != nullptr;
+  if (g.block_n == 64) return film ? launch_gemm_gn_instance<64, 6, 1>(g, num_sms, stream) : launch_gemm_gn_instance<64, 6, 2>(g, num_sms, stream);
+  if (g.block_n == 128) return film ? launch_gemm_gn_instance<128, 6, 1>(g, num_sms, stream) : launch_gemm_gn_instance<128, 6, 2>(g, num_sms, stream);
+  if (g.block_n == 256) return film ? launch_gemm_gn_instance<256, 4, 1>(g, num_sms, stream) : launch_gemm_gn_instance<256, 4, 2>(g, num_sms, stream);
   return cudaErrorInvalidValue;
 }
 
 // can this conv plan normalise its own output? (whole samples per row tile, whole groups per column tile)
 bool gn_fusable(const GemmPlan& g, int T, int C) {
   const int cg = C / 8;
-  return g.p.tiles_w == 1 && g.p.tiles_h == 1 && g.p.box_w == T && g.p.box_h == 1 && 128 % T == 0 && cg % 32 == 0 &&
+  return g.p.tiles_w == 1 && g.p.tiles_h == 1 && g.p.box_w == T && g.p.box_h == 1 && T >= 4 && 128 % T == 0 && cg % 32 == 0 &&
          g.block_n % cg == 0 && g.p.bias != nullptr && g.block_k == 64;
 }
 

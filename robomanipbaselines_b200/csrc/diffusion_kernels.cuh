@@ -20,11 +20,13 @@ constexpr int kGnMaxVec = 16;      // float4 vectors a lane may hold: T * (C / 8
 constexpr int kXcolWidth = 64;     // im2col row of the UNet input: kernel_size * input_dim <= 64 columns (rest zero)
 
 __device__ __forceinline__ float mish_f(float x) {
-  // x * tanh(softplus(x)), softplus threshold 20 as torch; tanh(log(1+e)) = (e^2 + 2e) / (e^2 + 2e + 2)
-  if (x > 20.0f) return x;
-  const float e = __expf(x);
+  // x * tanh(softplus(x)) with tanh(log(1 + e)) = n / (n + 2), n = e * (e + 2), e = exp(x). Branch-free: the exponent is
+  // clamped at 20 (torch's softplus threshold), where n / (n + 2) already rounds to 1 in fp32, so x > 20 returns x.
+  float e, rc;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(fminf(x, 20.0f) * 1.4426950408889634f));
   const float n = e * (e + 2.0f);
-  return x * __fdividef(n, n + 2.0f);
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rc) : "f"(n + 2.0f));
+  return x * (n * rc);
 }
 
 __device__ __forceinline__ float warp_sum(float v) {

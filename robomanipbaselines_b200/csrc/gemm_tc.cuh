@@ -178,13 +178,13 @@ __device__ __forceinline__ void gemm_epilogue(const GemmParams& p, uint8_t* smem
   }
 }
 
-template <int BLOCK_N>
+template <int BLOCK_N, bool FILM>
 __device__ __forceinline__ void gemm_gn_epilogue(const GemmParams& p, uint8_t* smem_stage, uint32_t tmem_base,
                                                  uint64_t* tmem_full_bar, uint64_t* tmem_empty_bar, int total_tiles,
                                                  int warp, int lane);
 
 // OUT_F32: fp32 output (else act_t). RES: 0 no residual, 1 act_t residual, 2 fp32 residual.
-// EPI: 0 plain epilogue (bias / residual / ReLU), 1 fused GroupNorm + Mish + FiLM + residual (gemm_gn.cuh).
+// EPI: 0 plain epilogue (bias / residual / ReLU); fused GroupNorm + Mish (gemm_gn.cuh) followed by 1: FiLM, 2: residual.
 template <int BLOCK_N, int BLOCK_K, int STAGES, bool OUT_F32, int RES, int EPI = 0>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
@@ -293,8 +293,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
   } else {
-    if constexpr (EPI == 1)
-      gemm_gn_epilogue<BLOCK_N>(p, smem_stage, tmem_base, tmem_full_bar, tmem_empty_bar, total_tiles, warp, lane);
+    if constexpr (EPI != 0)
+      gemm_gn_epilogue<BLOCK_N, EPI == 1>(p, smem_stage, tmem_base, tmem_full_bar, tmem_empty_bar, total_tiles, warp, lane);
     else
       gemm_epilogue<BLOCK_N, OUT_F32, RES>(p, smem_stage, tmem_base, tmem_full_bar, tmem_empty_bar, total_tiles, warp, lane);
   }
