@@ -97,6 +97,9 @@ class DiffusionPolicyBase(nn.Module):
         self.max_batch = max_batch
         self._unet = None
         self._steps = None
+        # the scheduler loop is thousands of small launches: replay it as ONE CUDA graph (captured per batch size)
+        self.use_cuda_graph = True
+        self._graphs = {}
 
     def load_state_dict(self, state_dict, strict=True, **kw):
         out = super().load_state_dict(state_dict, strict=strict, **kw)
@@ -104,6 +107,7 @@ class DiffusionPolicyBase(nn.Module):
         return out
 
     def _invalidate(self):
+        self._graphs = {}
         if self._unet is not None:
             self._unet.close()
         self._unet = None
@@ -138,8 +142,35 @@ class DiffusionPolicyBase(nn.Module):
         if step_noise is None and self.noise_scheduler.kind == 0:
             step_noise = torch.randn(len(steps), B, self.horizon, self.action_dim, device=dev, dtype=torch.float32,
                                      generator=generator)
-        return self.unet_for(B, dev).denoise(global_cond.contiguous(), x_init.contiguous(), steps, noise=step_noise,
-                                             out=out)
+        unet = self.unet_for(B, dev)
+        if not self.use_cuda_graph:
+            return unet.denoise(global_cond.contiguous(), x_init.contiguous(), steps, noise=step_noise, out=out)
+        key = (B, dev.index, len(steps), id(unet))
+        g = self._graphs.get(key)
+        if g is None:
+            st = {"gc": torch.empty_like(global_cond, memory_format=torch.contiguous_format),
+                  "x": torch.empty_like(x_init, memory_format=torch.contiguous_format),
+                  "noise": None if step_noise is None else torch.empty_like(step_noise, memory_format=torch.contiguous_format)}
+            st["out"] = torch.empty_like(st["x"])
+            st["gc"].copy_(global_cond); st["x"].copy_(x_init)
+            if step_noise is not None:
+                st["noise"].copy_(step_noise)
+            unet.denoise(st["gc"], st["x"], steps, noise=st["noise"], out=st["out"])    # warm-up: plans, func attributes
+            torch.cuda.synchronize(dev)
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                unet.denoise(st["gc"], st["x"], steps, noise=st["noise"], out=st["out"])
+            st["graph"] = graph
+            self._graphs = {key: st}                # one live graph (it pins the engine's workspace addresses)
+            g = st
+        g["gc"].copy_(global_cond); g["x"].copy_(x_init)
+        if step_noise is not None:
+            g["noise"].copy_(step_noise)
+        g["graph"].replay()
+        if out is not None:
+            out.copy_(g["out"])
+            return out
+        return g["out"].clone()
 
     def encode_obs(self, obs_dict):
         raise NotImplementedError

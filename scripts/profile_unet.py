@@ -90,6 +90,20 @@ def main():
     ms = e0.elapsed_time(e1) / reps
     print(f"{args.kind}-{len(steps)} loop at B={B}: {ms:.2f} ms per inference batch -> {B / ms * 1e3:.0f} inferences/s, "
           f"{8 * B / ms * 1e3:.0f} policy steps/s (n_action_steps 8); {eng.step_flops(B) * len(steps) / ms / 1e9:.1f} TFLOP/s")
+    # the same loop replayed as one CUDA graph (what DiffusionPolicyBase.conditional_sample does)
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        eng.denoise(gc, x, steps, noise=noise, out=out)
+    graph.replay()
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(reps):
+        graph.replay()
+    e1.record()
+    torch.cuda.synchronize()
+    msg = e0.elapsed_time(e1) / reps
+    print(f"  as one CUDA graph: {msg:.2f} ms -> {B / msg * 1e3:.0f} inferences/s, {8 * B / msg * 1e3:.0f} policy steps/s; "
+          f"{eng.step_flops(B) * len(steps) / msg / 1e9:.1f} TFLOP/s")
     if args.out:
         with open(args.out, "w") as f:
             json.dump({"batch": B, "total_ms": total, "loop_ms": ms, "launches": recs}, f, indent=1)
