@@ -192,6 +192,66 @@ def bench_diffusion(device, reps=2):
     return out
 
 
+def bench_micro(device):
+    """Stand-alone HBM micro-benchmarks of the two elementwise kernels that are too small to time inside a step
+    (SURVEY 8d): the scheduler step over 2^26 elements and the ensembling ring buffer over 65 536 episodes."""
+    import ctypes
+
+    from robomanipbaselines_b200 import _lib
+    from robomanipbaselines_b200._lib import check, cur_stream, ptr
+    from robomanipbaselines_b200.common.ensemble import make_weight_table
+    from robomanipbaselines_b200.common.schedulers import DDPMScheduler
+
+    lib = _lib.load()
+    peak = measured_peaks()["hbm_gbs"]
+    out = {}
+
+    def timed(fn, reps):
+        fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / reps
+
+    n = 1 << 26
+    x, o, z, y = (torch.randn(n, device=device) for _ in range(4))
+    st = DDPMScheduler(num_train_timesteps=100, beta_schedule="squaredcos_cap_v2").step_table(100)[40]
+    ms = timed(lambda: check(lib.rmb_scheduler_step(ptr(x), ptr(o), ptr(z), ctypes.byref(st), ptr(y), n, cur_stream()), "rmb_scheduler_step"), 10)
+    gbs = 16.0 * n / ms / 1e6
+    out["scheduler_step"] = {"kernel": "sched_step_kernel", "elements": n, "algorithmic_bytes": 16 * n, "ms": ms,
+                             "achieved_gbs": gbs, "peak_gbs": peak, "frac": gbs / peak,
+                             "what": "DDPM step t=59 (x, model output, noise in; x' out), 4 x 256 MB arrays >> L2"}
+    del x, o, z, y
+    B, C, Da = 65536, CHUNK, DA
+    ring = torch.zeros(B, C, C, Da, device=device)
+    chunks = torch.randn(B, C, Da, device=device)
+    step = torch.zeros(B, device=device, dtype=torch.int32)
+    wtab = torch.from_numpy(make_weight_table(C)).to(device)
+    p0, p1 = torch.ones(Da, device=device, dtype=torch.float64), torch.zeros(Da, device=device, dtype=torch.float64)
+    act = torch.empty(B, Da, device=device, dtype=torch.float64)
+
+    def ens():
+        check(lib.rmb_ensemble_step(ptr(ring), ptr(chunks), ptr(step), None, ptr(wtab), 0, ptr(p0), ptr(p1), 0.0,
+                                    ptr(act), None, None, B, C, Da, cur_stream()), "rmb_ensemble_step")
+
+    for _ in range(C):                       # fill the ring: every later call gathers the full 100-entry diagonal
+        ens()
+    ms = timed(ens, 10)
+    per_ep = 3 * C * Da * 4 + Da * 8         # chunk in + ring slot write + diagonal gather + action out
+    gbs = per_ep * B / ms / 1e6
+    out["ensemble_step"] = {"kernel": "ensemble_step_kernel", "episodes": B, "algorithmic_bytes": per_ep * B, "ms": ms,
+                            "achieved_gbs": gbs, "peak_gbs": peak, "frac": gbs / peak,
+                            "what": "temporal ensembling with a full 100-chunk history per episode, 18 GB ring buffer; "
+                                    "the diagonal gather touches one 28-byte row per 2.8 KB slot (sector-granular reads)"}
+    del ring, chunks
+    torch.cuda.empty_cache()
+    return out
+
+
 def cpu_reference_step(sd, meta, oracles, images_u8, raw_state, live_only):
     """One policy step of the reference path for len(oracles) episodes on the CPU (oracle port, fp32 PyTorch + numpy)."""
     from oracle import act_oracle, rollout_oracle
@@ -283,12 +343,12 @@ def main():
     gen = torch.Generator(device=device).manual_seed(1 + rank)
     imgs = [torch.randint(0, 256, (B, NCAM, IMG_H, IMG_W, 3), generator=gen, device=device, dtype=torch.uint8) for _ in range(2)]
     states = [torch.randn(B, DS, generator=gen, device=device, dtype=torch.float64) for _ in range(2)]
-    gathered = torch.empty(world * B, DA, device=device, dtype=torch.float64) if world > 1 else None
+    from robomanipbaselines_b200.common.sharding import gather_episodes
 
     def step(i):
         act = br.infer(imgs[i & 1], states[i & 1])
-        if world > 1:   # north_star: every rank sees all episodes' actions (KB-sized all-gather over NVLink)
-            dist.all_gather_into_tensor(gathered, act)
+        if world > 1:   # north_star: every rank sees all episodes' actions (KB-sized NCCL all-gather over NVLink)
+            act = gather_episodes(act, world * B)
         return act
 
     def barrier():
@@ -337,7 +397,7 @@ def main():
             act = br.infer(d_imgs[j], d_states[j])
             consumed[j].record(main_stream)
             if world > 1:
-                dist.all_gather_into_tensor(gathered, act)
+                gather_episodes(act, world * B)
             h_act.copy_(act, non_blocking=True)
 
     e2e_run(2)
@@ -425,6 +485,7 @@ def main():
             pol._invalidate()
             torch.cuda.empty_cache()
             line["other_configs"] = bench_diffusion(device)
+            line["microbench"] = bench_micro(device)
         if world == 1 and not args.no_cpu_baseline:
             sample = 4
             times, cores = time_cpu_baseline(sample, 4, 1, live_only=False)

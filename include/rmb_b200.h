@@ -181,6 +181,11 @@ typedef struct rmb_sched_step {
   float sigma;          /* DDPM sqrt(variance) (0 at t = 0) */
 } rmb_sched_step_t;
 
+/* One DDPMScheduler.step / DDIMScheduler.step over n float32 elements, stand-alone (the fused form runs inside
+ * rmb_unet1d_denoise): d_out[i] = step(d_x[i], d_model_out[i], d_noise[i]); d_noise may be NULL when sigma == 0. */
+int rmb_scheduler_step(const float* d_x, const float* d_model_out, const float* d_noise, const rmb_sched_step_t* step,
+                       float* d_out, int64_t n, void* stream);
+
 int rmb_unet_engine_create(const rmb_unet_config_t* cfg, rmb_unet_engine_t** out);
 void rmb_unet_engine_destroy(rmb_unet_engine_t* e);
 /* ConditionalUnet1D state-dict tensor (key relative to the module, e.g. "down_modules.0.0.blocks.0.block.0.weight"),

@@ -609,6 +609,20 @@ double rmb_unet_step_flops(const rmb_unet_engine_t* e, int batch) {
   return f * batch;
 }
 
+int rmb_scheduler_step(const float* d_x, const float* d_model_out, const float* d_noise, const rmb_sched_step_t* step,
+                       float* d_out, int64_t n, void* stream_) {
+  if (!d_x || !d_model_out || !step || !d_out || n < 0) return fail("rmb_scheduler_step: null argument");
+  if (step->kind != 0 && step->kind != 1) return fail("rmb_scheduler_step: scheduler kind must be 0 (DDPM) or 1 (DDIM)");
+  if (step->kind == 0 && step->sigma > 0.f && !d_noise) return fail("rmb_scheduler_step: sigma > 0 needs d_noise");
+  if (n == 0) return 0;
+  SchedStep st;
+  st.kind = step->kind; st.pred_sample = step->pred_sample; st.clip = step->clip; st.derive_eps = step->derive_eps;
+  st.s_beta = step->s_beta; st.s_alpha = step->s_alpha; st.c_x0 = step->c_x0; st.c_xt = step->c_xt; st.sigma = step->sigma;
+  sched_step_kernel<<<grid_for((n + 3) / 4, 256, 148), 256, 0, static_cast<cudaStream_t>(stream_)>>>(d_x, d_model_out, d_noise, d_out, n, st);
+  RMB_CUDA(cudaGetLastError());
+  return 0;
+}
+
 int rmb_unet1d_denoise(rmb_unet_engine_t* e, const float* d_global_cond, const float* d_x_init, const float* d_noise,
                        const rmb_sched_step_t* steps, int n_steps, float* d_x_out, int batch, void* stream_) {
   if (int r = unet_check(e, batch, "rmb_unet1d_denoise")) return r;

@@ -160,6 +160,25 @@ __device__ __forceinline__ float sched_step(const SchedStep& s, float x, float o
   return __fadd_rn(__fmul_rn(s.c_x0, x0), __fmul_rn(s.c_xt, dir));
 }
 
+// Stand-alone scheduler step over n elements (the same sched_step() the fused kernel applies): used by the bit-exact
+// parity test against the oracle and by the HBM micro-benchmark (3 reads + 1 write of 4 B per element).
+__global__ void __launch_bounds__(256) sched_step_kernel(const float* __restrict__ x, const float* __restrict__ model_out,
+                                                         const float* __restrict__ noise, float* __restrict__ out,
+                                                         long long n, const SchedStep st) {
+  const long long n4 = n >> 2;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n4;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const float4 a = __ldg(reinterpret_cast<const float4*>(x) + i), o = __ldg(reinterpret_cast<const float4*>(model_out) + i);
+    const float4 z = noise ? __ldg(reinterpret_cast<const float4*>(noise) + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+    reinterpret_cast<float4*>(out)[i] = make_float4(sched_step(st, a.x, o.x, z.x), sched_step(st, a.y, o.y, z.y),
+                                                    sched_step(st, a.z, o.z, z.z), sched_step(st, a.w, o.w, z.w));
+  }
+  if (blockIdx.x == 0 && threadIdx.x < (n & 3)) {
+    const long long i = (n4 << 2) + threadIdx.x;
+    out[i] = sched_step(st, x[i], model_out[i], noise ? noise[i] : 0.f);
+  }
+}
+
 // dynamic smem: T*C floats (normalised activations) + T*Da floats (new x)
 __global__ void __launch_bounds__(256) unet_final_step_kernel(const FinalParams p) {
   extern __shared__ float fs_smem[];

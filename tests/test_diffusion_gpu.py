@@ -278,3 +278,31 @@ def test_unet_forward_unfused_groupnorm(cuda, monkeypatch):
           f"launches {eng_fused.launches_per_step} vs {eng_plain.launches_per_step}")
     assert eng_fused.launches_per_step < eng_plain.launches_per_step
     assert (a - want).abs().max().item() <= 1e-2 and (b - want).abs().max().item() <= 1e-2
+
+
+@pytest.mark.parametrize("kind", ["ddpm", "ddim", "ddim_derive"])
+def test_scheduler_step_kernel_bit_exact(cuda, lib, kind):
+    """The device scheduler step (same sched_step() the fused kernel applies) against the oracle: bit-exact in fp32."""
+    import ctypes
+
+    from robomanipbaselines_b200._lib import check, cur_stream, ptr
+
+    if kind == "ddpm":
+        mine, orc = DDPMScheduler(**SCHED, prediction_type="epsilon"), dor.DDPMSchedulerOracle(**SCHED)
+        n_steps = 100
+    else:
+        d = kind == "ddim_derive"
+        mine = DDIMScheduler(**SCHED, prediction_type="sample", derive_epsilon=d)
+        orc = dor.DDIMSchedulerOracle(**SCHED, prediction_type="sample", derive_epsilon=d)
+        n_steps = 16
+    steps = mine.step_table(n_steps)
+    orc.set_timesteps(n_steps)
+    g = torch.Generator().manual_seed(21)
+    n = 4 * 16 * 7 + 3                                        # not a multiple of 4: exercises the tail
+    x, out, nz = torch.randn(n, generator=g), torch.randn(n, generator=g) * 2, torch.randn(n, generator=g)
+    dx, do, dn, dy = x.to(cuda), out.to(cuda), nz.to(cuda), torch.empty(n, device=cuda)
+    for i in (0, 1, len(steps) // 2, len(steps) - 1):
+        s = steps[i]
+        check(lib.rmb_scheduler_step(ptr(dx), ptr(do), ptr(dn), ctypes.byref(s), ptr(dy), n, cur_stream()), "rmb_scheduler_step")
+        want = orc.step(out, s.t, x, nz)
+        assert torch.equal(dy.cpu(), want), (kind, s.t)
