@@ -757,7 +757,9 @@ int rmb_ensemble_step(float* d_ring, const float* d_chunks, int32_t* d_step, con
   if (batch < 1 || C < 1 || Da < 1 || Da > 128) return fail("rmb_ensemble_step: bad sizes");
   if (norm_type != 0 && norm_type != 1) return fail("rmb_ensemble_step: norm_type must be 0 (gaussian) or 1 (limits)");
   DenormParams dn{d_p0, d_p1, out_min, norm_type};
-  ensemble_step_kernel<<<batch, 128, 0, static_cast<cudaStream_t>(stream_)>>>(d_ring, d_chunks, d_step, d_reset, d_wtab, dn, d_action, d_action_f32, d_action_norm, C, Da);
+  const size_t diag_bytes = static_cast<size_t>(C) * Da * sizeof(float);
+  const int use_smem = diag_bytes <= 48 * 1024 ? 1 : 0;
+  ensemble_step_kernel<<<batch, 128, use_smem ? diag_bytes : 0, static_cast<cudaStream_t>(stream_)>>>(d_ring, d_chunks, d_step, d_reset, d_wtab, dn, d_action, d_action_f32, d_action_norm, C, Da, use_smem);
   RMB_CUDA(cudaGetLastError());
   return 0;
 }

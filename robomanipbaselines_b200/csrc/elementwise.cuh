@@ -282,7 +282,7 @@ __global__ void ensemble_step_kernel(float* __restrict__ ring, const float* __re
                                      int32_t* __restrict__ step, const uint8_t* __restrict__ reset,
                                      const double* __restrict__ wtab, DenormParams dn, double* __restrict__ action_out,
                                      float* __restrict__ action_out_f32, double* __restrict__ action_norm_out, int C,
-                                     int Da) {
+                                     int Da, int use_smem) {
   const int b = blockIdx.x;
   int n = step[b];
   if (reset != nullptr && reset[b]) n = 0;
@@ -292,15 +292,32 @@ __global__ void ensemble_step_kernel(float* __restrict__ ring, const float* __re
   for (int i = threadIdx.x; i < C * Da; i += blockDim.x) ring_b[static_cast<long long>(slot) * C * Da + i] = chunk_b[i];
   __syncthreads();
   const int m = n + 1 < C ? n + 1 : C;
+  // stage the diagonal A[n-i][i] (i < m) in shared memory with all threads (m independent 28-byte gathers in flight at
+  // once instead of m dependent ones); the fp64 sum below keeps the reference's order
+  extern __shared__ float ens_diag[];
+  if (use_smem) {
+    for (int idx = threadIdx.x; idx < m * Da; idx += blockDim.x) {
+      const int i = idx / Da, d = idx - i * Da;
+      int s = (n - i) % C;
+      if (s < 0) s += C;
+      ens_diag[idx] = ring_b[(static_cast<long long>(s) * C + i) * Da + d];
+    }
+    __syncthreads();
+  }
   if (threadIdx.x < Da) {
     const int d = threadIdx.x;
     const double* w = wtab + static_cast<long long>(m - 1) * C;
     double acc = 0.0;
     for (int i = 0; i < m; ++i) {
-      int s = (n - i) % C;
-      if (s < 0) s += C;
-      const double a = static_cast<double>(ring_b[(static_cast<long long>(s) * C + i) * Da + d]);
-      acc = __dadd_rn(acc, __dmul_rn(w[m - 1 - i], a));
+      float av;
+      if (use_smem) {
+        av = ens_diag[i * Da + d];
+      } else {
+        int s = (n - i) % C;
+        if (s < 0) s += C;
+        av = ring_b[(static_cast<long long>(s) * C + i) * Da + d];
+      }
+      acc = __dadd_rn(acc, __dmul_rn(w[m - 1 - i], static_cast<double>(av)));
     }
     double o;
     if (dn.type == 0) o = __dadd_rn(__dmul_rn(dn.a[d], acc), dn.b[d]);
