@@ -255,6 +255,27 @@ int rmb_imgenc_encode(rmb_imgenc_engine_t* e, const float* d_images, float* d_ou
 int64_t rmb_imgenc_debug_read(rmb_imgenc_engine_t* e, float* d_out, int n_images, void* stream);
 double rmb_imgenc_flops(const rmb_imgenc_engine_t* e, int n_images);
 
+/* ---- DP3 observation pipeline on the device (the step before DP3.predict_action):
+ * convert_depth_image_to_pointcloud (common/utils/VisionUtils.py:55-87) -> crop_pointcloud_bb + downsample_pointcloud_fps
+ * (common/utils/Vision3dUtils.py:6-25) -> normalize_data + float32 cast (RolloutDiffusionPolicy3d.py:152-153), for
+ * `batch` already-resized camera frames at once. fp64 arithmetic in the reference's op order (bit-exact). */
+typedef struct rmb_pointcloud_params {
+  int32_t H, W;              /* data["image_size"] after cv2.resize (RolloutDiffusionPolicy3d.py:134-137) */
+  int32_t num_points;        /* data["num_points"] */
+  double focal_scaling;      /* (1 / tan(deg2rad(fovy) / 2)) * H / 2, made on the host with numpy (VisionUtils.py:59) */
+  double near_clip, far_clip;          /* 0, +inf */
+  int32_t has_min_bound, has_max_bound;
+  double min_bound[3], max_bound[3];
+  int32_t norm_type;         /* -1 none, 0 gaussian: (x - p0)/p1 (mean, std), 1 limits: p1*(x - p0) + out_min (min, scale) */
+  double norm_p0[6], norm_p1[6], norm_out_min;
+} rmb_pointcloud_params_t;
+int64_t rmb_pointcloud_scratch_bytes(int batch, int H, int W, int num_points);
+/* d_depth float32 [batch, H, W]; d_rgb uint8 [batch, H, W, 3]; d_out float32 [batch, num_points, 6] (xyz, rgb/255);
+ * d_count int32 [batch] (points that survived clip + crop) or NULL; d_indices int32 [batch, num_points] (FPS indices
+ * into the cropped cloud, -1 padded) or NULL. */
+int rmb_pointcloud_from_depth(const float* d_depth, const uint8_t* d_rgb, const rmb_pointcloud_params_t* p, void* d_scratch,
+                              float* d_out, int32_t* d_count, int32_t* d_indices, int batch, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -70,6 +70,17 @@ class ImgEncConfig(ctypes.Structure):
     ]
 
 
+class PointcloudParams(ctypes.Structure):
+    """Mirror of rmb_pointcloud_params_t."""
+
+    _fields_ = [
+        ("H", c_int32), ("W", c_int32), ("num_points", c_int32), ("focal_scaling", c_double), ("near_clip", c_double),
+        ("far_clip", c_double), ("has_min_bound", c_int32), ("has_max_bound", c_int32), ("min_bound", c_double * 3),
+        ("max_bound", c_double * 3), ("norm_type", c_int32), ("norm_p0", c_double * 6), ("norm_p1", c_double * 6),
+        ("norm_out_min", c_double),
+    ]
+
+
 # name -> (restype, argtypes); must list every symbol include/rmb_b200.h declares (tests check this)
 SIGNATURES = {
     "rmb_last_error": (c_char_p, []),
@@ -127,6 +138,9 @@ SIGNATURES = {
     "rmb_imgenc_encode": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p]),
     "rmb_imgenc_debug_read": (c_int64, [c_void_p, c_void_p, c_int, c_void_p]),
     "rmb_imgenc_flops": (c_double, [c_void_p, c_int]),
+    "rmb_pointcloud_scratch_bytes": (c_int64, [c_int, c_int, c_int, c_int]),
+    "rmb_pointcloud_from_depth": (c_int, [c_void_p, c_void_p, POINTER(PointcloudParams), c_void_p, c_void_p, c_void_p,
+                                          c_void_p, c_int, c_void_p]),
 }
 
 _lib = None

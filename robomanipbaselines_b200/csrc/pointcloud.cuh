@@ -1,0 +1,170 @@
+// Device-side DP3 observation pipeline: the step immediately before DP3.predict_action.
+//   convert_depth_image_to_pointcloud  robo_manip_baselines/common/utils/VisionUtils.py:55-87
+//   crop_pointcloud_bb                 robo_manip_baselines/common/utils/Vision3dUtils.py:6-14
+//   downsample_pointcloud_fps          robo_manip_baselines/common/utils/Vision3dUtils.py:17-25 (pytorch3d FPS, start index 0)
+//   normalize_data + float32 cast      policy/diffusion_policy_3d/RolloutDiffusionPolicy3d.py:152-153
+// One CTA per cloud. Arithmetic is fp64 with the reference's dtype flow and op order (see oracle/pointcloud_oracle.py):
+// separately rounded multiplies / adds, so back-projection, crop, FPS indices and the normalised float32 output are
+// bit-exact with the numpy path. Included at the end of act_engine.cu.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace rmb {
+
+constexpr int kPcThreads = 512;
+
+struct PcParams {
+  int H, W, K;
+  double focal, near_clip, far_clip;
+  int has_min, has_max;
+  double mn[3], mx[3];
+  int norm_type;            // -1 none, 0 gaussian ((x - p0) / p1), 1 limits (p1 * (x - p0) + out_min)
+  double p0[6], p1[6], out_min;
+};
+
+// scratch per cloud: pts [HW][6] double, mind [HW] double
+__global__ void __launch_bounds__(kPcThreads) pointcloud_from_depth_kernel(const float* __restrict__ depth,
+                                                                           const uint8_t* __restrict__ rgb,
+                                                                           const PcParams p, double* __restrict__ scratch,
+                                                                           float* __restrict__ out, int* __restrict__ count,
+                                                                           int* __restrict__ indices) {
+  __shared__ int warp_cnt[kPcThreads / 32];
+  __shared__ int s_base, s_sel;
+  __shared__ double red_v[kPcThreads / 32];
+  __shared__ int red_i[kPcThreads / 32];
+  __shared__ double sel_pt[6];
+  const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int HW = p.H * p.W;
+  double* pts = scratch + static_cast<long long>(b) * HW * 7;
+  double* mind = pts + static_cast<long long>(HW) * 6;
+  const float* dep = depth + static_cast<long long>(b) * HW;
+  const uint8_t* col = rgb + static_cast<long long>(b) * HW * 3;
+  if (tid == 0) s_base = 0;
+  __syncthreads();
+  // ---- back-projection + clip + bounding box, stable compaction in pixel order
+  const float half_h = 0.5f * static_cast<float>(p.H), half_w = 0.5f * static_cast<float>(p.W);
+  for (int start = 0; start < HW; start += kPcThreads) {
+    const int pix = start + tid;
+    bool keep = false;
+    double x = 0, y = 0, z = 0;
+    if (pix < HW) {
+      const int i = pix / p.W, j = pix - i * p.W;
+      const float dz = dep[pix];
+      z = static_cast<double>(dz);
+      // ((float(j) - 0.5*W) / focal) * depth : float32 grid, float64 from the division on (VisionUtils.py:60-71)
+      x = __dmul_rn(__ddiv_rn(static_cast<double>(static_cast<float>(j) - half_w), p.focal), z);
+      y = __dmul_rn(__ddiv_rn(static_cast<double>(static_cast<float>(i) - half_h), p.focal), z);
+      keep = (p.near_clip < z) && (z < p.far_clip);
+      if (p.has_min) keep = keep && x > p.mn[0] && y > p.mn[1] && z > p.mn[2];
+      if (p.has_max) keep = keep && x < p.mx[0] && y < p.mx[1] && z < p.mx[2];
+    }
+    const unsigned bal = __ballot_sync(0xffffffffu, keep);
+    if (lane == 0) warp_cnt[warp] = __popc(bal);
+    __syncthreads();
+    int off = s_base;
+    for (int w2 = 0; w2 < warp; ++w2) off += warp_cnt[w2];
+    if (keep) {
+      double* q = pts + static_cast<long long>(off + __popc(bal & ((1u << lane) - 1u))) * 6;
+      q[0] = x; q[1] = y; q[2] = z;
+      q[3] = static_cast<double>(__fdiv_rn(static_cast<float>(col[pix * 3 + 0]), 255.0f));
+      q[4] = static_cast<double>(__fdiv_rn(static_cast<float>(col[pix * 3 + 1]), 255.0f));
+      q[5] = static_cast<double>(__fdiv_rn(static_cast<float>(col[pix * 3 + 2]), 255.0f));
+    }
+    __syncthreads();
+    if (tid == 0) {
+      int tot = 0;
+      for (int w2 = 0; w2 < kPcThreads / 32; ++w2) tot += warp_cnt[w2];
+      s_base += tot;
+    }
+    __syncthreads();
+  }
+  const int N = s_base;
+  if (tid == 0 && count != nullptr) count[b] = N;
+  int* idx_out = indices + static_cast<long long>(b) * p.K;
+  // ---- farthest point sampling on the 6-D points (the reference passes xyz and rgb columns)
+  for (int i = tid; i < N; i += kPcThreads) mind[i] = INFINITY;
+  for (int k = tid; k < p.K; k += kPcThreads) idx_out[k] = (k == 0 && N > 0) ? 0 : -1;
+  if (tid == 0) s_sel = 0;
+  __syncthreads();
+  const int kmax = p.K < N ? p.K : N;
+  for (int k = 1; k < kmax; ++k) {
+    if (tid < 6) sel_pt[tid] = pts[static_cast<long long>(s_sel) * 6 + tid];
+    __syncthreads();
+    double best = -1.0; int best_i = 0x7fffffff;
+    for (int i = tid; i < N; i += kPcThreads) {
+      const double* q = pts + static_cast<long long>(i) * 6;
+      double d2 = 0.0;
+#pragma unroll
+      for (int d = 0; d < 6; ++d) {
+        const double df = __dsub_rn(q[d], sel_pt[d]);
+        d2 = __dadd_rn(d2, __dmul_rn(df, df));
+      }
+      const double m = fmin(mind[i], d2);
+      mind[i] = m;
+      if (m > best) { best = m; best_i = i; }              // ascending i per thread: strict > keeps the first
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const double ov = __shfl_xor_sync(0xffffffffu, best, o);
+      const int oi = __shfl_xor_sync(0xffffffffu, best_i, o);
+      if (ov > best || (ov == best && oi < best_i)) { best = ov; best_i = oi; }
+    }
+    if (lane == 0) { red_v[warp] = best; red_i[warp] = best_i; }
+    __syncthreads();
+    if (tid == 0) {
+      double bv = red_v[0]; int bi = red_i[0];
+      for (int w2 = 1; w2 < kPcThreads / 32; ++w2)
+        if (red_v[w2] > bv || (red_v[w2] == bv && red_i[w2] < bi)) { bv = red_v[w2]; bi = red_i[w2]; }
+      s_sel = bi;
+      idx_out[k] = bi;
+    }
+    __syncthreads();
+  }
+  __syncthreads();
+  // ---- gather (-1 picks the last point, as numpy indexing does), normalise in fp64, cast to float32
+  for (int e = tid; e < p.K * 6; e += kPcThreads) {
+    const int k = e / 6, d = e - k * 6;
+    float v = 0.f;
+    if (N > 0) {
+      int src = idx_out[k];
+      if (src < 0) src = N - 1;
+      double a = pts[static_cast<long long>(src) * 6 + d];
+      if (p.norm_type == 0) a = __ddiv_rn(__dsub_rn(a, p.p0[d]), p.p1[d]);
+      else if (p.norm_type == 1) a = __dadd_rn(__dmul_rn(p.p1[d], __dsub_rn(a, p.p0[d])), p.out_min);
+      v = static_cast<float>(a);
+    }
+    out[(static_cast<long long>(b) * p.K + k) * 6 + d] = v;
+  }
+}
+
+}  // namespace rmb
+
+extern "C" {
+
+int64_t rmb_pointcloud_scratch_bytes(int batch, int H, int W, int num_points) {
+  if (batch < 1 || H < 1 || W < 1 || num_points < 1) return fail("rmb_pointcloud_scratch_bytes: bad sizes");
+  return static_cast<int64_t>(batch) * H * W * 7 * sizeof(double) + static_cast<int64_t>(batch) * num_points * sizeof(int);
+}
+
+int rmb_pointcloud_from_depth(const float* d_depth, const uint8_t* d_rgb, const rmb_pointcloud_params_t* prm, void* d_scratch,
+                              float* d_out, int32_t* d_count, int32_t* d_indices, int batch, void* stream_) {
+  if (!d_depth || !d_rgb || !prm || !d_scratch || !d_out) return fail("rmb_pointcloud_from_depth: null argument");
+  if (batch < 1 || prm->H < 1 || prm->W < 1 || prm->num_points < 1) return fail("rmb_pointcloud_from_depth: bad sizes");
+  if (prm->norm_type < -1 || prm->norm_type > 1) return fail("rmb_pointcloud_from_depth: norm_type must be -1, 0 or 1");
+  if (!(prm->focal_scaling > 0.0)) return fail("rmb_pointcloud_from_depth: focal_scaling must be positive");
+  rmb::PcParams p;
+  p.H = prm->H; p.W = prm->W; p.K = prm->num_points;
+  p.focal = prm->focal_scaling; p.near_clip = prm->near_clip; p.far_clip = prm->far_clip;
+  p.has_min = prm->has_min_bound; p.has_max = prm->has_max_bound;
+  for (int i = 0; i < 3; ++i) { p.mn[i] = prm->min_bound[i]; p.mx[i] = prm->max_bound[i]; }
+  p.norm_type = prm->norm_type; p.out_min = prm->norm_out_min;
+  for (int i = 0; i < 6; ++i) { p.p0[i] = prm->norm_p0[i]; p.p1[i] = prm->norm_p1[i]; }
+  double* scratch = static_cast<double*>(d_scratch);
+  int* idx = d_indices ? d_indices : reinterpret_cast<int*>(scratch + static_cast<long long>(batch) * p.H * p.W * 7);
+  rmb::pointcloud_from_depth_kernel<<<batch, rmb::kPcThreads, 0, static_cast<cudaStream_t>(stream_)>>>(d_depth, d_rgb, p, scratch, d_out, d_count, idx);
+  RMB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+}  // extern "C"

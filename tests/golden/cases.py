@@ -39,3 +39,24 @@ def act_inputs(case):
                 img[b, n, :, :, c] = 127 + 90 * np.sin(fx * xx + fy * yy + ph)
     img += rng.normal(0, 20, size=img.shape).astype(np.float32)
     return qpos, np.clip(img, 0, 255).astype(np.uint8)
+
+
+# ---- DP3 observation pipeline (depth image -> point cloud), see make_pointcloud_golden.py
+POINTCLOUD_CASES = {
+    "small": dict(H=12, W=16, fovy=45.0, seed=31, min_bound=[-0.5, -0.5, 0.4], max_bound=[0.5, 0.5, 1.5], holes=True),
+    "img84": dict(H=84, W=84, fovy=58.0, seed=32, min_bound=[-0.6, -0.6, 0.3], max_bound=[0.6, 0.6, 1.6], holes=False),
+}
+
+
+def pointcloud_inputs(case, batch=None):
+    """float32 depth (H, W) in metres (zeros = invalid pixels when `holes`) and uint8 rgb (H, W, 3); with `batch` a
+    leading batch dimension of independent draws."""
+    import numpy as np
+
+    rng = np.random.default_rng(case["seed"])
+    shape = (case["H"], case["W"]) if batch is None else (batch, case["H"], case["W"])
+    depth = rng.uniform(0.3, 2.0, shape).astype(np.float32)
+    if case.get("holes"):
+        depth[rng.uniform(size=shape) < 0.1] = 0.0
+    rgb = rng.integers(0, 256, shape + (3,), dtype=np.uint8)
+    return depth, rgb

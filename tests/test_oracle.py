@@ -84,3 +84,22 @@ def test_get_state_and_images_oracle():
     stats = {"mean": g["get_state_mean"], "std": g["get_state_std"], "norm_config": {"type": "gaussian"}}
     assert np.array_equal(rollout_oracle.get_state(g["get_state_raw"], stats), g["get_state_out"])
     assert np.array_equal(rollout_oracle.get_images(list(g["get_images_in"])), g["get_images_out"])
+
+
+@pytest.mark.parametrize("name", ["small", "img84"])
+def test_pointcloud_oracle_matches_reference_golden(name):
+    """oracle/pointcloud_oracle.py against the outputs of the reference's own VisionUtils / Vision3dUtils functions
+    (tests/golden/make_pointcloud_golden.py): bit for bit, including the float64 dtype flow."""
+    from cases import POINTCLOUD_CASES, pointcloud_inputs
+    from oracle import pointcloud_oracle as po
+
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "pointcloud_golden.npz"))
+    c = POINTCLOUD_CASES[name]
+    depth, rgb = pointcloud_inputs(c)
+    pc = np.concat(po.convert_depth_image_to_pointcloud(depth, c["fovy"], rgb), axis=1)
+    assert pc.dtype == g[name + "_pointcloud"].dtype and np.array_equal(pc, g[name + "_pointcloud"])
+    assert np.array_equal(po.crop_pointcloud_bb(pc, c["min_bound"], c["max_bound"]), g[name + "_cropped"])
+    idx = po.farthest_point_sampling(g[name + "_cropped"], 32)
+    assert idx[0] == 0 and len(set(idx.tolist())) == 32            # distinct points, start index 0
+    few = po.farthest_point_sampling(g[name + "_cropped"][:5], 8)
+    assert sorted(few[:5].tolist()) == [0, 1, 2, 3, 4] and (few[5:] == -1).all()

@@ -1,0 +1,56 @@
+"""GPU parity of the device-side DP3 observation pipeline (rmb_pointcloud_from_depth) against oracle/pointcloud_oracle.py,
+whose back-projection and crop are pinned on the reference's own functions (tests/golden/pointcloud_golden.npz):
+valid-point counts, FPS indices and the float32 output are bit-exact."""
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(HERE, "golden"))
+from cases import POINTCLOUD_CASES, pointcloud_inputs  # noqa: E402
+from oracle import pointcloud_oracle as po  # noqa: E402
+from robomanipbaselines_b200.common.synthetic import synthetic_norm_stats  # noqa: E402
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("name,K,norm", [("small", 32, None), ("small", 128, "gaussian"), ("img84", 256, "limits"),
+                                         ("img84", 1024, "gaussian")])
+def test_pointcloud_pipeline_bit_exact(cuda, name, K, norm):
+    from robomanipbaselines_b200.common.pointcloud import DepthToPointcloud
+
+    c = POINTCLOUD_CASES[name]
+    B = 3
+    depth, rgb = pointcloud_inputs(c, batch=B)
+    stats = synthetic_norm_stats(6, 9, norm) if norm else None
+    pipe = DepthToPointcloud(B, (c["W"], c["H"]), c["fovy"], K, c["min_bound"], c["max_bound"], stats, device=str(cuda))
+    got = pipe(torch.from_numpy(depth).to(cuda), torch.from_numpy(rgb).to(cuda)).cpu().numpy()
+    cnt, idx = pipe.count.cpu().numpy(), pipe.indices.cpu().numpy()
+    for b in range(B):
+        pc = np.concat(po.convert_depth_image_to_pointcloud(depth[b], c["fovy"], rgb[b]), axis=1)
+        pc = po.crop_pointcloud_bb(pc, c["min_bound"], c["max_bound"])
+        want_idx = po.farthest_point_sampling(pc, K)
+        want, n = po.get_pointcloud(depth[b], rgb[b], c["fovy"], c["min_bound"], c["max_bound"], K, stats)
+        assert cnt[b] == n == pc.shape[0]
+        assert np.array_equal(idx[b], want_idx), (name, b, np.flatnonzero(idx[b] != want_idx)[:5])
+        assert got[b].dtype == want.dtype and np.array_equal(got[b], want), (name, b)
+    print(f"[pointcloud {name} K={K} norm={norm}] valid points {cnt.tolist()}, output bit-exact")
+
+
+def test_pointcloud_matches_reference_golden_directly(cuda):
+    """The first frame of each case is the very input the reference functions were run on: device output rows must be
+    rows of the stored reference crop (float64 -> float32)."""
+    from robomanipbaselines_b200.common.pointcloud import DepthToPointcloud
+
+    g = np.load(os.path.join(HERE, "golden", "pointcloud_golden.npz"))
+    for name, c in POINTCLOUD_CASES.items():
+        depth, rgb = pointcloud_inputs(c)
+        pipe = DepthToPointcloud(1, (c["W"], c["H"]), c["fovy"], 64, c["min_bound"], c["max_bound"], None, device=str(cuda))
+        got = pipe(torch.from_numpy(depth[None]).to(cuda), torch.from_numpy(rgb[None]).to(cuda)).cpu().numpy()[0]
+        ref = g[name + "_cropped"]
+        assert int(pipe.count[0]) == ref.shape[0]
+        idx = pipe.indices.cpu().numpy()[0]
+        assert np.array_equal(got, ref[idx].astype(np.float32))
