@@ -276,6 +276,14 @@ int64_t rmb_pointcloud_scratch_bytes(int batch, int H, int W, int num_points);
 int rmb_pointcloud_from_depth(const float* d_depth, const uint8_t* d_rgb, const rmb_pointcloud_params_t* p, void* d_scratch,
                               float* d_out, int32_t* d_count, int32_t* d_indices, int batch, void* stream);
 
+/* ---- cv2.resize(img, (W2, H2)) with INTER_LINEAR on the device (RolloutDiffusionPolicy.py:117,
+ * RolloutDiffusionPolicy3d.py:134-137). uint8: OpenCV's fixed-point path, bit-exact for the reference's down-scaling;
+ * out_mode 0 = uint8 HWC [n, H2, W2, 3]; out_mode 1 = float32 CHW [n, 3, H2, W2] = (v * (1/255)) * scale + offset
+ * (scale 2, offset -1 is the Diffusion Policy input, RolloutDiffusionPolicy.py:119-123). float32: single-channel depth. */
+int rmb_resize_u8_bilinear(const uint8_t* d_src, int n, int H, int W, int H2, int W2, int out_mode, float scale,
+                           float offset, void* d_dst, void* stream);
+int rmb_resize_f32_bilinear(const float* d_src, int n, int H, int W, int H2, int W2, float* d_dst, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -138,6 +138,9 @@ SIGNATURES = {
     "rmb_imgenc_encode": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p]),
     "rmb_imgenc_debug_read": (c_int64, [c_void_p, c_void_p, c_int, c_void_p]),
     "rmb_imgenc_flops": (c_double, [c_void_p, c_int]),
+    "rmb_resize_u8_bilinear": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_float, c_float, c_void_p,
+                                       c_void_p]),
+    "rmb_resize_f32_bilinear": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
     "rmb_pointcloud_scratch_bytes": (c_int64, [c_int, c_int, c_int, c_int]),
     "rmb_pointcloud_from_depth": (c_int, [c_void_p, c_void_p, POINTER(PointcloudParams), c_void_p, c_void_p, c_void_p,
                                           c_void_p, c_int, c_void_p]),

@@ -7,7 +7,7 @@ PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG_DIR, "csrc")
 LIB_PATH = os.path.join(PKG_DIR, "librmb_b200.so")
 SOURCES = ["act_engine.cu"]
-HEADERS = ["ptx.cuh", "gemm_tc.cuh", "gemm_plan.h", "tma_host.h", "attention_tc.cuh", "elementwise.cuh", "conv_halo.cuh", "diffusion_kernels.cuh", "diffusion_engine.cuh", "imgenc_engine.cuh", "gemm_gn.cuh", "pointcloud.cuh"]
+HEADERS = ["ptx.cuh", "gemm_tc.cuh", "gemm_plan.h", "tma_host.h", "attention_tc.cuh", "elementwise.cuh", "conv_halo.cuh", "diffusion_kernels.cuh", "diffusion_engine.cuh", "imgenc_engine.cuh", "gemm_gn.cuh", "pointcloud.cuh", "resize.cuh"]
 
 
 def _nvcc():

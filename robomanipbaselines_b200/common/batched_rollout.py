@@ -34,8 +34,10 @@ def _norm_params(stats, direction):
 
 
 class BatchedRollout:
-    def __init__(self, policy, batch, model_meta_info, device="cuda:0", no_temp_ensem=False):
-        """policy: robomanipbaselines_b200.policy.act.ACTPolicy with weights loaded."""
+    def __init__(self, policy, batch, model_meta_info, device="cuda:0", no_temp_ensem=False, use_cuda_graph=None):
+        """policy: robomanipbaselines_b200.policy.act.ACTPolicy with weights loaded.
+        use_cuda_graph: replay one policy step (normalise -> ACT forward -> ensembling, ~50 launches) as a single CUDA
+        graph with static input buffers; default on for batch <= 8, where the step is launch-latency bound."""
         self.lib = _lib.load()
         self.policy = policy
         self.B = batch
@@ -59,6 +61,8 @@ class BatchedRollout:
         self.action = torch.zeros(batch, self.Da, device=dev, dtype=torch.float64)
         self.action_norm = torch.zeros(batch, self.Da, device=dev, dtype=torch.float64)
         self._fifo_pos = 0   # no_temp_ensem: index into the current chunk (all episodes are stepped in lock-step)
+        self.use_cuda_graph = (batch <= 8) if use_cuda_graph is None else bool(use_cuda_graph)
+        self._graph = None   # (graph, static images, static raw state, image shape)
 
     def reset(self, mask=None):
         """RolloutAct.reset_variables (:62-66) for the episodes in `mask` (bool (B,), default all)."""
@@ -80,6 +84,32 @@ class BatchedRollout:
         Returns the denormalised float64 actions (B, Da) (device tensor, valid until the next call)."""
         if self.no_temp_ensem:
             return self._infer_fifo(images_u8, raw_state)
+        if self.use_cuda_graph:
+            return self._infer_graph(images_u8, raw_state)
+        return self._infer_eager(images_u8, raw_state)
+
+    def _infer_graph(self, images_u8, raw_state):
+        key = (tuple(images_u8.shape), images_u8.dtype)
+        if self._graph is None or self._graph[3] != key:
+            s_img, s_state = torch.empty_like(images_u8), torch.empty_like(raw_state)
+            s_img.copy_(images_u8); s_state.copy_(raw_state)
+            # warm-up outside the capture (plans, kernel attributes) on copies of the rollout state, so that the
+            # per-episode counters and the ring buffer are exactly what the caller left them
+            saved = (self.ring.clone(), self.step.clone(), self.reset_mask.clone())
+            self._infer_eager(s_img, s_state, clear_reset=False)
+            torch.cuda.synchronize(self.device)
+            self.ring.copy_(saved[0]); self.step.copy_(saved[1]); self.reset_mask.copy_(saved[2])
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self._infer_eager(s_img, s_state, clear_reset=True)
+            # the capture did not execute: state is still the caller's
+            self._graph = (g, s_img, s_state, key)
+        g, s_img, s_state, _ = self._graph
+        s_img.copy_(images_u8); s_state.copy_(raw_state)
+        g.replay()
+        return self.action
+
+    def _infer_eager(self, images_u8, raw_state, clear_reset=True):
         self.normalize_state(raw_state)
         img_h, img_w = images_u8.shape[2], images_u8.shape[3]
         eng = self.policy.engine_for(self.B, img_h, img_w, self.device)
@@ -88,7 +118,8 @@ class BatchedRollout:
                                          ptr(self.wtab), self.a_type, ptr(self.a_p0), ptr(self.a_p1), self.a_out_min,
                                          ptr(self.action), None, ptr(self.action_norm), self.B, self.C, self.Da,
                                          cur_stream()), "rmb_ensemble_step")
-        self.reset_mask.zero_()
+        if clear_reset:
+            self.reset_mask.zero_()
         return self.action
 
     def _infer_fifo(self, images_u8, raw_state):

@@ -887,3 +887,4 @@ int rmb_layernorm512(const float* d_x, const float* d_gamma, const float* d_beta
 #include "diffusion_engine.cuh"
 #include "imgenc_engine.cuh"
 #include "pointcloud.cuh"
+#include "resize.cuh"

@@ -22,6 +22,9 @@ run t_stem 300 $PT tests/test_kernels_gpu.py -k "preprocess_and_stem"
 run t_attn 300 $PT tests/test_kernels_gpu.py -k "test_attention"
 run t_engine 600 $PT tests/test_act_engine_gpu.py
 ENGINE_RC=$?
+run t_diffusion 900 $PT tests/test_diffusion_gpu.py
+run t_pointcloud 300 $PT tests/test_pointcloud_gpu.py
+run t_resize 300 $PT tests/test_resize_gpu.py
 if [ "$1" != "--no-bench" ] && [ $ENGINE_RC -eq 0 ]; then
   run smoke 300 python -c "import __graft_entry__ as g; g.smoke()"
   run bench 900 python bench.py --steps 5 --warmup 3
