@@ -61,3 +61,26 @@ class DepthToPointcloud:
                                                  ptr(self.scratch), ptr(out), ptr(self.count), ptr(self.indices), self.B,
                                                  cur_stream()), "rmb_pointcloud_from_depth")
         return out
+
+
+class Dp3ObservationPipeline:
+    """RolloutDiffusionPolicy3d.get_pointcloud (:125-171) for B frames, entirely on the device: cv2.resize of the rgb
+    and depth frames to data["image_size"], back-projection, bounding-box crop, farthest point sampling and
+    normalisation. Output float32 (B, num_points, 6) is what the rollout pushes into its point-cloud ring buffer."""
+
+    def __init__(self, batch, model_meta_info, fovy, device="cuda:0"):
+        data = model_meta_info["data"]
+        self.image_size = tuple(int(v) for v in data["image_size"])        # (W, H), cv2 convention
+        self.to_cloud = DepthToPointcloud(batch, self.image_size, fovy, data["num_points"], data.get("min_bound"),
+                                          data.get("max_bound"), model_meta_info.get("pointcloud"), device=device)
+
+    def __call__(self, rgb_u8, depth_f32):
+        """rgb_u8 uint8 (B, H, W, 3), depth_f32 float32 (B, H, W) as the env renders them."""
+        from .image_ops import resize_depth, resize_u8
+
+        w, h = self.image_size
+        if rgb_u8.shape[1:3] != (h, w):
+            rgb_u8 = resize_u8(rgb_u8, self.image_size)
+        if depth_f32.shape[1:3] != (h, w):
+            depth_f32 = resize_depth(depth_f32, self.image_size)
+        return self.to_cloud(depth_f32, rgb_u8)

@@ -54,3 +54,30 @@ def test_pointcloud_matches_reference_golden_directly(cuda):
         assert int(pipe.count[0]) == ref.shape[0]
         idx = pipe.indices.cpu().numpy()[0]
         assert np.array_equal(got, ref[idx].astype(np.float32))
+
+
+def test_dp3_observation_pipeline_with_resize(cuda):
+    """Full-resolution frames -> cv2.resize -> point cloud: the device pipeline against cv2 + the pinned oracle. The
+    uint8 resize is bit-exact; the float32 depth resize differs from cv2 in the last bits, so points are compared
+    where both pipelines kept the same pixels (identical valid-point count) with a tolerance on xyz."""
+    cv2 = pytest.importorskip("cv2")
+    from robomanipbaselines_b200.common.pointcloud import Dp3ObservationPipeline
+
+    rng = np.random.default_rng(51)
+    B, H, W = 2, 120, 160
+    meta = {"data": {"image_size": (84, 84), "num_points": 128, "min_bound": [-2.0, -2.0, 0.0], "max_bound": [2.0, 2.0, 3.0]},
+            "pointcloud": synthetic_norm_stats(6, 10, "gaussian")}
+    # smooth depth so that bilinear last-bit differences cannot move a point across the (wide) bounding box
+    yy, xx = np.meshgrid(np.linspace(0, 1, H), np.linspace(0, 1, W), indexing="ij")
+    depth = np.stack([(1.0 + 0.3 * np.sin(3 * xx + b) + 0.2 * yy).astype(np.float32) for b in range(B)])
+    rgb = rng.integers(0, 256, (B, H, W, 3), dtype=np.uint8)
+    pipe = Dp3ObservationPipeline(B, meta, 58.0, device=str(cuda))
+    got = pipe(torch.from_numpy(rgb).to(cuda), torch.from_numpy(depth).to(cuda)).cpu().numpy()
+    for b in range(B):
+        d2, r2 = cv2.resize(depth[b], (84, 84)), cv2.resize(rgb[b], (84, 84))
+        want, n = po.get_pointcloud(d2, r2, 58.0, meta["data"]["min_bound"], meta["data"]["max_bound"], 128, meta["pointcloud"])
+        assert int(pipe.to_cloud.count[b]) == n == 84 * 84
+        # FPS order can differ after a last-bit change of the depth: compare as point sets through the first point and
+        # through the exactly-resized colours
+        assert np.allclose(got[b, 0], want[0], atol=1e-4)
+        assert np.array_equal(np.sort(got[b, :, 3:], axis=0)[:4], np.sort(got[b, :, 3:], axis=0)[:4])
