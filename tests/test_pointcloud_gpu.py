@@ -80,4 +80,5 @@ def test_dp3_observation_pipeline_with_resize(cuda):
         # FPS order can differ after a last-bit change of the depth: compare as point sets through the first point and
         # through the exactly-resized colours
         assert np.allclose(got[b, 0], want[0], atol=1e-4)
-        assert np.array_equal(np.sort(got[b, :, 3:], axis=0)[:4], np.sort(got[b, :, 3:], axis=0)[:4])
+        dmin = np.abs(got[b][:, None, :] - want[None, :, :]).max(axis=2).min(axis=1)
+        assert (dmin <= 1e-4).mean() >= 0.9, (dmin <= 1e-4).mean()
