@@ -38,7 +38,7 @@ struct HaloParams {
 template <int BLOCK_K>
 struct HaloSmem {
   static constexpr int kWTapBytes = 64 * BLOCK_K * 2;
-  static constexpr int kStagingBytes = 2 * 16384;   // epilogue: output tile + residual tile (128 px x 64 ch act_t each)
+  static constexpr int kStagingBytes = 2 * 16384;   // epilogue: one output tile (128 px x 64 ch act_t) per epilogue group
   static constexpr int kBarrierBytes = 256;
   static int total(int n_taps, int n_stages, uint32_t stage_bytes) {
     return n_taps * kWTapBytes + n_stages * static_cast<int>(stage_bytes) + kStagingBytes + kBarrierBytes + 1024;
@@ -47,93 +47,89 @@ struct HaloSmem {
 
 // Epilogue of the halo conv (warps 0..7): TMEM -> registers (+bias, +residual, ReLU) -> 16-bit tile in shared memory in
 // the TMA layout -> ONE cp.async.bulk.tensor store per tile (coalesced by hardware, clipped at the image border).
-// Thread = accumulator row (TMEM lane quarter = warp % 4) x 32 of the 64 output channels (warp / 4). The residual tile
-// (identity branch of the BasicBlock) arrives by TMA as well, issued one tile ahead by the store-issuing thread.
+// These convs have short K (7 or 27 MMAs per tile), so a tile's epilogue costs about as much as its MMAs: the eight
+// epilogue warps therefore work as TWO independent groups of four (group g owns accumulator g, output staging tile g and
+// named barrier 1 + g) and drain two tiles concurrently. Thread = accumulator row (TMEM lane quarter = warp % 4), all 64
+// output channels. The residual (identity branch of the BasicBlock) is the thread's own 128-byte row, prefetched into
+// registers before the accumulator is waited for.
 template <int RES>
-__device__ __forceinline__ void halo_epilogue(const CUtensorMap* tmap_out, const CUtensorMap* tmap_res,
-                                              const GemmParams& p, uint8_t* out_stage, uint8_t* res_stage,
-                                              uint64_t* res_full, uint32_t tmem_base, uint64_t* tmem_full_bar,
-                                              uint64_t* tmem_empty_bar, int total_tiles, int warp, int lane) {
-  const int q = warp & 3, half = warp >> 2;
+__device__ __forceinline__ void halo_epilogue(const CUtensorMap* tmap_out, const GemmParams& p, uint8_t* out_stage_base,
+                                              uint32_t tmem_base, uint64_t* tmem_full_bar, uint64_t* tmem_empty_bar,
+                                              int total_tiles, int warp, int lane) {
+  const int q = warp & 3, grp = warp >> 2;
   const int r = q * 32 + lane;
-  const bool issuer = (threadIdx.x == 0);
-  float bias[32];
-#pragma unroll
-  for (int i = 0; i < 8; ++i) {
-    const float4 b4 = (p.bias != nullptr) ? __ldg(reinterpret_cast<const float4*>(p.bias + half * 32) + i)
-                                          : make_float4(0.f, 0.f, 0.f, 0.f);
-    bias[4 * i] = b4.x; bias[4 * i + 1] = b4.y; bias[4 * i + 2] = b4.z; bias[4 * i + 3] = b4.w;
-  }
+  const bool issuer = (q == 0 && lane == 0);
+  const int wl = r % p.box_w, hl = r / p.box_w;
   const float relu_floor = p.relu ? 0.0f : -INFINITY;
-  const uint32_t out_base = smem_u32(out_stage), res_base = smem_u32(res_stage);
-  uint32_t off[4];                                   // this thread's four 16-byte chunks inside its 128-byte row
+  const uint32_t out_base = smem_u32(out_stage_base + grp * 16384);
+  uint32_t off[8];                                   // this thread's eight 16-byte chunks inside its 128-byte row
 #pragma unroll
-  for (int c = 0; c < 4; ++c) off[c] = r * 128 + (((half * 4 + c) ^ (r & 7)) << 4);
-  const uint32_t res_bar = smem_u32(res_full);
-  const uint32_t tile_bytes = 128u * 128u;
-  auto tile_origin = [&](int tile, int* w0, int* h0, int* bt) {
-    *w0 = (tile % p.tiles_w) * p.box_w;
-    *h0 = ((tile / p.tiles_w) % p.tiles_h) * p.box_h;
-    *bt = tile / (p.tiles_w * p.tiles_h);
+  for (int c = 0; c < 8; ++c) off[c] = r * 128 + ((c ^ (r & 7)) << 4);
+  uint32_t acc_phase = 0;
+  // residual row of tile `t` for this thread (nullptr outside the image or past the last tile)
+  auto res_row = [&](int t) -> const uint4* {
+    if (RES == 0 || t >= total_tiles) return nullptr;
+    const int w = (t % p.tiles_w) * p.box_w + wl, h = ((t / p.tiles_w) % p.tiles_h) * p.box_h + hl;
+    const int bt2 = t / (p.tiles_w * p.tiles_h);
+    if (w >= p.W || h >= p.H) return nullptr;
+    return reinterpret_cast<const uint4*>(static_cast<const act_t*>(p.residual) + ((static_cast<long long>(bt2) * p.H + h) * p.W + w) * 64);
   };
-  if (RES != 0 && issuer && static_cast<int>(blockIdx.x) < total_tiles) {
-    int w0, h0, bt;
-    tile_origin(blockIdx.x, &w0, &h0, &bt);
-    mbar_arrive_expect_tx_u32(res_bar, tile_bytes);
-    tma_load_5d_u32(res_base, tmap_res, res_bar, 0, w0, 0, h0, bt);
+  uint4 rv[8];
+  if (RES != 0) {
+    const uint4* rp = res_row(blockIdx.x + grp * gridDim.x);
+#pragma unroll
+    for (int c = 0; c < 8; ++c) rv[c] = rp ? __ldg(rp + c) : make_uint4(0u, 0u, 0u, 0u);
   }
-  int acc = 0; uint32_t acc_phase = 0, res_phase = 0;
-  for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-    mbar_wait(&tmem_full_bar[acc], acc_phase);
+  for (int tile = blockIdx.x + grp * gridDim.x; tile < total_tiles; tile += 2 * gridDim.x) {
+    const int w0 = (tile % p.tiles_w) * p.box_w;
+    const int h0 = ((tile / p.tiles_w) % p.tiles_h) * p.box_h;
+    const int bt = tile / (p.tiles_w * p.tiles_h);
+    const uint4* rp_next = res_row(tile + 2 * gridDim.x);       // reloaded chunk by chunk as soon as a chunk is consumed
+    mbar_wait(&tmem_full_bar[grp], acc_phase);
     tc_fence_after();
-    uint32_t v[32];
-    tmem_ld_32x32b_x32(tmem_base + acc * 64 + half * 32 + (static_cast<uint32_t>(q * 32) << 16), v);
+    uint32_t v0[32], v1[32];
+    const uint32_t t_row = tmem_base + grp * 64 + (static_cast<uint32_t>(q * 32) << 16);
+    tmem_ld_32x32b_x32(t_row, v0);
+    tmem_ld_32x32b_x32(t_row + 32, v1);
     tmem_ld_wait();
     tc_fence_before();
     __syncwarp();
-    if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);          // 8 arrivals free the accumulator for the next tile
-    float f[32];
+    if (lane == 0) mbar_arrive(&tmem_empty_bar[grp]);           // 4 arrivals free this group's accumulator
+    if (issuer) bulk_wait_group_read0();                        // this group's previous store has read its staging tile
+    named_bar_sync(1 + grp, 128);
 #pragma unroll
-    for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]) + bias[i];
-    if (RES != 0) {
-      mbar_wait(res_full, res_phase);
-      res_phase ^= 1;
+    for (int c = 0; c < 8; ++c) {
+      const uint32_t* v = (c < 4) ? &v0[8 * c] : &v1[8 * (c - 4)];
+      float f[8];
 #pragma unroll
-      for (int c = 0; c < 4; ++c) {
-        const uint4 rv = ld_shared_v4u(res_base + off[c]);
-        const uint32_t u[4] = {rv.x, rv.y, rv.z, rv.w};
+      for (int h2 = 0; h2 < 2; ++h2) {
+        const float4 b4 = (p.bias != nullptr) ? __ldg(reinterpret_cast<const float4*>(p.bias + 8 * c) + h2) : make_float4(0.f, 0.f, 0.f, 0.f);
+        f[4 * h2 + 0] = __uint_as_float(v[4 * h2 + 0]) + b4.x;
+        f[4 * h2 + 1] = __uint_as_float(v[4 * h2 + 1]) + b4.y;
+        f[4 * h2 + 2] = __uint_as_float(v[4 * h2 + 2]) + b4.z;
+        f[4 * h2 + 3] = __uint_as_float(v[4 * h2 + 3]) + b4.w;
+      }
+      if (RES != 0) {
+        const uint32_t u[4] = {rv[c].x, rv[c].y, rv[c].z, rv[c].w};
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
           const float2 t = unpack_act2(u[j]);
-          f[8 * c + 2 * j] += t.x; f[8 * c + 2 * j + 1] += t.y;
+          f[2 * j] += t.x; f[2 * j + 1] += t.y;
         }
+        rv[c] = rp_next ? __ldg(rp_next + c) : make_uint4(0u, 0u, 0u, 0u);   // next tile's residual, in flight from here
       }
-    }
-    if (issuer) bulk_wait_group_read0();                        // the previous tile's store has read out_stage
-    named_bar_sync(1, 256);
-#pragma unroll
-    for (int c = 0; c < 4; ++c) {
-      uint32_t w[4];
-#pragma unroll
-      for (int j = 0; j < 4; ++j)
-        w[j] = pack_act2(fmaxf(f[8 * c + 2 * j], relu_floor), fmaxf(f[8 * c + 2 * j + 1], relu_floor));
-      st_shared_v4(out_base + off[c], w[0], w[1], w[2], w[3]);
+      st_shared_v4(out_base + off[c], pack_act2(fmaxf(f[0], relu_floor), fmaxf(f[1], relu_floor)),
+                   pack_act2(fmaxf(f[2], relu_floor), fmaxf(f[3], relu_floor)),
+                   pack_act2(fmaxf(f[4], relu_floor), fmaxf(f[5], relu_floor)),
+                   pack_act2(fmaxf(f[6], relu_floor), fmaxf(f[7], relu_floor)));
     }
     fence_proxy_async_smem();                                   // generic-proxy writes -> visible to the TMA store
-    named_bar_sync(1, 256);                                     // tile complete; residual tile consumed by everyone
+    named_bar_sync(1 + grp, 128);
     if (issuer) {
-      int w0, h0, bt;
-      tile_origin(tile, &w0, &h0, &bt);
       tma_store_5d(tmap_out, out_base, 0, w0, 0, h0, bt);
       bulk_commit_group();
-      const int next = tile + gridDim.x;
-      if (RES != 0 && next < total_tiles) {
-        tile_origin(next, &w0, &h0, &bt);
-        mbar_arrive_expect_tx_u32(res_bar, tile_bytes);
-        tma_load_5d_u32(res_base, tmap_res, res_bar, 0, w0, 0, h0, bt);
-      }
     }
-    if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    acc_phase ^= 1;
   }
   if (issuer) bulk_wait_group0();
 }
@@ -170,7 +166,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < kHaloMaxStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-    for (int a = 0; a < 2; ++a) { mbar_init(&tmem_full_bar[a], 1); mbar_init(&tmem_empty_bar[a], 8); }
+    for (int a = 0; a < 2; ++a) { mbar_init(&tmem_full_bar[a], 1); mbar_init(&tmem_empty_bar[a], 4); }
     mbar_init(w_bar, 1);
     mbar_init(res_full, 1);
     fence_mbar_init();
@@ -258,8 +254,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
   } else {
-    halo_epilogue<RES>(&tmap_out, &tmap_res, p, smem_stage, smem_stage + 16384, res_full, tmem_base, tmem_full_bar,
-                       tmem_empty_bar, total_tiles, warp, lane);
+    halo_epilogue<RES>(&tmap_out, p, smem_stage, tmem_base, tmem_full_bar, tmem_empty_bar, total_tiles, warp, lane);
   }
 
   tc_fence_before();
