@@ -17,27 +17,37 @@
 namespace {
 
 // gemm_tc_kernel with the fused GroupNorm + Mish + FiLM + residual epilogue (gemm_gn.cuh)
-template <int BN, int ST, int EPI>
+template <int BN, int ST, int EPI, bool PAIR>
 cudaError_t launch_gemm_gn_instance(const GemmPlan& g, int num_sms, cudaStream_t stream) {
-  using S = GemmSmem<BN, 64, ST>;
+  using S = GemmSmem<BN, 64, ST, PAIR>;
+  static_assert(S::kTotal <= 232448, "shared memory");
+  auto kern = PAIR ? gemm_tc_pair_kernel<BN, 64, ST, false, 0, EPI> : gemm_tc_kernel<BN, 64, ST, false, 0, EPI>;
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<BN, 64, ST, false, 0, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal);
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal);
     if (e != cudaSuccess) return e;
     attr_set = true;
   }
-  const long long tiles = 1ll * g.p.tiles_w * g.p.tiles_h * g.p.tiles_b * g.p.n_col_tiles;
-  const int grid = static_cast<int>(std::min<long long>(tiles, num_sms));
-  gemm_tc_kernel<BN, 64, ST, false, 0, EPI><<<grid, kGemmThreads, S::kTotal, stream>>>(g.ta, g.tb, g.p);
+  kern<<<gemm_grid(g, num_sms), kGemmThreads, S::kTotal, stream>>>(g.ta, g.tb, g.p);
   return cudaGetLastError();
 }
 
-cudaError_t launch_gemm_gn(const GemmPlan& g, int num_sms, cudaStream_t stream) {
-  const bool film = g.p.gn_film_gc != nullptr;
-  if (g.block_n == 64) return film ? launch_gemm_gn_instance<64, 6, 1>(g, num_sms, stream) : launch_gemm_gn_instance<64, 6, 2>(g, num_sms, stream);
-  if (g.block_n == 128) return film ? launch_gemm_gn_instance<128, 6, 1>(g, num_sms, stream) : launch_gemm_gn_instance<128, 6, 2>(g, num_sms, stream);
-  if (g.block_n == 256) return film ? launch_gemm_gn_instance<256, 4, 1>(g, num_sms, stream) : launch_gemm_gn_instance<256, 4, 2>(g, num_sms, stream);
+template <int EPI>
+cudaError_t launch_gemm_gn_epi(const GemmPlan& g, int num_sms, cudaStream_t stream) {
+  if (g.pair) {
+    if (g.block_n == 64) return launch_gemm_gn_instance<64, 8, EPI, true>(g, num_sms, stream);
+    if (g.block_n == 128) return launch_gemm_gn_instance<128, 8, EPI, true>(g, num_sms, stream);
+    if (g.block_n == 256) return launch_gemm_gn_instance<256, 6, EPI, true>(g, num_sms, stream);
+    return cudaErrorInvalidValue;
+  }
+  if (g.block_n == 64) return launch_gemm_gn_instance<64, 6, EPI, false>(g, num_sms, stream);
+  if (g.block_n == 128) return launch_gemm_gn_instance<128, 6, EPI, false>(g, num_sms, stream);
+  if (g.block_n == 256) return launch_gemm_gn_instance<256, 4, EPI, false>(g, num_sms, stream);
   return cudaErrorInvalidValue;
+}
+
+cudaError_t launch_gemm_gn(const GemmPlan& g, int num_sms, cudaStream_t stream) {
+  return g.p.gn_film_gc != nullptr ? launch_gemm_gn_epi<1>(g, num_sms, stream) : launch_gemm_gn_epi<2>(g, num_sms, stream);
 }
 
 // can this conv plan normalise its own output? (whole samples per row tile, whole groups per column tile)
@@ -73,7 +83,8 @@ bool plan_conv1d(GemmPlan* g, const void* in, int c_extent, long long row_stride
   const uint64_t K = (uint64_t)ntaps * Cin;
   const uint64_t wdims[2] = {K, (uint64_t)Cout};
   const uint64_t wstr[1] = {K * e};
-  const uint32_t wbox[2] = {64, (uint32_t)g->block_n};
+  g->pair = gemm_use_pair(p);
+  const uint32_t wbox[2] = {64, (uint32_t)(g->pair ? g->block_n / 2 : g->block_n)};
   if (!make_tmap_act(&g->tb, Wt, 2, wdims, wstr, wbox, 128, err)) return false;
   g->flops = 2ll * B * W_view * Cout * (long long)K;
   return true;

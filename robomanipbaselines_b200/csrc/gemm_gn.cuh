@@ -15,10 +15,10 @@
 namespace rmb {
 
 // FILM = true: conv0 of a block (FiLM after the Mish, no residual); FILM = false: conv1 (residual or nothing).
-template <int BLOCK_N, bool FILM>
+template <int BLOCK_N, bool FILM, bool PAIR>
 __device__ __forceinline__ void gemm_gn_epilogue(const GemmParams& p, uint8_t* smem_stage, uint32_t tmem_base,
-                                                 uint64_t* tmem_full_bar, uint64_t* tmem_empty_bar, int total_tiles,
-                                                 int warp, int lane) {
+                                                 uint64_t* tmem_full_bar, uint64_t* tmem_empty_bar,
+                                                 const TileSched<PAIR>& ts, int warp, int lane) {
   constexpr int kChunks = BLOCK_N / 32;   // 32-column chunks of a tile
   constexpr int kMine = kChunks / 2;      // chunks handled by this warp: columns half * BLOCK_N/2 .. +BLOCK_N/2
   float2* stat = reinterpret_cast<float2*>(smem_stage);          // [128 rows][kChunks] (sum, sum of squares): <= 8 KB
@@ -34,7 +34,8 @@ __device__ __forceinline__ void gemm_gn_epilogue(const GemmParams& p, uint8_t* s
   const float inv_n = 1.0f / static_cast<float>(T * p.gn_cg);
   const int N = p.n_col_tiles * BLOCK_N;
   int acc = 0; uint32_t acc_phase = 0;
-  for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+  for (int ti = ts.first; ti < ts.count; ti += ts.step) {
+    const int tile = ts.tile(ti);
     const int ct = tile % p.n_col_tiles, bt = tile / p.n_col_tiles;
     const int b = bt * p.box_b + bl;
     const bool valid = (r < rows_per_tile) && (b < p.B);
@@ -131,7 +132,7 @@ __device__ __forceinline__ void gemm_gn_epilogue(const GemmParams& p, uint8_t* s
       if (j + 1 == kMine) {
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);         // 8 arrivals free the accumulator
+        if (lane == 0) ts.release_acc(tmem_empty_bar, acc);       // 8 arrivals (per CTA) free the accumulator
       }
       const float mean = g_mean[j], rstd = g_rstd[j];
 #pragma unroll

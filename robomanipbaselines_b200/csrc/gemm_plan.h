@@ -1,5 +1,6 @@
 // Host-side planning of gemm_tc_kernel launches: tensor maps, tap tables, row tiling.
 #pragma once
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -15,8 +16,18 @@ struct GemmPlan {
   CUtensorMap ta, tb;
   GemmParams p;
   int block_n = 0, block_k = 0;
+  bool pair = false;     // launch gemm_tc_pair_kernel (tb's box then holds block_n / 2 weight rows)
   long long flops = 0;   // 2*rows*N*K of useful work (for reporting)
 };
+
+// CTA pairs pay when the launch is throughput-bound (a tile for every SM): a pair loads 2/3 of the operand bytes per
+// output tile, and the L2 -> SM path is what bounds the single-CTA 128 x 256 tile (48 KB per k-block against 524 MMA
+// clocks; ncu: 61 B/clk/SM ingest with the tensor pipe 47 % busy). RMB_GEMM_NO_PAIR=1 keeps single-CTA tiles (A/B runs).
+inline bool gemm_use_pair(const GemmParams& p) {
+  static const bool off = [] { const char* e = getenv("RMB_GEMM_NO_PAIR"); return e != nullptr && e[0] == '1'; }();
+  const long long row_tiles = 1ll * p.tiles_w * p.tiles_h * p.tiles_b;
+  return !off && (row_tiles % 2 == 0 || row_tiles >= 32) && row_tiles * p.n_col_tiles >= 148;
+}
 
 inline int pick_block_n(int N) {
   if (N % 256 == 0) return 256;
@@ -74,7 +85,8 @@ inline bool plan_linear(GemmPlan* g, const void* A, long long M, int K, int lda,
   if (!make_tmap_act(&g->ta, A, 5, dims, strides, box, 128, err)) return false;
   const uint64_t wdims[2] = {static_cast<uint64_t>(K), static_cast<uint64_t>(N)};
   const uint64_t wstr[1] = {static_cast<uint64_t>(K) * 2};
-  const uint32_t wbox[2] = {64, static_cast<uint32_t>(g->block_n)};
+  g->pair = gemm_use_pair(p);
+  const uint32_t wbox[2] = {64, static_cast<uint32_t>(g->pair ? g->block_n / 2 : g->block_n)};
   if (!make_tmap_act(&g->tb, Wt, 2, wdims, wstr, wbox, 128, err)) return false;
   g->flops = 2ll * M * N * K;
   return true;
@@ -129,7 +141,8 @@ inline bool plan_conv(GemmPlan* g, const void* in, int B, int H, int W, int Cin,
   const uint64_t K = (uint64_t)ksize * ksize * Cin;
   const uint64_t wdims[2] = {K, (uint64_t)Cout};
   const uint64_t wstr[1] = {K * e};
-  const uint32_t wbox[2] = {64, (uint32_t)g->block_n};
+  g->pair = gemm_use_pair(p);
+  const uint32_t wbox[2] = {64, (uint32_t)(g->pair ? g->block_n / 2 : g->block_n)};
   if (!make_tmap_act(&g->tb, Wt, 2, wdims, wstr, wbox, 128, err)) return false;
   g->flops = 2ll * B * OH * OW * Cout * (long long)K;
   return true;
@@ -174,42 +187,55 @@ inline bool plan_conv1(GemmPlan* g, const void* in_padded, int B, int H, int W, 
   return true;
 }
 
-template <int BN, int BK, int ST, bool OUT_F32, int RES>
+// grid of a persistent GEMM launch: one CTA per SM, or one cluster of two per SM pair
+inline int gemm_grid(const GemmPlan& g, int num_sms) {
+  const long long row_tiles = 1ll * g.p.tiles_w * g.p.tiles_h * g.p.tiles_b;
+  if (!g.pair) return static_cast<int>(std::min<long long>(row_tiles * g.p.n_col_tiles, num_sms));
+  return 2 * static_cast<int>(std::min<long long>((row_tiles + 1) / 2 * g.p.n_col_tiles, num_sms / 2));
+}
+
+template <int BN, int BK, int ST, bool OUT_F32, int RES, bool PAIR>
 inline cudaError_t launch_gemm_instance(const GemmPlan& g, int num_sms, cudaStream_t stream) {
-  using S = GemmSmem<BN, BK, ST>;
+  using S = GemmSmem<BN, BK, ST, PAIR>;
+  static_assert(S::kTotal <= 232448, "shared memory");
+  auto kern = PAIR ? gemm_tc_pair_kernel<BN, BK, ST, OUT_F32, RES> : gemm_tc_kernel<BN, BK, ST, OUT_F32, RES>;
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<BN, BK, ST, OUT_F32, RES>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal);
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal);
     if (e != cudaSuccess) return e;
     attr_set = true;
   }
-  const long long tiles = 1ll * g.p.tiles_w * g.p.tiles_h * g.p.tiles_b * g.p.n_col_tiles;
-  const int grid = static_cast<int>(std::min<long long>(tiles, num_sms));
-  gemm_tc_kernel<BN, BK, ST, OUT_F32, RES><<<grid, kGemmThreads, S::kTotal, stream>>>(g.ta, g.tb, g.p);
+  kern<<<gemm_grid(g, num_sms), kGemmThreads, S::kTotal, stream>>>(g.ta, g.tb, g.p);
   return cudaGetLastError();
 }
 
 // epilogue modes in use: act out (+ act residual) for the convs and QKV / FFN-up projections; fp32 out (+ fp32
 // residual) for the transformer's residual stream
-template <int BN, int BK, int ST>
+template <int BN, int BK, int ST, bool PAIR>
 inline cudaError_t launch_gemm_variant(const GemmPlan& g, int num_sms, cudaStream_t stream) {
   const bool has_res = g.p.residual != nullptr;
   if (!g.p.out_f32) {
-    if (!has_res) return launch_gemm_instance<BN, BK, ST, false, 0>(g, num_sms, stream);
-    if (!g.p.res_f32) return launch_gemm_instance<BN, BK, ST, false, 1>(g, num_sms, stream);
+    if (!has_res) return launch_gemm_instance<BN, BK, ST, false, 0, PAIR>(g, num_sms, stream);
+    if (!g.p.res_f32) return launch_gemm_instance<BN, BK, ST, false, 1, PAIR>(g, num_sms, stream);
   } else {
-    if (!has_res) return launch_gemm_instance<BN, BK, ST, true, 0>(g, num_sms, stream);
-    if (g.p.res_f32) return launch_gemm_instance<BN, BK, ST, true, 2>(g, num_sms, stream);
-    return launch_gemm_instance<BN, BK, ST, true, 1>(g, num_sms, stream);
+    if (!has_res) return launch_gemm_instance<BN, BK, ST, true, 0, PAIR>(g, num_sms, stream);
+    if (g.p.res_f32) return launch_gemm_instance<BN, BK, ST, true, 2, PAIR>(g, num_sms, stream);
+    return launch_gemm_instance<BN, BK, ST, true, 1, PAIR>(g, num_sms, stream);
   }
   return cudaErrorInvalidValue;   // act out + fp32 residual: not needed on this path
 }
 
 inline cudaError_t launch_gemm(const GemmPlan& g, int num_sms, cudaStream_t stream) {
-  if (g.block_k == 32 && g.block_n == 64) return launch_gemm_variant<64, 32, 8>(g, num_sms, stream);
-  if (g.block_k == 64 && g.block_n == 64) return launch_gemm_variant<64, 64, 6>(g, num_sms, stream);
-  if (g.block_k == 64 && g.block_n == 128) return launch_gemm_variant<128, 64, 6>(g, num_sms, stream);
-  if (g.block_k == 64 && g.block_n == 256) return launch_gemm_variant<256, 64, 4>(g, num_sms, stream);
+  if (g.pair) {
+    if (g.block_k == 64 && g.block_n == 64) return launch_gemm_variant<64, 64, 8, true>(g, num_sms, stream);
+    if (g.block_k == 64 && g.block_n == 128) return launch_gemm_variant<128, 64, 8, true>(g, num_sms, stream);
+    if (g.block_k == 64 && g.block_n == 256) return launch_gemm_variant<256, 64, 6, true>(g, num_sms, stream);
+    return cudaErrorInvalidValue;
+  }
+  if (g.block_k == 32 && g.block_n == 64) return launch_gemm_variant<64, 32, 8, false>(g, num_sms, stream);
+  if (g.block_k == 64 && g.block_n == 64) return launch_gemm_variant<64, 64, 6, false>(g, num_sms, stream);
+  if (g.block_k == 64 && g.block_n == 128) return launch_gemm_variant<128, 64, 6, false>(g, num_sms, stream);
+  if (g.block_k == 64 && g.block_n == 256) return launch_gemm_variant<256, 64, 4, false>(g, num_sms, stream);
   return cudaErrorInvalidValue;
 }
 

@@ -49,22 +49,42 @@ struct GemmParams {
   int gn_cg;                 // channels per group = N / 8
 };
 
-template <int BLOCK_N, int BLOCK_K, int STAGES>
+// PAIR: two CTAs of a cluster work on one 256-row tile (tcgen05 cta_group::2); each holds its 128 rows of A and half
+// of the BLOCK_N rows of B, so a k-block costs a CTA 2/3 of the L2 -> SM bytes of the single-CTA tile.
+template <int BLOCK_N, int BLOCK_K, int STAGES, bool PAIR = false>
 struct GemmSmem {
   static constexpr int kABytes = 128 * BLOCK_K * 2;
-  static constexpr int kBBytes = BLOCK_N * BLOCK_K * 2;
+  static constexpr int kBBytes = (PAIR ? BLOCK_N / 2 : BLOCK_N) * BLOCK_K * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kBarrierBytes = 256;
   static constexpr int kStagingBytes = 8 * 4096;   // epilogue: one 32 x 128 B staging tile per warp
   static constexpr int kTotal = STAGES * kStageBytes + kStagingBytes + kBarrierBytes + 1024;  // +1024: alignment slack
 };
 
+// Persistent tile loop of one CTA. Single CTA: tiles blockIdx.x, +gridDim.x, ... PAIR: cluster c walks pair tiles
+// c, +clusters, ...; pair tile (prt, ct) is row tiles 2*prt (leader) and 2*prt + 1 (peer) of column tile ct. tile(i)
+// is the (row tile * n_col_tiles + column tile) id the roles decode as before; a row tile past the end is all padding.
+template <bool PAIR>
+struct TileSched {
+  int first, step, count, rank, n_col_tiles;
+  uint32_t acc_empty_addr;   // PAIR: shared::cluster address of the leader's tmem_empty_bar[0]
+  __device__ __forceinline__ int tile(int i) const {
+    if (!PAIR) return i;
+    return (2 * (i / n_col_tiles) + rank) * n_col_tiles + (i % n_col_tiles);
+  }
+  // accumulator `acc` has been read out by this warp
+  __device__ __forceinline__ void release_acc(uint64_t* tmem_empty_bar, int acc) const {
+    if (PAIR) mbar_arrive_cluster(acc_empty_addr + acc * 8);
+    else mbar_arrive(&tmem_empty_bar[acc]);
+  }
+};
+
 // ---------------------------------------------------------------------------------------------------------------------
 // Epilogue shared by the GEMM / conv kernels (warps 0..7 of the CTA).
-template <int BLOCK_N, bool OUT_F32, int RES>
+template <int BLOCK_N, bool OUT_F32, int RES, bool PAIR>
 __device__ __forceinline__ void gemm_epilogue(const GemmParams& p, uint8_t* smem_stage, uint32_t tmem_base,
-                                              uint64_t* tmem_full_bar, uint64_t* tmem_empty_bar, int total_tiles,
-                                              int warp, int lane) {
+                                              uint64_t* tmem_full_bar, uint64_t* tmem_empty_bar,
+                                              const TileSched<PAIR>& ts, int warp, int lane) {
   const int rows_per_tile = p.box_w * p.box_h * p.box_b;
   // ------------------------------------------------------------ epilogue warps 0..7
   // Warp e reads TMEM lanes 32*(e%4)..+31 (hardware rule: lane quarter = warp id % 4) and the 32-column chunks
@@ -94,7 +114,8 @@ __device__ __forceinline__ void gemm_epilogue(const GemmParams& p, uint8_t* smem
   const uint32_t ld_odd = stg + (rsel + 4) * 128 + ((sub ^ (rsel + 4)) << 4);
   const float relu_floor = p.relu ? 0.0f : -INFINITY;
   const int col_in_tile = half * 32 + sub * 4;    // first of this lane's 4 columns inside chunk 0 of this warp
-  for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+  for (int ti = ts.first; ti < ts.count; ti += ts.step) {
+    const int tile = ts.tile(ti);
     const int ct = tile % p.n_col_tiles;
     const int rt = tile / p.n_col_tiles;
     const int wt = rt % p.tiles_w;
@@ -137,7 +158,7 @@ __device__ __forceinline__ void gemm_epilogue(const GemmParams& p, uint8_t* smem
       if (j + 1 < kChunksPerWarp) tmem_ld_32x32b_x32(t_row + (j + 1) * 64, v);
       else tc_fence_before();
       __syncwarp();
-      if (j + 1 == kChunksPerWarp && lane == 0) mbar_arrive(&tmem_empty_bar[acc]);   // 8 arrivals free the accumulator
+      if (j + 1 == kChunksPerWarp && lane == 0) ts.release_acc(tmem_empty_bar, acc);   // 8 arrivals (per CTA) free the accumulator
       float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
       if (bias_ptr != nullptr) bv = __ldg(reinterpret_cast<const float4*>(bias_ptr + j * 64));
       float4 f[8];
@@ -178,24 +199,23 @@ __device__ __forceinline__ void gemm_epilogue(const GemmParams& p, uint8_t* smem
   }
 }
 
-template <int BLOCK_N, bool FILM>
+template <int BLOCK_N, bool FILM, bool PAIR>
 __device__ __forceinline__ void gemm_gn_epilogue(const GemmParams& p, uint8_t* smem_stage, uint32_t tmem_base,
-                                                 uint64_t* tmem_full_bar, uint64_t* tmem_empty_bar, int total_tiles,
-                                                 int warp, int lane);
+                                                 uint64_t* tmem_full_bar, uint64_t* tmem_empty_bar,
+                                                 const TileSched<PAIR>& ts, int warp, int lane);
 
 // OUT_F32: fp32 output (else act_t). RES: 0 no residual, 1 act_t residual, 2 fp32 residual.
 // EPI: 0 plain epilogue (bias / residual / ReLU); fused GroupNorm + Mish (gemm_gn.cuh) followed by 1: FiLM, 2: residual.
-template <int BLOCK_N, int BLOCK_K, int STAGES, bool OUT_F32, int RES, int EPI = 0>
-__global__ void __launch_bounds__(kGemmThreads, 1)
-gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
-               const __grid_constant__ GemmParams p) {
+// PAIR: launched as clusters of two CTAs (gemm_tc_pair_kernel); see GemmSmem / TileSched.
+template <int BLOCK_N, int BLOCK_K, int STAGES, bool OUT_F32, int RES, int EPI, bool PAIR>
+__device__ __forceinline__ void gemm_tc_body(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, const GemmParams& p) {
   static_assert(BLOCK_K == 64 || BLOCK_K == 32, "BLOCK_K selects the 128B / 64B swizzle");
   static_assert(BLOCK_N == 64 || BLOCK_N == 128 || BLOCK_N == 256, "BLOCK_N");
-  using S = GemmSmem<BLOCK_N, BLOCK_K, STAGES>;
+  using S = GemmSmem<BLOCK_N, BLOCK_K, STAGES, PAIR>;
   constexpr uint32_t kSwizzleLayout = (BLOCK_K == 64) ? 2u : 4u;   // SWIZZLE_128B : SWIZZLE_64B
   constexpr uint32_t kSBO = 8u * BLOCK_K * 2u;                      // 8-row core-matrix group stride
   constexpr uint32_t kTmemCols = 2 * BLOCK_N;                       // double-buffered accumulator
-  constexpr uint32_t kIdesc = make_idesc_f16(128, BLOCK_N, false, false);
+  constexpr uint32_t kIdesc = make_idesc_f16(PAIR ? 256 : 128, BLOCK_N, false, false);
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -203,48 +223,63 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
   uint8_t* smem_b = smem + STAGES * S::kABytes;
   uint8_t* smem_stage = smem + STAGES * S::kStageBytes;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem_stage + S::kStagingBytes);
-  uint64_t* full_bar = bars;                    // [STAGES]
-  uint64_t* empty_bar = bars + STAGES;          // [STAGES]
-  uint64_t* tmem_full_bar = bars + 2 * STAGES;  // [2]
-  uint64_t* tmem_empty_bar = tmem_full_bar + 2; // [2]
+  uint64_t* full_bar = bars;                    // [STAGES]   PAIR: the leader's are used (both CTAs' TMA bytes land on it)
+  uint64_t* empty_bar = bars + STAGES;          // [STAGES]   PAIR: the leader's commit arrives on both CTAs' copies
+  uint64_t* tmem_full_bar = bars + 2 * STAGES;  // [2]        PAIR: likewise
+  uint64_t* tmem_empty_bar = tmem_full_bar + 2; // [2]        PAIR: the leader's collects both CTAs' epilogue warps
   uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  const int rank = PAIR ? static_cast<int>(cluster_ctarank()) : 0;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-    for (int a = 0; a < 2; ++a) { mbar_init(&tmem_full_bar[a], 1); mbar_init(&tmem_empty_bar[a], 8); }
+    for (int a = 0; a < 2; ++a) { mbar_init(&tmem_full_bar[a], 1); mbar_init(&tmem_empty_bar[a], PAIR ? 16 : 8); }
     fence_mbar_init();
   }
   if (warp == 8 && lane == 0) { prefetch_tmap(&tmap_a); prefetch_tmap(&tmap_b); }
-  if (warp == 9) { tmem_alloc(tmem_ptr_smem, kTmemCols); tmem_relinquish(); }
+  if (warp == 9) {
+    if (PAIR) { tmem_alloc_pair(tmem_ptr_smem, kTmemCols); tmem_relinquish_pair(); }
+    else { tmem_alloc(tmem_ptr_smem, kTmemCols); tmem_relinquish(); }
+  }
   tc_fence_before();
-  __syncthreads();
+  if (PAIR) cluster_sync_all(); else __syncthreads();   // PAIR: the peer's barriers are live before anything lands on them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
 
   const int rows_per_tile = p.box_w * p.box_h * p.box_b;
   const int num_kb = p.num_taps * p.chunks_per_tap;
   const int row_tiles = p.tiles_w * p.tiles_h * p.tiles_b;
-  const int total_tiles = row_tiles * p.n_col_tiles;
-  const uint32_t tx_bytes = static_cast<uint32_t>(rows_per_tile * BLOCK_K * 2 + S::kBBytes);
+  TileSched<PAIR> ts;
+  ts.rank = rank; ts.n_col_tiles = p.n_col_tiles;
+  if (PAIR) {
+    ts.first = blockIdx.x >> 1; ts.step = gridDim.x >> 1; ts.count = ((row_tiles + 1) >> 1) * p.n_col_tiles;
+    ts.acc_empty_addr = mapa_u32(smem_u32(tmem_empty_bar), 0);
+  } else {
+    ts.first = blockIdx.x; ts.step = gridDim.x; ts.count = row_tiles * p.n_col_tiles;
+    ts.acc_empty_addr = 0;
+  }
+  const uint32_t cta_tx_bytes = static_cast<uint32_t>(rows_per_tile * BLOCK_K * 2 + S::kBBytes);
 
   // The producer and MMA warps run their loops warp-uniformly (all 32 lanes, identical control flow) and only the
   // issuing instruction is predicated on one elected lane: loop state stays in uniform registers and the per-k-block
   // instruction count -- the throughput limit of a single issuing thread -- is a few dozen instead of ~150.
   if (warp == 8) {
     // ------------------------------------------------------------ TMA producer
-    const uint32_t a_base = smem_u32(smem_a), b_base = smem_u32(smem_b), full_base = smem_u32(full_bar);
+    const uint32_t a_base = smem_u32(smem_a), b_base = smem_u32(smem_b);
+    const uint32_t full_base = PAIR ? mapa_u32(smem_u32(full_bar), 0) : smem_u32(full_bar);
+    const int n_half = PAIR ? rank * (BLOCK_N / 2) : 0;
     int stage = 0; uint32_t phase = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+    for (int ti = ts.first; ti < ts.count; ti += ts.step) {
+      const int tile = ts.tile(ti);
       const int ct = tile % p.n_col_tiles;
       const int rt = tile / p.n_col_tiles;
       const int wt = rt % p.tiles_w;
       const int ht = (rt / p.tiles_w) % p.tiles_h;
       const int bt = rt / (p.tiles_w * p.tiles_h);
       const int w0 = wt * p.box_w, h0 = ht * p.box_h, b0 = bt * p.box_b;
-      const int n0 = ct * BLOCK_N;
+      const int n0 = ct * BLOCK_N + n_half;
       int kcol = 0;                                   // column of the weight matrix = kb * BLOCK_K
       for (int tap = 0; tap < p.num_taps; ++tap) {
         const int c0 = p.tap_c0[tap], d1 = w0 + p.tap_d1[tap], d2 = p.tap_d2[tap], d3 = h0 + p.tap_d3[tap];
@@ -252,9 +287,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
           mbar_wait(&empty_bar[stage], phase ^ 1);
           if (elect_one()) {
             const uint32_t fb = full_base + stage * 8;
-            mbar_arrive_expect_tx_u32(fb, tx_bytes);
-            tma_load_5d_u32(a_base + stage * S::kABytes, &tmap_a, fb, c0 + ch * BLOCK_K, d1, d2, d3, b0);
-            tma_load_2d_u32(b_base + stage * S::kBBytes, &tmap_b, fb, kcol, n0);
+            if (PAIR) {
+              if (rank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * cta_tx_bytes);   // the peer's boxes land here too
+              tma_load_5d_pair(a_base + stage * S::kABytes, &tmap_a, fb, c0 + ch * BLOCK_K, d1, d2, d3, b0);
+              tma_load_2d_pair(b_base + stage * S::kBBytes, &tmap_b, fb, kcol, n0);
+            } else {
+              mbar_arrive_expect_tx_u32(fb, cta_tx_bytes);
+              tma_load_5d_u32(a_base + stage * S::kABytes, &tmap_a, fb, c0 + ch * BLOCK_K, d1, d2, d3, b0);
+              tma_load_2d_u32(b_base + stage * S::kBBytes, &tmap_b, fb, kcol, n0);
+            }
           }
           __syncwarp();
           kcol += BLOCK_K;
@@ -263,45 +304,72 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
       }
     }
   } else if (warp == 9) {
-    // ------------------------------------------------------------ MMA issuer (one elected lane issues)
-    const uint64_t a_desc0 = make_smem_desc(smem_u32(smem_a), 0, kSBO, kSwizzleLayout);
-    const uint64_t b_desc0 = make_smem_desc(smem_u32(smem_b), 0, kSBO, kSwizzleLayout);
-    const uint32_t empty_base = smem_u32(empty_bar);
-    int stage = 0; uint32_t phase = 0;
-    int acc = 0; uint32_t acc_phase = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-      mbar_wait(&tmem_empty_bar[acc], acc_phase ^ 1);
-      tc_fence_after();
-      const uint32_t d_tmem = tmem_base + acc * BLOCK_N;
-      for (int kb = 0; kb < num_kb; ++kb) {
-        mbar_wait(&full_bar[stage], phase);
+    // ------------------------------------------------------------ MMA issuer (one elected lane issues; PAIR: leader only)
+    if (rank == 0) {
+      const uint64_t a_desc0 = make_smem_desc(smem_u32(smem_a), 0, kSBO, kSwizzleLayout);
+      const uint64_t b_desc0 = make_smem_desc(smem_u32(smem_b), 0, kSBO, kSwizzleLayout);
+      const uint32_t empty_base = smem_u32(empty_bar);
+      int stage = 0; uint32_t phase = 0;
+      int acc = 0; uint32_t acc_phase = 0;
+      for (int ti = ts.first; ti < ts.count; ti += ts.step) {
+        mbar_wait(&tmem_empty_bar[acc], acc_phase ^ 1);
         tc_fence_after();
-        if (elect_one()) {
-          // the 14-bit start-address field (bytes >> 4) never carries: all of shared memory is < 256 KB
-          const uint64_t da = a_desc0 + static_cast<uint64_t>(stage * (S::kABytes >> 4));
-          const uint64_t db = b_desc0 + static_cast<uint64_t>(stage * (S::kBBytes >> 4));
+        const uint32_t d_tmem = tmem_base + acc * BLOCK_N;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          if (elect_one()) {
+            // the 14-bit start-address field (bytes >> 4) never carries: all of shared memory is < 256 KB
+            const uint64_t da = a_desc0 + static_cast<uint64_t>(stage * (S::kABytes >> 4));
+            const uint64_t db = b_desc0 + static_cast<uint64_t>(stage * (S::kBBytes >> 4));
 #pragma unroll
-          for (int k = 0; k < BLOCK_K / 16; ++k)
-            umma_f16_ss(d_tmem, da + 2 * k, db + 2 * k, kIdesc, (kb | k) != 0 ? 1u : 0u);
-          umma_commit_u32(empty_base + stage * 8);    // frees this smem stage when the MMAs above retire
+            for (int k = 0; k < BLOCK_K / 16; ++k) {
+              if (PAIR) umma_f16_ss_pair(d_tmem, da + 2 * k, db + 2 * k, kIdesc, (kb | k) != 0 ? 1u : 0u);
+              else umma_f16_ss(d_tmem, da + 2 * k, db + 2 * k, kIdesc, (kb | k) != 0 ? 1u : 0u);
+            }
+            // frees this smem stage (in both CTAs) when the MMAs above retire
+            if (PAIR) umma_commit_pair_u32(empty_base + stage * 8, 3u);
+            else umma_commit_u32(empty_base + stage * 8);
+          }
+          __syncwarp();
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+        if (elect_one()) {                                   // accumulator complete -> epilogue (of both CTAs)
+          if (PAIR) umma_commit_pair_u32(smem_u32(&tmem_full_bar[acc]), 3u);
+          else umma_commit(&tmem_full_bar[acc]);
         }
         __syncwarp();
-        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
-      if (elect_one()) umma_commit(&tmem_full_bar[acc]);   // accumulator complete -> epilogue
-      __syncwarp();
-      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
   } else {
     if constexpr (EPI != 0)
-      gemm_gn_epilogue<BLOCK_N, EPI == 1>(p, smem_stage, tmem_base, tmem_full_bar, tmem_empty_bar, total_tiles, warp, lane);
+      gemm_gn_epilogue<BLOCK_N, EPI == 1, PAIR>(p, smem_stage, tmem_base, tmem_full_bar, tmem_empty_bar, ts, warp, lane);
     else
-      gemm_epilogue<BLOCK_N, OUT_F32, RES>(p, smem_stage, tmem_base, tmem_full_bar, tmem_empty_bar, total_tiles, warp, lane);
+      gemm_epilogue<BLOCK_N, OUT_F32, RES, PAIR>(p, smem_stage, tmem_base, tmem_full_bar, tmem_empty_bar, ts, warp, lane);
   }
 
   tc_fence_before();
-  __syncthreads();
-  if (warp == 9) { tc_fence_after(); tmem_dealloc(tmem_base, kTmemCols); }
+  if (PAIR) cluster_sync_all(); else __syncthreads();   // PAIR: nothing of the peer is touched after this point
+  if (warp == 9) {
+    tc_fence_after();
+    if (PAIR) tmem_dealloc_pair(tmem_base, kTmemCols); else tmem_dealloc(tmem_base, kTmemCols);
+  }
+}
+
+template <int BLOCK_N, int BLOCK_K, int STAGES, bool OUT_F32, int RES, int EPI = 0>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+               const __grid_constant__ GemmParams p) {
+  gemm_tc_body<BLOCK_N, BLOCK_K, STAGES, OUT_F32, RES, EPI, false>(tmap_a, tmap_b, p);
+}
+
+// CTA-pair version: grid = 2 x clusters; tmap_b's box holds BLOCK_N / 2 weight rows.
+template <int BLOCK_N, int BLOCK_K, int STAGES, bool OUT_F32, int RES, int EPI = 0>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
+gemm_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                    const __grid_constant__ GemmParams p) {
+  gemm_tc_body<BLOCK_N, BLOCK_K, STAGES, OUT_F32, RES, EPI, true>(tmap_a, tmap_b, p);
 }
 
 }  // namespace rmb
