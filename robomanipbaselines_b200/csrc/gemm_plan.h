@@ -60,6 +60,7 @@ inline void fill_common(GemmParams& p, const float* bias, const void* residual, 
   p.bias = bias; p.residual = residual; p.ld_res = ld_res; p.res_f32 = res_f32 ? 1 : 0;
   p.out = out; p.ld_out = ld_out; p.out_f32 = out_f32 ? 1 : 0; p.relu = relu ? 1 : 0;
   p.remap_ncam = 0; p.remap_L = 0; p.remap_off = 0;
+  p.n_valid = 1 << 30;
 }
 
 // out[M, N] = A[M, K] (row-major, leading dim lda) * Wt[N, K]^T
@@ -69,15 +70,20 @@ inline bool plan_linear(GemmPlan* g, const void* A, long long M, int K, int lda,
   *g = GemmPlan();
   g->block_k = 64;
   g->block_n = pick_block_n(N);
+  // wide N that 256 does not divide (dim_feedforward 3200): 256-wide tiles with a ragged last one beat 128-wide tiles,
+  // whose operand bytes per flop are 4/3 higher; the weight rows past N are TMA zero fill, their columns are not stored
+  const bool ragged = N >= 1024 && N % 256 != 0 && N % 64 == 0;
+  if (ragged) g->block_n = 256;
   if (g->block_n == 0 || K % 64 != 0) { if (err) *err = "plan_linear: N must be a multiple of 64 and K of 64"; return false; }
   GemmParams& p = g->p;
   p.box_w = 128; p.box_h = 1; p.box_b = 1;
   p.W = static_cast<int>(M); p.H = 1; p.B = 1;
   p.tiles_w = static_cast<int>((M + 127) / 128); p.tiles_h = 1; p.tiles_b = 1;
-  p.n_col_tiles = N / g->block_n;
+  p.n_col_tiles = (N + g->block_n - 1) / g->block_n;
   p.num_taps = 1; p.chunks_per_tap = K / 64;
   for (int t = 0; t < kMaxTaps; ++t) { p.tap_c0[t] = p.tap_d1[t] = p.tap_d2[t] = p.tap_d3[t] = 0; }
   fill_common(p, bias, residual, ld_res, res_f32, out, ld_out, out_f32, relu);
+  if (ragged) p.n_valid = N;
   const uint64_t dims[5] = {static_cast<uint64_t>(K), static_cast<uint64_t>(M), 1, 1, 1};
   const uint64_t row = static_cast<uint64_t>(lda) * 2;
   const uint64_t strides[4] = {row, row * M, row * M, row * M};

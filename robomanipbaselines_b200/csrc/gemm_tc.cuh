@@ -21,7 +21,8 @@ struct GemmParams {
   int tiles_w, tiles_h, tiles_b;
   int box_w, box_h, box_b;   // rows per tile = box_w*box_h*box_b <= 128
   int W, H, B;               // output extents (rows = B*H*W)
-  int n_col_tiles;           // N / BLOCK_N
+  int n_col_tiles;           // ceil(N / BLOCK_N)
+  int n_valid;               // N: columns at or past it (ragged last column tile, plain epilogue only) are not stored
   // K loop: k-block kb -> (tap = kb / chunks_per_tap, chunk = kb % chunks_per_tap)
   int num_taps, chunks_per_tap;
   int tap_c0[kMaxTaps];      // added to coordinate 0 (channel / phase-channel offset)
@@ -159,8 +160,9 @@ __device__ __forceinline__ void gemm_epilogue(const GemmParams& p, uint8_t* smem
       else tc_fence_before();
       __syncwarp();
       if (j + 1 == kChunksPerWarp && lane == 0) ts.release_acc(tmem_empty_bar, acc);   // 8 arrivals (per CTA) free the accumulator
+      const bool col_ok = col0 + j * 64 < p.n_valid;   // warp-uniform: N is a multiple of 64, a chunk is 32 columns
       float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (bias_ptr != nullptr) bv = __ldg(reinterpret_cast<const float4*>(bias_ptr + j * 64));
+      if (bias_ptr != nullptr && col_ok) bv = __ldg(reinterpret_cast<const float4*>(bias_ptr + j * 64));
       float4 f[8];
   #pragma unroll
       for (int it = 0; it < 8; ++it) f[it] = ld_shared_v4f(((it & 1) ? ld_odd : ld_even) + (it >> 1) * 1024);
@@ -168,7 +170,7 @@ __device__ __forceinline__ void gemm_epilogue(const GemmParams& p, uint8_t* smem
         float4 rv[8];
   #pragma unroll
         for (int it = 0; it < 8; ++it)
-          rv[it] = (optr[it] != nullptr) ? __ldg(reinterpret_cast<const float4*>(rptr[it] + j * 64 * kResEsz))
+          rv[it] = (optr[it] != nullptr && col_ok) ? __ldg(reinterpret_cast<const float4*>(rptr[it] + j * 64 * kResEsz))
                                          : make_float4(0.f, 0.f, 0.f, 0.f);
   #pragma unroll
         for (int it = 0; it < 8; ++it) { f[it].x += rv[it].x; f[it].y += rv[it].y; f[it].z += rv[it].z; f[it].w += rv[it].w; }
@@ -176,7 +178,7 @@ __device__ __forceinline__ void gemm_epilogue(const GemmParams& p, uint8_t* smem
         uint2 rv[8];
   #pragma unroll
         for (int it = 0; it < 8; ++it)
-          rv[it] = (optr[it] != nullptr) ? __ldg(reinterpret_cast<const uint2*>(rptr[it] + j * 64 * kResEsz))
+          rv[it] = (optr[it] != nullptr && col_ok) ? __ldg(reinterpret_cast<const uint2*>(rptr[it] + j * 64 * kResEsz))
                                          : make_uint2(0u, 0u);
   #pragma unroll
         for (int it = 0; it < 8; ++it) {
@@ -188,7 +190,7 @@ __device__ __forceinline__ void gemm_epilogue(const GemmParams& p, uint8_t* smem
       for (int it = 0; it < 8; ++it) {
         const float ox = fmaxf(f[it].x + bv.x, relu_floor), oy = fmaxf(f[it].y + bv.y, relu_floor);
         const float oz = fmaxf(f[it].z + bv.z, relu_floor), ow = fmaxf(f[it].w + bv.w, relu_floor);
-        if (optr[it] != nullptr) {
+        if (optr[it] != nullptr && col_ok) {
           if (OUT_F32) *reinterpret_cast<float4*>(optr[it] + j * 64 * kOutEsz) = make_float4(ox, oy, oz, ow);
           else *reinterpret_cast<uint2*>(optr[it] + j * 64 * kOutEsz) = make_uint2(pack_act2(ox, oy), pack_act2(oz, ow));
         }

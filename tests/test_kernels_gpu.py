@@ -30,6 +30,8 @@ def _report(name, got, ref):
 @pytest.mark.parametrize("M,N,K,flags", [
     (128, 64, 64, 0), (128, 128, 64, 0), (128, 256, 128, 0), (300, 512, 512, 1), (1000, 3200, 512, 1),
     (1204, 512, 3200, 2 | 4), (77, 1024, 512, 2), (4096, 512, 512, 0), (20000, 256, 576, 1),
+    # CTA-pair launches (a tile per SM): even / odd row-tile counts, ragged last column tile (N = 3200, 1088), residuals
+    (19000, 256, 128, 0), (4700, 3200, 512, 1), (38001, 64, 64, 2), (9000, 1088, 192, 2 | 4), (5000, 1024, 256, 0),
 ])
 def test_gemm(lib, cuda, M, N, K, flags):
     g = torch.Generator(device="cpu").manual_seed(M * 7 + N * 3 + K)
