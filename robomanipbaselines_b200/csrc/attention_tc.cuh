@@ -1,6 +1,6 @@
 // Multi-head attention (head dim 64) on tcgen05/TMEM for the DETR encoder self-attention and decoder cross-attention
 // (nn.MultiheadAttention inside third_party/act/detr/models/transformer.py:166-179,229-250; 8 heads x 64, no masks,
-// dropout off at eval). One CTA = one (episode, head, 128-query tile), 8 warps, two CTAs per SM.
+// dropout off at eval). One CTA = one (episode, head, 128-query tile), 8 softmax warps + 1 issuer warp, two CTAs per SM.
 //
 // Sequence lengths here are short (S = 2 + 300*Ncam = 302..902 keys), so the softmax is done in two sweeps over the
 // keys instead of an online-rescaled single sweep:
@@ -10,8 +10,11 @@
 //   * warp w owns TMEM lanes 32*(w%4).. (one query row per thread) and key columns 64*(w/4)..+63 of each S tile: two
 //     threads per row, row max / row sum combined through shared memory once per sweep;
 //   * the per-element work is FFMA + EX2 + FADD + half a pack; key masking only runs on the last (ragged) key block;
-//   * S(g+1) is issued right behind PV(g), and K / V tiles arrive by TMA two blocks ahead, so the tensor pipe and the
-//     loads run under the softmax of the co-resident CTA and of this CTA's next block.
+//   * a ninth warp issues every TMA load and MMA, driven by two mbarriers the softmax warps arrive on ("S is in
+//     registers", "P is in shared memory"): S(g+1) goes to the tensor pipe the moment S(g) has left TMEM, under the
+//     softmax arithmetic of block g, and no softmax warp ever waits for another one's issue work (with thread 0 as the
+//     issuer, 31 % of the stall samples sat on the two __syncthreads per block: ncu, profiles/r01n_*);
+//   * K / V tiles arrive by TMA two blocks ahead.
 //   Q: K-major A operand [128 q x 64 d];  K: K-major B operand [128 kv x 64 d];
 //   P: K-major A operand [128 q x 128 kv] (two 64-wide swizzle atoms);  V: MN-major B operand [64 d x 128 kv].
 #pragma once
@@ -31,7 +34,7 @@ struct AttnParams {
   int ld_out;
 };
 
-constexpr int kAttnThreads = 256;
+constexpr int kAttnThreads = 288;   // warps 0-7: softmax (one query row x 64 keys per thread), warp 8: TMA + MMA issuer
 // 112 KB of tiles + barriers: two CTAs must fit one SM's 228 KB (each also pays 1 KB of system-reserved shared memory),
 // so there is no alignment slack (the dynamic window is declared 1024-byte aligned and checked) and the row statistics
 // exchanged between the two column halves alias tile buffers that are idle at that moment.
@@ -68,7 +71,9 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
   uint64_t* v_bar = bars + 3;           // [2] V block landed (stage = kt & 1)
   uint64_t* s_bar = bars + 5;           // S = QK^T complete
   uint64_t* o_bar = bars + 6;           // O += PV complete
-  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 7);
+  uint64_t* sc_bar = bars + 7;          // S read out of TMEM by the eight softmax warps
+  uint64_t* pr_bar = bars + 8;          // P tile written by the eight softmax warps
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 9);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int quarter = warp & 3, half = warp >> 2;
@@ -84,6 +89,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
     mbar_init(&k_bar[0], 1); mbar_init(&k_bar[1], 1);
     mbar_init(&v_bar[0], 1); mbar_init(&v_bar[1], 1);
     mbar_init(s_bar, 1); mbar_init(o_bar, 1);
+    mbar_init(sc_bar, 8); mbar_init(pr_bar, 8);
     fence_mbar_init();
     prefetch_tmap(&tmap_q); prefetch_tmap(&tmap_k); prefetch_tmap(&tmap_v);
   }
@@ -99,7 +105,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
   constexpr uint32_t kIdescS = make_idesc_f16(128, 128, false, false);   // S[128 q,128 kv] = Q * K^T
   constexpr uint32_t kIdescO = make_idesc_f16(128, 64, false, true);     // O[128 q, 64 d] = P * V (V is MN-major)
 
-  // ---- single-thread helpers (tid 0): TMA loads and MMA issue
+  // ---- single-thread helpers (warp 8, lane 0): TMA loads and MMA issue
   auto load_k = [&](int g) {                  // K block of step g (both sweeps walk the same blocks) -> stage g & 1
     const int st = g & 1;
     mbar_arrive_expect_tx(&k_bar[st], 16384u);
@@ -132,87 +138,100 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
     umma_commit(o_bar);
   };
 
-  if (tid == 0) {
-    mbar_arrive_expect_tx(q_bar, 16384u);
-    tma_load_3d(sQ, &tmap_q, q_bar, p.q_col0 + head * 64, qt * 128, p.q_shared ? 0 : b);
-    load_k(0);
-    load_k(1);                                 // total >= 2 always
-    mbar_wait(q_bar, 0);
-    issue_s(0);
-  }
-
-  float row_max = -INFINITY, row_sum = 0.f, mscaled = 0.f;
-  const uint32_t p_row = smem_u32(sP) + half * 16384 + row * 128;   // this thread's 64 keys = swizzle atom `half`
-  for (int g = 0; g < total; ++g) {
-    const int sweep = (g >= nkt) ? 1 : 0;
-    const int kt = sweep ? g - nkt : g;
-    const bool ragged = (kt == nkt - 1) && ((p.Lk & 127) != 0);
-    const int kcol0 = kt * 128 + half * 64;    // first key of this thread's 64 columns
-    __syncwarp();
-    mbar_wait(s_bar, g & 1);
-    tc_fence_after();
-    uint32_t v[64];
-    tmem_ld_32x32b_x32(tmem_S + lane_off + half * 64, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
-    tmem_ld_32x32b_x32(tmem_S + lane_off + half * 64 + 32, *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
-    tmem_ld_wait();
-    if (sweep == 0) {
-      if (ragged) {
-#pragma unroll
-        for (int i = 0; i < 64; ++i)
-          if (kcol0 + i < p.Lk) row_max = fmaxf(row_max, __uint_as_float(v[i]));
-      } else {
-#pragma unroll
-        for (int i = 0; i < 64; i += 2) row_max = max3(row_max, __uint_as_float(v[i]), __uint_as_float(v[i + 1]));
-      }
-      if (kt == nkt - 1) red_max[half * 128 + row] = row_max;
-    } else {
-      uint32_t pk[32];
-      if (ragged) {
-#pragma unroll
-        for (int i = 0; i < 64; i += 2) {
-          const float p0 = (kcol0 + i < p.Lk) ? fast_exp2(fmaf(__uint_as_float(v[i]), p.scale_log2e, -mscaled)) : 0.f;
-          const float p1 = (kcol0 + i + 1 < p.Lk) ? fast_exp2(fmaf(__uint_as_float(v[i + 1]), p.scale_log2e, -mscaled)) : 0.f;
-          row_sum += p0 + p1;
-          pk[i >> 1] = pack_act2(p0, p1);
-        }
-      } else {
-#pragma unroll
-        for (int i = 0; i < 64; i += 2) {
-          const float p0 = fast_exp2(fmaf(__uint_as_float(v[i]), p.scale_log2e, -mscaled));
-          const float p1 = fast_exp2(fmaf(__uint_as_float(v[i + 1]), p.scale_log2e, -mscaled));
-          row_sum += p0 + p1;
-          pk[i >> 1] = pack_act2(p0, p1);
-        }
-      }
-      if (kt > 0) {                            // PV of the previous block has finished reading the P tile
-        mbar_wait(o_bar, (kt - 1) & 1);
+  if (warp == 8) {
+    // ------------------------------------------------------------ issuer: TMA loads and MMAs, off the softmax warps' path
+    if (lane == 0) {
+      mbar_arrive_expect_tx(q_bar, 16384u);
+      tma_load_3d(sQ, &tmap_q, q_bar, p.q_col0 + head * 64, qt * 128, p.q_shared ? 0 : b);
+      load_k(0);
+      load_k(1);                               // total >= 2 always
+      mbar_wait(q_bar, 0);
+      issue_s(0);
+      for (int g = 0; g < total; ++g) {
+        mbar_wait(sc_bar, g & 1);              // S(g) is in registers in all eight warps
         tc_fence_after();
+        if (g + 1 < total) issue_s(g + 1);     // runs under this block's softmax arithmetic
+        if (g + 2 < total) load_k(g + 2);      // stage g & 1: S(g) is complete
+        if (g == nkt - 1) load_v(0);
+        if (g >= nkt) {
+          const int kt = g - nkt;
+          mbar_wait(pr_bar, kt & 1);           // P(kt) is in shared memory; its writers had waited for PV(kt - 1)
+          if (kt + 1 < nkt) load_v(kt + 1);    // stage (kt + 1) & 1, last read by PV(kt - 1)
+          issue_pv(kt);
+        }
       }
-#pragma unroll
-      for (int j = 0; j < 8; ++j)
-        st_shared_v4(p_row + ((j ^ (row & 7)) << 4), pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
-      fence_proxy_async_smem();                // generic-proxy smem writes -> visible to the tensor core (async proxy)
     }
-    tc_fence_before();
-    __syncthreads();
-    if (tid == 0) {
+  } else {
+    // ------------------------------------------------------------ softmax warps 0..7
+    float row_max = -INFINITY, row_sum = 0.f, mscaled = 0.f;
+    const uint32_t p_row = smem_u32(sP) + half * 16384 + row * 128;   // this thread's 64 keys = swizzle atom `half`
+    for (int g = 0; g < total; ++g) {
+      const int sweep = (g >= nkt) ? 1 : 0;
+      const int kt = sweep ? g - nkt : g;
+      const bool ragged = (kt == nkt - 1) && ((p.Lk & 127) != 0);
+      const int kcol0 = kt * 128 + half * 64;    // first key of this thread's 64 columns
+      __syncwarp();
+      mbar_wait(s_bar, g & 1);
       tc_fence_after();
-      if (sweep == 1) issue_pv(kt);
-      if (g + 1 < total) issue_s(g + 1);
-      if (g + 2 < total) load_k(g + 2);        // stage g & 1: S(g) has been consumed
-      if (g + 1 >= nkt && g + 1 < total) load_v(g + 1 - nkt);   // stage last read by PV two blocks ago (o_bar waited)
+      uint32_t v[64];
+      tmem_ld_32x32b_x32(tmem_S + lane_off + half * 64, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
+      tmem_ld_32x32b_x32(tmem_S + lane_off + half * 64 + 32, *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
+      tmem_ld_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(sc_bar);        // 8 arrivals: the S buffer may be overwritten
+      if (sweep == 0) {
+        if (ragged) {
+#pragma unroll
+          for (int i = 0; i < 64; ++i)
+            if (kcol0 + i < p.Lk) row_max = fmaxf(row_max, __uint_as_float(v[i]));
+        } else {
+#pragma unroll
+          for (int i = 0; i < 64; i += 2) row_max = max3(row_max, __uint_as_float(v[i]), __uint_as_float(v[i + 1]));
+        }
+        if (kt == nkt - 1) {                     // exact row maximum over both column halves
+          red_max[half * 128 + row] = row_max;
+          named_bar_sync(1, 256);
+          row_max = fmaxf(row_max, red_max[(half ^ 1) * 128 + row]);
+          mscaled = row_max * p.scale_log2e;
+        }
+      } else {
+        uint32_t pk[32];
+        if (ragged) {
+#pragma unroll
+          for (int i = 0; i < 64; i += 2) {
+            const float p0 = (kcol0 + i < p.Lk) ? fast_exp2(fmaf(__uint_as_float(v[i]), p.scale_log2e, -mscaled)) : 0.f;
+            const float p1 = (kcol0 + i + 1 < p.Lk) ? fast_exp2(fmaf(__uint_as_float(v[i + 1]), p.scale_log2e, -mscaled)) : 0.f;
+            row_sum += p0 + p1;
+            pk[i >> 1] = pack_act2(p0, p1);
+          }
+        } else {
+#pragma unroll
+          for (int i = 0; i < 64; i += 2) {
+            const float p0 = fast_exp2(fmaf(__uint_as_float(v[i]), p.scale_log2e, -mscaled));
+            const float p1 = fast_exp2(fmaf(__uint_as_float(v[i + 1]), p.scale_log2e, -mscaled));
+            row_sum += p0 + p1;
+            pk[i >> 1] = pack_act2(p0, p1);
+          }
+        }
+        if (kt > 0) {                            // PV of the previous block has finished reading the P tile
+          mbar_wait(o_bar, (kt - 1) & 1);
+          tc_fence_after();
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          st_shared_v4(p_row + ((j ^ (row & 7)) << 4), pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+        fence_proxy_async_smem();                // generic-proxy smem writes -> visible to the tensor core (async proxy)
+        __syncwarp();
+        if (lane == 0) mbar_arrive(pr_bar);      // 8 arrivals: PV(kt) may be issued
+      }
     }
-    if (sweep == 0 && kt == nkt - 1) {          // exact row maximum over both column halves
-      row_max = fmaxf(row_max, red_max[(half ^ 1) * 128 + row]);
-      mscaled = row_max * p.scale_log2e;
-    }
-  }
-  __syncwarp();
-  red_sum[half * 128 + row] = row_sum;
-  mbar_wait(o_bar, (nkt - 1) & 1);
-  tc_fence_after();
-  __syncthreads();
-  const float inv = 1.0f / (row_sum + red_sum[(half ^ 1) * 128 + row]);
+    __syncwarp();
+    red_sum[half * 128 + row] = row_sum;
+    mbar_wait(o_bar, (nkt - 1) & 1);
+    tc_fence_after();
+    named_bar_sync(1, 256);
+    const float inv = 1.0f / (row_sum + red_sum[(half ^ 1) * 128 + row]);
 
   // O tile: this thread writes 32 of the head's 64 output columns of its query row
   const int q = qt * 128 + row;
@@ -231,6 +250,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
                        pack_act2(__uint_as_float(o[8 * i + 6]) * inv, __uint_as_float(o[8 * i + 7]) * inv));
     }
   }
+  }   // softmax warps
   tc_fence_before();
   __syncthreads();
   if (warp == 0) { tc_fence_after(); tmem_dealloc(tmem_base, 256); }
