@@ -613,7 +613,7 @@ static int forward_impl(rmb_act_engine_t* e, const void* d_images, int image_for
     return 0;
   };
   auto run_gemm = [&](const char* name, const GemmPlan& g, double a_bytes) -> int {
-    begin(name, "gemm_tc_kernel", (double)g.flops, gemm_bytes(g, a_bytes));
+    begin(name, g.pair ? "gemm_tc_pair_kernel" : "gemm_tc_kernel", (double)g.flops, gemm_bytes(g, a_bytes));
     RMB_CUDA(launch_gemm(g, sms, s));
     end();
     return 0;

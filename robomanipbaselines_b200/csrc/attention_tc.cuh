@@ -84,14 +84,19 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
   const int nkt = (p.Lk + 127) / 128;
   const int total = 2 * nkt;
 
-  if (tid == 0) {
+  if (tid == 256) {   // issuer thread: barriers, then Q and the first two K blocks go out under the TMEM allocation + CTA sync
     mbar_init(q_bar, 1);
     mbar_init(&k_bar[0], 1); mbar_init(&k_bar[1], 1);
     mbar_init(&v_bar[0], 1); mbar_init(&v_bar[1], 1);
     mbar_init(s_bar, 1); mbar_init(o_bar, 1);
     mbar_init(sc_bar, 8); mbar_init(pr_bar, 8);
     fence_mbar_init();
-    prefetch_tmap(&tmap_q); prefetch_tmap(&tmap_k); prefetch_tmap(&tmap_v);
+    mbar_arrive_expect_tx(q_bar, 16384u);
+    tma_load_3d(sQ, &tmap_q, q_bar, p.q_col0 + head * 64, qt * 128, p.q_shared ? 0 : b);
+    mbar_arrive_expect_tx(&k_bar[0], 16384u);
+    tma_load_3d(sK, &tmap_k, &k_bar[0], p.k_col0 + head * 64, 0, b);
+    mbar_arrive_expect_tx(&k_bar[1], 16384u);                        // total >= 2 always: block 1, or block 0 of sweep 1
+    tma_load_3d(sK + 16384, &tmap_k, &k_bar[1], p.k_col0 + head * 64, (1 % nkt) * 128, b);
   }
   if (warp == 0) { __syncwarp(); tmem_alloc(tmem_ptr_smem, 256); tmem_relinquish(); }
   tc_fence_before();
@@ -141,10 +146,6 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
   if (warp == 8) {
     // ------------------------------------------------------------ issuer: TMA loads and MMAs, off the softmax warps' path
     if (lane == 0) {
-      mbar_arrive_expect_tx(q_bar, 16384u);
-      tma_load_3d(sQ, &tmap_q, q_bar, p.q_col0 + head * 64, qt * 128, p.q_shared ? 0 : b);
-      load_k(0);
-      load_k(1);                               // total >= 2 always
       mbar_wait(q_bar, 0);
       issue_s(0);
       for (int g = 0; g < total; ++g) {

@@ -548,13 +548,13 @@ static int unet_run_eval(rmb_unet_engine* e, rmb_unet_engine::Plans* pl, int nb,
   const float* film_t_row = e->film_t + (size_t)t * e->film_total;
   for (auto& op : pl->ops) {
     if (op.kind == 0) {
-      begin(op.name, "gemm_tc_kernel", (double)op.g.flops, op.bytes);
+      begin(op.name, op.g.pair ? "gemm_tc_pair_kernel" : "gemm_tc_kernel", (double)op.g.flops, op.bytes);
       RMB_CUDA(launch_gemm(op.g, e->num_sms, s));
       end();
     } else if (op.kind == 2) {
       GemmPlan g = op.g;
       g.p.gn_film_t = film_t_row;
-      begin(op.name, "gemm_tc_kernel<gn>", (double)op.g.flops, op.bytes);
+      begin(op.name, g.pair ? "gemm_tc_pair_kernel<gn>" : "gemm_tc_kernel<gn>", (double)op.g.flops, op.bytes);
       RMB_CUDA(launch_gemm_gn(g, e->num_sms, s));
       end();
     } else {
