@@ -30,6 +30,7 @@ struct HaloParams {
   uint32_t box_bytes;                 // bytes one box deposits (expect_tx)
   uint32_t stage_bytes;               // box_bytes rounded up to 1024
   int n_stages;
+  int out_bufs;                       // staging tiles per epilogue group (2: the TMA store of tile i overlaps the packing of tile i+1)
   int n_taps;
   uint32_t tap_aoff[kMaxTaps];        // byte offset of the tap's first A row inside its box (multiple of 8 rows)
   int tap_w[kMaxTaps];                // index of the tap's 64 x BLOCK_K weight slice in the resident weights
@@ -38,10 +39,10 @@ struct HaloParams {
 template <int BLOCK_K>
 struct HaloSmem {
   static constexpr int kWTapBytes = 64 * BLOCK_K * 2;
-  static constexpr int kStagingBytes = 2 * 16384;   // epilogue: one output tile (128 px x 64 ch act_t) per epilogue group
+  static constexpr int kStagingTileBytes = 16384;   // epilogue: one output tile (128 px x 64 ch act_t); 2 groups x out_bufs of them
   static constexpr int kBarrierBytes = 256;
-  static int total(int n_taps, int n_stages, uint32_t stage_bytes) {
-    return n_taps * kWTapBytes + n_stages * static_cast<int>(stage_bytes) + kStagingBytes + kBarrierBytes + 1024;
+  static int total(int n_taps, int n_stages, uint32_t stage_bytes, int out_bufs) {
+    return n_taps * kWTapBytes + n_stages * static_cast<int>(stage_bytes) + 2 * out_bufs * kStagingTileBytes + kBarrierBytes + 1024;
   }
 };
 
@@ -53,7 +54,7 @@ struct HaloSmem {
 // output channels. The residual (identity branch of the BasicBlock) is the thread's own 128-byte row, prefetched into
 // registers before the accumulator is waited for.
 template <int RES>
-__device__ __forceinline__ void halo_epilogue(const CUtensorMap* tmap_out, const GemmParams& p, uint8_t* out_stage_base,
+__device__ __forceinline__ void halo_epilogue(const CUtensorMap* tmap_out, const GemmParams& p, int out_bufs, uint8_t* out_stage_base,
                                               uint32_t tmem_base, uint64_t* tmem_full_bar, uint64_t* tmem_empty_bar,
                                               int total_tiles, int warp, int lane) {
   const int q = warp & 3, grp = warp >> 2;
@@ -61,7 +62,8 @@ __device__ __forceinline__ void halo_epilogue(const CUtensorMap* tmap_out, const
   const bool issuer = (q == 0 && lane == 0);
   const int wl = r % p.box_w, hl = r / p.box_w;
   const float relu_floor = p.relu ? 0.0f : -INFINITY;
-  const uint32_t out_base = smem_u32(out_stage_base + grp * 16384);
+  const uint32_t out_base0 = smem_u32(out_stage_base + grp * out_bufs * 16384);
+  uint32_t buf = 0;
   uint32_t off[8];                                   // this thread's eight 16-byte chunks inside its 128-byte row
 #pragma unroll
   for (int c = 0; c < 8; ++c) off[c] = r * 128 + ((c ^ (r & 7)) << 4);
@@ -95,7 +97,8 @@ __device__ __forceinline__ void halo_epilogue(const CUtensorMap* tmap_out, const
     tc_fence_before();
     __syncwarp();
     if (lane == 0) mbar_arrive(&tmem_empty_bar[grp]);           // 4 arrivals free this group's accumulator
-    if (issuer) bulk_wait_group_read0();                        // this group's previous store has read its staging tile
+    const uint32_t out_base = out_base0 + buf * 16384;
+    if (issuer) { if (out_bufs == 2) bulk_wait_group_read1(); else bulk_wait_group_read0(); }   // the store that last used this staging tile has read it
     named_bar_sync(1 + grp, 128);
 #pragma unroll
     for (int c = 0; c < 8; ++c) {
@@ -130,6 +133,7 @@ __device__ __forceinline__ void halo_epilogue(const CUtensorMap* tmap_out, const
       bulk_commit_group();
     }
     acc_phase ^= 1;
+    if (out_bufs == 2) buf ^= 1;
   }
   if (issuer) bulk_wait_group0();
 }
@@ -152,7 +156,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   uint8_t* smem_w = smem;
   uint8_t* smem_a = smem_w + hp.n_taps * S::kWTapBytes;
   uint8_t* smem_stage = smem_a + hp.n_stages * hp.stage_bytes;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_stage + S::kStagingBytes);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_stage + 2 * hp.out_bufs * S::kStagingTileBytes);
   uint64_t* full_bar = bars;                              // [kHaloMaxStages]
   uint64_t* empty_bar = bars + kHaloMaxStages;            // [kHaloMaxStages]
   uint64_t* tmem_full_bar = bars + 2 * kHaloMaxStages;    // [2]
@@ -254,7 +258,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
   } else {
-    halo_epilogue<RES>(&tmap_out, p, smem_stage, tmem_base, tmem_full_bar, tmem_empty_bar, total_tiles, warp, lane);
+    halo_epilogue<RES>(&tmap_out, p, hp.out_bufs, smem_stage, tmem_base, tmem_full_bar, tmem_empty_bar, total_tiles, warp, lane);
   }
 
   tc_fence_before();

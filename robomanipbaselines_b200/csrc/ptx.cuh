@@ -179,6 +179,7 @@ __device__ __forceinline__ void tma_store_5d(const void* tmap, uint32_t smem_src
 }
 __device__ __forceinline__ void bulk_commit_group() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_group_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_group_read1() { asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_group0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 // named barrier over `nthreads` threads (a multiple of 32) of the CTA
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
