@@ -28,7 +28,7 @@ cudaError_t launch_gemm_gn_instance(const GemmPlan& g, int num_sms, cudaStream_t
     if (e != cudaSuccess) return e;
     attr_set = true;
   }
-  kern<<<gemm_grid(g, num_sms), kGemmThreads, S::kTotal, stream>>>(g.ta, g.tb, g.p);
+  kern<<<gemm_grid(g, num_sms), kGemmThreads, S::kTotal, stream>>>(g.ta, g.tb, g.ta, g.p);
   return cudaGetLastError();
 }
 

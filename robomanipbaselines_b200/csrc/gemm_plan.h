@@ -13,9 +13,10 @@
 namespace rmb {
 
 struct GemmPlan {
-  CUtensorMap ta, tb;
+  CUtensorMap ta, tb, tout;   // tout: [rows, N] 16-bit output in 64-column x 128-row boxes (tma_out launches only)
   GemmParams p;
   int block_n = 0, block_k = 0;
+  bool tma_out = false;  // epilogue stores through tout (plain matrices, 16-bit output, no residual, no row remap)
   bool pair = false;     // launch gemm_tc_pair_kernel (tb's box then holds block_n / 2 weight rows)
   long long flops = 0;   // 2*rows*N*K of useful work (for reporting)
 };
@@ -94,6 +95,14 @@ inline bool plan_linear(GemmPlan* g, const void* A, long long M, int K, int lda,
   g->pair = gemm_use_pair(p);
   const uint32_t wbox[2] = {64, static_cast<uint32_t>(g->pair ? g->block_n / 2 : g->block_n)};
   if (!make_tmap_act(&g->tb, Wt, 2, wdims, wstr, wbox, 128, err)) return false;
+  static const bool no_tma_out = [] { const char* e = getenv("RMB_GEMM_NO_TMA_OUT"); return e != nullptr && e[0] == '1'; }();
+  if (!out_f32 && residual == nullptr && !no_tma_out && M >= 128) {
+    const uint64_t odims[2] = {static_cast<uint64_t>(N), static_cast<uint64_t>(M)};
+    const uint64_t ostr[1] = {static_cast<uint64_t>(ld_out) * 2};
+    const uint32_t obox[2] = {64, 128};
+    if (!make_tmap_act(&g->tout, out, 2, odims, ostr, obox, 128, err)) return false;
+    g->tma_out = true;
+  }
   g->flops = 2ll * M * N * K;
   return true;
 }
@@ -200,18 +209,18 @@ inline int gemm_grid(const GemmPlan& g, int num_sms) {
   return 2 * static_cast<int>(std::min<long long>((row_tiles + 1) / 2 * g.p.n_col_tiles, num_sms / 2));
 }
 
-template <int BN, int BK, int ST, bool OUT_F32, int RES, bool PAIR>
+template <int BN, int BK, int ST, bool OUT_F32, int RES, bool PAIR, int EPI = 0>
 inline cudaError_t launch_gemm_instance(const GemmPlan& g, int num_sms, cudaStream_t stream) {
-  using S = GemmSmem<BN, BK, ST, PAIR>;
+  using S = GemmSmem<BN, BK, ST, PAIR, EPI>;
   static_assert(S::kTotal <= 232448, "shared memory");
-  auto kern = PAIR ? gemm_tc_pair_kernel<BN, BK, ST, OUT_F32, RES> : gemm_tc_kernel<BN, BK, ST, OUT_F32, RES>;
+  auto kern = PAIR ? gemm_tc_pair_kernel<BN, BK, ST, OUT_F32, RES, EPI> : gemm_tc_kernel<BN, BK, ST, OUT_F32, RES, EPI>;
   static bool attr_set = false;
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal);
     if (e != cudaSuccess) return e;
     attr_set = true;
   }
-  kern<<<gemm_grid(g, num_sms), kGemmThreads, S::kTotal, stream>>>(g.ta, g.tb, g.p);
+  kern<<<gemm_grid(g, num_sms), kGemmThreads, S::kTotal, stream>>>(g.ta, g.tb, g.tma_out ? g.tout : g.ta, g.p);
   return cudaGetLastError();
 }
 
@@ -221,6 +230,9 @@ template <int BN, int BK, int ST, bool PAIR>
 inline cudaError_t launch_gemm_variant(const GemmPlan& g, int num_sms, cudaStream_t stream) {
   const bool has_res = g.p.residual != nullptr;
   if (!g.p.out_f32) {
+    if constexpr (BK == 64) {
+      if (!has_res && g.tma_out) return launch_gemm_instance<BN, BK, ST, false, 0, PAIR, 3>(g, num_sms, stream);
+    }
     if (!has_res) return launch_gemm_instance<BN, BK, ST, false, 0, PAIR>(g, num_sms, stream);
     if (!g.p.res_f32) return launch_gemm_instance<BN, BK, ST, false, 1, PAIR>(g, num_sms, stream);
   } else {

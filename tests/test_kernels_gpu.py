@@ -32,6 +32,9 @@ def _report(name, got, ref):
     (1204, 512, 3200, 2 | 4), (77, 1024, 512, 2), (4096, 512, 512, 0), (20000, 256, 576, 1),
     # CTA-pair launches (a tile per SM): even / odd row-tile counts, ragged last column tile (N = 3200, 1088), residuals
     (19000, 256, 128, 0), (4700, 3200, 512, 1), (38001, 64, 64, 2), (9000, 1088, 192, 2 | 4), (5000, 1024, 256, 0),
+    # bit 3: no residual -> 16-bit outputs go through the TMA-store epilogue (single CTA and pair, ragged M and N)
+    (300, 512, 512, 8 | 1), (129, 128, 64, 8), (1000, 3200, 512, 8 | 1), (4700, 3200, 512, 8 | 1), (19000, 256, 128, 8),
+    (38001, 64, 64, 8), (77, 1024, 512, 8), (9000, 1088, 192, 8), (5000, 1024, 256, 8 | 2),
 ])
 def test_gemm(lib, cuda, M, N, K, flags):
     g = torch.Generator(device="cpu").manual_seed(M * 7 + N * 3 + K)
@@ -43,9 +46,11 @@ def test_gemm(lib, cuda, M, N, K, flags):
     if not res_f32:
         res = _bf16(res)
     out = torch.empty(M, N, device=cuda, dtype=torch.float32 if flags & 2 else _act_dtype())
-    check(lib.rmb_gemm(ptr(A), ptr(W), ptr(bias), ptr(res), ptr(out), M, N, K, flags, cur_stream()), "gemm")
+    use_res = not (flags & 8)
+    out.fill_(-77.0)
+    check(lib.rmb_gemm(ptr(A), ptr(W), ptr(bias), ptr(res) if use_res else None, ptr(out), M, N, K, flags & 7, cur_stream()), "gemm")
     torch.cuda.synchronize()
-    ref = A.float() @ W.float().t() + bias + res.float()
+    ref = A.float() @ W.float().t() + bias + (res.float() if use_res else 0.0)
     if flags & 1:
         ref = ref.relu()
     err, scale = _report(f"gemm {M}x{N}x{K} f{flags}", out, ref)
