@@ -133,6 +133,15 @@ __device__ __forceinline__ void gemm_epilogue(const GemmParams& p, uint8_t* smem
         my_orow = (b / p.remap_ncam) * p.remap_L + p.remap_off + h * (p.W * p.remap_ncam) + (b % p.remap_ncam) * p.W + w;
     }
     const int col0 = ct * BLOCK_N + col_in_tile;
+    if (RES != 0 && my_grow >= 0) {
+      // this row's residual segments of the tile go to L2 now, while the accumulator is still being built: the loads
+      // in pass 2 then see L2 latency instead of HBM latency (no registers to hold them across the chunk loop)
+      const char* rrow = static_cast<const char*>(p.residual) +
+                         (static_cast<long long>(my_grow) * p.ld_res + ct * BLOCK_N + half * 32) * kResEsz;
+#pragma unroll
+      for (int j = 0; j < kChunksPerWarp; ++j)
+        if (ct * BLOCK_N + half * 32 + j * 64 < p.n_valid) prefetch_l2(rrow + j * 64 * kResEsz);
+    }
     char* optr[8];
     const char* rptr[8];
   #pragma unroll
