@@ -458,6 +458,17 @@ def main():
                                   "tflops": (v["flops"] / (v["ms"] * 1e-3) / 1e12) if v["ms"] > 0 else None}
                               for k, v in by_kernel.items()},
         }
+        # DRAM bytes per launch of the dominant kernel: from the committed ncu capture of this same command (bench.py never
+        # runs a profiler itself); mean over the launches of one step, like `achieved`
+        tpath = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01o_gemm_pair_dram_traffic.json")
+        if dom == "gemm_tc_pair_kernel" and B == 256 and os.path.exists(tpath):
+            with open(tpath) as f:
+                tj = json.load(f)
+            if tj.get("launches") == d["launches"]:
+                roofline["traffic"] = tj["dram_bytes_per_launch_mean"]
+                roofline["traffic_unit"] = "bytes/launch (dram__bytes_read.sum + dram__bytes_write.sum)"
+                roofline["traffic_source"] = "profiles/r01o_gemm_pair_dram_traffic.json"
+                roofline["algorithmic_bytes_per_launch"] = d["bytes"] / d["launches"]
         n_launch = eng.num_launches + 2      # + normalize_state + ensemble_step
         line = {
             "metric": METRIC, "value": world * B * K / (ms_total * 1e-3), "unit": UNIT, "n_gpus": world, "steps": K,
