@@ -23,12 +23,14 @@ cudaError_t launch_gemm_gn_instance(const GemmPlan& g, int num_sms, cudaStream_t
   static_assert(S::kTotal <= 232448, "shared memory");
   auto kern = PAIR ? gemm_tc_pair_kernel<BN, 64, ST, false, 0, EPI> : gemm_tc_kernel<BN, 64, ST, false, 0, EPI>;
   static bool attr_set = false;
+  static int max_pairs = 0;
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal);
     if (e != cudaSuccess) return e;
+    max_pairs = PAIR ? max_active_pairs(kern, S::kTotal, num_sms) : 0;
     attr_set = true;
   }
-  kern<<<gemm_grid(g, num_sms), kGemmThreads, S::kTotal, stream>>>(g.ta, g.tb, g.ta, g.p);
+  kern<<<gemm_grid(g, num_sms, max_pairs), kGemmThreads, S::kTotal, stream>>>(g.ta, g.tb, g.ta, g.p);
   return cudaGetLastError();
 }
 
@@ -565,7 +567,7 @@ static int unet_run_eval(rmb_unet_engine* e, rmb_unet_engine::Plans* pl, int nb,
       end();
     }
   }
-  const int smem = (fin.gn.T * fin.gn.C + fin.gn.T * fin.Da) * (int)sizeof(float);
+  const int smem = (fin.gn.T * fin.gn.C + 3 * fin.gn.T * fin.Da) * (int)sizeof(float);
   static bool attr_set = false;
   if (!attr_set) {
     RMB_CUDA(cudaFuncSetAttribute(unet_final_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));

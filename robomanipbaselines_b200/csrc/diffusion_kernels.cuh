@@ -179,7 +179,7 @@ __global__ void __launch_bounds__(256) sched_step_kernel(const float* __restrict
   }
 }
 
-// dynamic smem: T*C floats (normalised activations) + T*Da floats (new x)
+// dynamic smem: T*C floats (normalised activations) + 3 * T*Da floats (new x, current x, noise)
 __global__ void __launch_bounds__(256) unet_final_step_kernel(const FinalParams p) {
   extern __shared__ float fs_smem[];
   float* ys = fs_smem;
@@ -187,6 +187,15 @@ __global__ void __launch_bounds__(256) unet_final_step_kernel(const FinalParams 
   const int b = blockIdx.x, g = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int C = p.gn.C, T = p.gn.T, Da = p.Da;
   const int Cg = C >> 3, vpr = Cg >> 2, nvec = T * vpr;
+  float* x_in = xs + T * Da;
+  float* nz_in = x_in + T * Da;
+  // the sample's current x and this step's noise are fetched now, under the GroupNorm pass: the head loop below would
+  // otherwise pay one HBM round trip per output element in its single-lane tail
+  for (int i = threadIdx.x; i < T * Da; i += 256) {
+    const long long gi = static_cast<long long>(b) * T * Da + i;
+    x_in[i] = p.x[gi];
+    nz_in[i] = (p.noise != nullptr && p.st.kind != 2) ? __ldg(p.noise + gi) : 0.0f;
+  }
   {
     float4 v[kGnMaxVec];
     float mean, rstd;
@@ -220,10 +229,9 @@ __global__ void __launch_bounds__(256) unet_final_step_kernel(const FinalParams 
       const long long gi = (static_cast<long long>(b) * T + t) * Da + a;
       if (p.st.kind == 2) {
         p.model_out[gi] = out;
-        xs[o] = p.x[gi];
+        xs[o] = x_in[o];
       } else {
-        const float nz = (p.noise != nullptr) ? __ldg(p.noise + gi) : 0.0f;
-        const float xn = sched_step(p.st, p.x[gi], out, nz);
+        const float xn = sched_step(p.st, x_in[o], out, nz_in[o]);
         p.x[gi] = xn;
         xs[o] = xn;
       }

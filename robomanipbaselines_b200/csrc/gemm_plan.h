@@ -1,5 +1,6 @@
 // Host-side planning of gemm_tc_kernel launches: tensor maps, tap tables, row tiling.
 #pragma once
+#include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
 
@@ -202,11 +203,29 @@ inline bool plan_conv1(GemmPlan* g, const void* in_padded, int B, int H, int W, 
   return true;
 }
 
-// grid of a persistent GEMM launch: one CTA per SM, or one cluster of two per SM pair
-inline int gemm_grid(const GemmPlan& g, int num_sms) {
+// grid of a persistent GEMM launch: one CTA per SM, or one cluster of two per co-schedulable SM pair
+inline int gemm_grid(const GemmPlan& g, int num_sms, int max_pairs) {
   const long long row_tiles = 1ll * g.p.tiles_w * g.p.tiles_h * g.p.tiles_b;
   if (!g.pair) return static_cast<int>(std::min<long long>(row_tiles * g.p.n_col_tiles, num_sms));
-  return 2 * static_cast<int>(std::min<long long>((row_tiles + 1) / 2 * g.p.n_col_tiles, num_sms / 2));
+  return 2 * static_cast<int>(std::min<long long>((row_tiles + 1) / 2 * g.p.n_col_tiles, max_pairs));
+}
+
+// How many 2-CTA clusters of `kern` the device can hold at once (a GPC with an odd number of usable SMs leaves one out):
+// the persistent pair kernels must not launch more, or the surplus clusters would run as a second wave.
+template <typename K>
+inline int max_active_pairs(K kern, int smem_bytes, int num_sms) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(static_cast<unsigned>(num_sms & ~1), 1, 1);
+  cfg.blockDim = dim3(kGemmThreads, 1, 1);
+  cfg.dynamicSmemBytes = static_cast<size_t>(smem_bytes);
+  cudaLaunchAttribute attr;
+  attr.id = cudaLaunchAttributeClusterDimension;
+  attr.val.clusterDim.x = 2; attr.val.clusterDim.y = 1; attr.val.clusterDim.z = 1;
+  cfg.attrs = &attr; cfg.numAttrs = 1;
+  int n = 0;
+  if (cudaOccupancyMaxActiveClusters(&n, kern, &cfg) != cudaSuccess || n <= 0) { (void)cudaGetLastError(); n = num_sms / 2; }
+  if (getenv("RMB_VERBOSE")) fprintf(stderr, "[rmb] co-resident 2-CTA clusters: %d (%d SMs, %d B smem)\n", n, num_sms, smem_bytes);
+  return std::min(n, num_sms / 2);
 }
 
 template <int BN, int BK, int ST, bool OUT_F32, int RES, bool PAIR, int EPI = 0>
@@ -215,12 +234,14 @@ inline cudaError_t launch_gemm_instance(const GemmPlan& g, int num_sms, cudaStre
   static_assert(S::kTotal <= 232448, "shared memory");
   auto kern = PAIR ? gemm_tc_pair_kernel<BN, BK, ST, OUT_F32, RES, EPI> : gemm_tc_kernel<BN, BK, ST, OUT_F32, RES, EPI>;
   static bool attr_set = false;
+  static int max_pairs = 0;
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal);
     if (e != cudaSuccess) return e;
+    max_pairs = PAIR ? max_active_pairs(kern, S::kTotal, num_sms) : 0;
     attr_set = true;
   }
-  kern<<<gemm_grid(g, num_sms), kGemmThreads, S::kTotal, stream>>>(g.ta, g.tb, g.tma_out ? g.tout : g.ta, g.p);
+  kern<<<gemm_grid(g, num_sms, max_pairs), kGemmThreads, S::kTotal, stream>>>(g.ta, g.tb, g.tma_out ? g.tout : g.ta, g.p);
   return cudaGetLastError();
 }
 
