@@ -31,11 +31,18 @@ inline bool gemm_use_pair(const GemmParams& p) {
   return !off && (row_tiles % 2 == 0 || row_tiles >= 32) && row_tiles * p.n_col_tiles >= 148;
 }
 
-inline int pick_block_n(int N) {
-  if (N % 256 == 0) return 256;
-  if (N % 128 == 0) return 128;
-  if (N % 64 == 0) return 64;
-  return 0;
+// Column-tile width. Wide tiles re-read the A operand least, so they win whenever there is a tile for every SM; a
+// launch with fewer tiles than SMs (batch-1 latency: 5 row tiles) is bound by the serial k-loop of its few CTAs, and
+// narrower tiles spread the same work over up to 4x as many SMs (K = 3200 FFN-down at batch 1: 31 us with 10 tiles).
+inline int pick_block_n(int N, long long row_tiles = 1 << 20) {
+  const int cand[3] = {256, 128, 64};
+  int smallest = 0;
+  for (int bn : cand) {
+    if (N % bn != 0) continue;
+    if (row_tiles * (N / bn) >= 148) return bn;
+    smallest = bn;
+  }
+  return smallest;
 }
 
 // Choose the pixel box (bw x bh x bb <= 128 rows) that wastes the fewest MMA rows for an OW x OH x B output.
@@ -71,10 +78,10 @@ inline bool plan_linear(GemmPlan* g, const void* A, long long M, int K, int lda,
                         bool out_f32, bool relu, std::string* err) {
   *g = GemmPlan();
   g->block_k = 64;
-  g->block_n = pick_block_n(N);
+  g->block_n = pick_block_n(N, (M + 127) / 128);
   // wide N that 256 does not divide (dim_feedforward 3200): 256-wide tiles with a ragged last one beat 128-wide tiles,
   // whose operand bytes per flop are 4/3 higher; the weight rows past N are TMA zero fill, their columns are not stored
-  const bool ragged = N >= 1024 && N % 256 != 0 && N % 64 == 0;
+  const bool ragged = N >= 1024 && N % 256 != 0 && N % 64 == 0 && ((M + 127) / 128) * ((N + 255) / 256) >= 148;
   if (ragged) g->block_n = 256;
   if (g->block_n == 0 || K % 64 != 0) { if (err) *err = "plan_linear: N must be a multiple of 64 and K of 64"; return false; }
   GemmParams& p = g->p;
@@ -115,8 +122,7 @@ inline bool plan_conv(GemmPlan* g, const void* in, int B, int H, int W, int Cin,
                       bool out_f32, bool relu, std::string* err) {
   *g = GemmPlan();
   g->block_k = 64;
-  g->block_n = pick_block_n(Cout);
-  if (g->block_n == 0 || Cin % 64 != 0) { if (err) *err = "plan_conv: Cout and Cin must be multiples of 64"; return false; }
+  if (Cout % 64 != 0 || Cin % 64 != 0) { if (err) *err = "plan_conv: Cout and Cin must be multiples of 64"; return false; }
   if ((ksize != 1 && ksize != 3) || (stride != 1 && stride != 2)) { if (err) *err = "plan_conv: unsupported k/stride"; return false; }
   if (stride == 2 && (H % 2 != 0 || W % 2 != 0)) { if (err) *err = "plan_conv: stride-2 conv needs even H and W"; return false; }
   const int pad = ksize / 2;
@@ -125,6 +131,7 @@ inline bool plan_conv(GemmPlan* g, const void* in, int B, int H, int W, int Cin,
   pick_box(OW, OH, B, &p.box_w, &p.box_h, &p.box_b);
   p.W = OW; p.H = OH; p.B = B;
   p.tiles_w = (OW + p.box_w - 1) / p.box_w; p.tiles_h = (OH + p.box_h - 1) / p.box_h; p.tiles_b = (B + p.box_b - 1) / p.box_b;
+  g->block_n = pick_block_n(Cout, 1ll * p.tiles_w * p.tiles_h * p.tiles_b);
   p.n_col_tiles = Cout / g->block_n;
   p.num_taps = ksize * ksize; p.chunks_per_tap = Cin / 64;
   for (int t = 0; t < kMaxTaps; ++t) { p.tap_c0[t] = p.tap_d1[t] = p.tap_d2[t] = p.tap_d3[t] = 0; }
