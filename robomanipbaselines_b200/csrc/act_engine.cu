@@ -75,8 +75,7 @@ cudaError_t launch_attention(const AttnPlan& a, cudaStream_t stream) {
     if (e != cudaSuccess) return e;
     attr_set = true;
   }
-  attention_tc_kernel<<<a.grid, kAttnThreads, kAttnSmemBytes, stream>>>(a.tq, a.tk, a.tv, a.p);
-  return cudaGetLastError();
+  return launch_pdl(attention_tc_kernel, dim3(a.grid), dim3(kAttnThreads), kAttnSmemBytes, stream, a.tq, a.tk, a.tv, a.p);
 }
 
 int grid_for(long long work_items, int threads, int num_sms) {
@@ -625,10 +624,10 @@ static int forward_impl(rmb_act_engine_t* e, const void* d_images, int image_for
     const double out_b = (double)NI * H * (W + 8) * 8;
     if (image_format == 0) {
       begin("preprocess_u8", "preprocess_u8_kernel", 0, (double)NI * H * W * 3 + out_b);
-      preprocess_u8_kernel<<<grid_for(items, 256, sms), 256, 0, s>>>(static_cast<const uint8_t*>(d_images), e->x0, NI, H, W, mean, istd);
+      RMB_CUDA(launch_pdl(preprocess_u8_kernel, dim3(grid_for(items, 256, sms)), dim3(256), 0, s, static_cast<const uint8_t*>(d_images), e->x0, NI, H, W, mean, istd));
     } else {
       begin("preprocess_f32", "preprocess_f32_kernel", 0, (double)NI * H * W * 12 + out_b);
-      preprocess_f32_kernel<<<grid_for(items, 256, sms), 256, 0, s>>>(static_cast<const float*>(d_images), e->x0, NI, H, W, mean, istd);
+      RMB_CUDA(launch_pdl(preprocess_f32_kernel, dim3(grid_for(items, 256, sms)), dim3(256), 0, s, static_cast<const float*>(d_images), e->x0, NI, H, W, mean, istd));
     }
     end();
   }
@@ -636,7 +635,7 @@ static int forward_impl(rmb_act_engine_t* e, const void* d_images, int image_for
   {
     const long long items = (long long)NI * (H / 4) * (W / 4) * 8;
     begin("maxpool3x3/2", "maxpool3x3s2_kernel", 0, (double)NI * (H / 2) * (W / 2) * 128 + (double)NI * (H / 4) * (W / 4) * 128);
-    maxpool3x3s2_kernel<<<grid_for(items, 256, sms), 256, 0, s>>>(e->c1, e->stage[0][2], NI, H / 2, W / 2, 64);
+    RMB_CUDA(launch_pdl(maxpool3x3s2_kernel, dim3(grid_for(items, 256, sms)), dim3(256), 0, s, (const act_t*)e->c1, e->stage[0][2], NI, H / 2, W / 2, 64));
     end();
   }
   const int chans[4] = {64, 128, 256, 512};
@@ -660,11 +659,11 @@ static int forward_impl(rmb_act_engine_t* e, const void* d_images, int image_for
   }
   RMB_RUN(run_gemm("input_proj 1x1 -> tokens", bp->input_proj, (double)NI * e->Hf * e->Wf * 512 * 2));
   begin("latent+proprio tokens", "act_extra_tokens_kernel", 0, (double)batch * 2 * 512 * 4);
-  act_extra_tokens_kernel<<<batch, 256, 0, s>>>(d_qpos, c.state_dim, e->latent_bias, e->w_state, e->b_state, e->tok_f32, L);
+  RMB_CUDA(launch_pdl(act_extra_tokens_kernel, dim3(batch), dim3(256), 0, s, d_qpos, c.state_dim, (const float*)e->latent_bias, (const float*)e->w_state, (const float*)e->b_state, e->tok_f32, L));
   end();
   const int ln_grid = grid_for(BL * 32, 256, sms);
   begin("tokens cast(+pos)", "layernorm512_kernel", 0, (double)BL * 512 * (4 + 2 + 2));
-  layernorm512_kernel<<<ln_grid, 256, 0, s>>>(e->tok_f32, nullptr, nullptr, e->pos, L, nullptr, e->tok_b, e->tok_pb, BL, 0, 1e-5f);
+  RMB_CUDA(launch_pdl(layernorm512_kernel, dim3(ln_grid), dim3(256), 0, s, e->tok_f32, nullptr, nullptr, e->pos, L, nullptr, e->tok_b, e->tok_pb, BL, 0, 1e-5f));
   end();
   const double tokb = (double)BL * 512 * 2;
   const double attn_flops = 4.0 * batch * (double)L * L * 512, attn_bytes = (double)BL * 512 * 2 * 4;
@@ -681,13 +680,13 @@ static int forward_impl(rmb_act_engine_t* e, const void* d_images, int image_for
     snprintf(nm, sizeof(nm), "enc%d out proj +res", l); RMB_RUN(run_gemm(nm, pl.o, tokb));   // y = ao Wo^T + bo + x
     snprintf(nm, sizeof(nm), "enc%d norm1", l);
     begin(nm, "layernorm512_kernel", 0, (double)BL * 512 * (4 + 4 + 2));
-    layernorm512_kernel<<<ln_grid, 256, 0, s>>>(e->y_f32, w.g1, w.be1, nullptr, L, e->x1_f32, e->x1_b, nullptr, BL, 1, 1e-5f);
+    RMB_CUDA(launch_pdl(layernorm512_kernel, dim3(ln_grid), dim3(256), 0, s, e->y_f32, w.g1, w.be1, nullptr, L, e->x1_f32, e->x1_b, nullptr, BL, 1, 1e-5f));
     end();
     snprintf(nm, sizeof(nm), "enc%d linear1+relu", l); RMB_RUN(run_gemm(nm, pl.ff1, tokb));
     snprintf(nm, sizeof(nm), "enc%d linear2 +res", l); RMB_RUN(run_gemm(nm, pl.ff2, (double)BL * FF * 2));   // y = relu(.) W2^T + b2 + x1
     snprintf(nm, sizeof(nm), "enc%d norm2", l);
     begin(nm, "layernorm512_kernel", 0, (double)BL * 512 * (4 + 4 + 2 + 2));
-    layernorm512_kernel<<<ln_grid, 256, 0, s>>>(e->y_f32, w.g2, w.be2, e->pos, L, e->tok_f32, e->tok_b, e->tok_pb, BL, 1, 1e-5f);
+    RMB_CUDA(launch_pdl(layernorm512_kernel, dim3(ln_grid), dim3(256), 0, s, e->y_f32, w.g2, w.be2, e->pos, L, e->tok_f32, e->tok_b, e->tok_pb, BL, 1, 1e-5f));
     end();
   }
   RMB_RUN(run_gemm("dec0 K proj", bp->dk, tokb));
@@ -698,12 +697,12 @@ static int forward_impl(rmb_act_engine_t* e, const void* d_images, int image_for
   RMB_RUN(run_gemm("dec0 out proj +tgt", bp->dout, (double)BC * 512 * 2));
   const int lnd_grid = grid_for(BC * 32, 256, sms);
   begin("dec0 norm2", "layernorm512_kernel", 0, (double)BC * 512 * (4 + 4 + 2));
-  layernorm512_kernel<<<lnd_grid, 256, 0, s>>>(e->yd, e->dec.g2, e->dec.be2, nullptr, C, e->t_f32, e->t_b, nullptr, BC, 1, 1e-5f);
+  RMB_CUDA(launch_pdl(layernorm512_kernel, dim3(lnd_grid), dim3(256), 0, s, e->yd, e->dec.g2, e->dec.be2, nullptr, C, e->t_f32, e->t_b, nullptr, BC, 1, 1e-5f));
   end();
   RMB_RUN(run_gemm("dec0 linear1+relu", bp->dff1, (double)BC * 512 * 2));
   RMB_RUN(run_gemm("dec0 linear2 +res", bp->dff2, (double)BC * FF * 2));
   begin("norm3+decoder.norm+action_head", "act_head_kernel", 2.0 * BC * 512 * c.action_dim, (double)BC * 512 * 4 + (double)BC * c.action_dim * 4);
-  act_head_kernel<<<lnd_grid, 256, 0, s>>>(e->yd2, e->dec.g3, e->dec.be3, e->dec.gn, e->dec.ben, e->w_head, e->b_head, d_a_hat, BC, c.action_dim, 1e-5f);
+  RMB_CUDA(launch_pdl(act_head_kernel, dim3(lnd_grid), dim3(256), 0, s, e->yd2, e->dec.g3, e->dec.be3, e->dec.gn, e->dec.ben, e->w_head, e->b_head, d_a_hat, BC, c.action_dim, 1e-5f));
   end();
 #undef RMB_RUN
   RMB_CUDA(cudaGetLastError());
@@ -759,8 +758,7 @@ int rmb_ensemble_step(float* d_ring, const float* d_chunks, int32_t* d_step, con
   DenormParams dn{d_p0, d_p1, out_min, norm_type};
   const size_t diag_bytes = static_cast<size_t>(C) * Da * sizeof(float);
   const int use_smem = diag_bytes <= 48 * 1024 ? 1 : 0;
-  ensemble_step_kernel<<<batch, 128, use_smem ? diag_bytes : 0, static_cast<cudaStream_t>(stream_)>>>(d_ring, d_chunks, d_step, d_reset, d_wtab, dn, d_action, d_action_f32, d_action_norm, C, Da, use_smem);
-  RMB_CUDA(cudaGetLastError());
+  RMB_CUDA(launch_pdl(ensemble_step_kernel, dim3(batch), dim3(128), use_smem ? diag_bytes : 0, static_cast<cudaStream_t>(stream_), d_ring, d_chunks, d_step, d_reset, d_wtab, dn, d_action, d_action_f32, d_action_norm, C, Da, use_smem));
   return 0;
 }
 
@@ -769,8 +767,7 @@ int rmb_normalize(const double* d_x, int norm_type, const double* d_p0, const do
   if (!d_x || !d_p0 || !d_p1 || !d_y) return fail("rmb_normalize: null argument");
   if (norm_type != 0 && norm_type != 1) return fail("rmb_normalize: norm_type must be 0 or 1");
   if (rows * D == 0) return 0;
-  normalize_state_kernel<<<grid_for(rows * D, 256, 148), 256, 0, static_cast<cudaStream_t>(stream_)>>>(d_x, d_p0, d_p1, out_min, norm_type, d_y, rows * D, D);
-  RMB_CUDA(cudaGetLastError());
+  RMB_CUDA(launch_pdl(normalize_state_kernel, dim3(grid_for(rows * D, 256, 148)), dim3(256), 0, static_cast<cudaStream_t>(stream_), d_x, d_p0, d_p1, out_min, norm_type, d_y, rows * D, D));
   return 0;
 }
 

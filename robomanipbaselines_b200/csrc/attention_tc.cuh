@@ -54,6 +54,7 @@ __device__ __forceinline__ float max3(float a, float b, float c) {
 __global__ void __launch_bounds__(kAttnThreads, 2)
 attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_k,
                     const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ AttnParams p) {
+  pdl_trigger();
   extern __shared__ __align__(1024) uint8_t smem[];
   if ((smem_u32(smem) & 1023u) != 0) {   // swizzled tiles need 1024-byte alignment; never observed, but do not guess
     if (threadIdx.x == 0 && atomicCAS(&g_rmb_fault, 0, 2) == 0) printf("[rmb] attention: shared memory window misaligned\n");
@@ -91,6 +92,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
     mbar_init(s_bar, 1); mbar_init(o_bar, 1);
     mbar_init(sc_bar, 8); mbar_init(pr_bar, 8);
     fence_mbar_init();
+    pdl_wait();                                                      // Q / K / V are the previous kernels' outputs
     mbar_arrive_expect_tx(q_bar, 16384u);
     tma_load_3d(sQ, &tmap_q, q_bar, p.q_col0 + head * 64, qt * 128, p.q_shared ? 0 : b);
     mbar_arrive_expect_tx(&k_bar[0], 16384u);
@@ -102,6 +104,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_wait();                                                        // (the issuer thread has already waited)
   const uint32_t tmem_base = *tmem_ptr_smem;
   const uint32_t tmem_S = tmem_base;          // 128 fp32 columns
   const uint32_t tmem_O = tmem_base + 128;    // 64 fp32 columns

@@ -143,6 +143,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
 conv_halo_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                  const __grid_constant__ CUtensorMap tmap_out, const __grid_constant__ CUtensorMap tmap_res,
                  const __grid_constant__ HaloParams hp) {
+  pdl_trigger();
   using S = HaloSmem<BLOCK_K>;
   constexpr int BLOCK_N = 64;
   constexpr uint32_t kSwizzleLayout = (BLOCK_K == 64) ? 2u : 4u;   // SWIZZLE_128B : SWIZZLE_64B
@@ -181,6 +182,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
+  pdl_wait();                                           // everything above ran under the previous kernel's tail
 
   const int total_tiles = p.tiles_w * p.tiles_h * p.tiles_b;
 

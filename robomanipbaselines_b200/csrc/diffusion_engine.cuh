@@ -30,8 +30,7 @@ cudaError_t launch_gemm_gn_instance(const GemmPlan& g, int num_sms, cudaStream_t
     max_pairs = PAIR ? max_active_pairs(kern, S::kTotal, num_sms) : 0;
     attr_set = true;
   }
-  kern<<<gemm_grid(g, num_sms, max_pairs), kGemmThreads, S::kTotal, stream>>>(g.ta, g.tb, g.ta, g.p);
-  return cudaGetLastError();
+  return launch_pdl(kern, dim3(gemm_grid(g, num_sms, max_pairs)), dim3(kGemmThreads), S::kTotal, stream, g.ta, g.tb, g.ta, g.p);
 }
 
 template <int EPI>

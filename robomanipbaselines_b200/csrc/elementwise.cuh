@@ -21,6 +21,8 @@ constexpr int kConv1PadPixels = 4;  // zero pixels on each side of a row in the 
 // One thread = 4 pixels (12 input bytes as 3 x u32, 32 output bytes as 2 x uint4).
 __global__ void preprocess_u8_kernel(const uint8_t* __restrict__ in, act_t* __restrict__ out, int n_img, int H,
                                      int W, float3 mean, float3 inv_std) {
+  pdl_trigger();
+  pdl_wait();
   const int quads_per_row = W / 4 + 2;  // incl. one zero quad on each side
   const long long total = static_cast<long long>(n_img) * H * quads_per_row;
   for (long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; idx < total;
@@ -58,6 +60,8 @@ __global__ void preprocess_u8_kernel(const uint8_t* __restrict__ in, act_t* __re
 // float32 CHW image in [0,1] (the reference nn.Module's input) -> same padded NHWC4 act_t layout.
 __global__ void preprocess_f32_kernel(const float* __restrict__ in, act_t* __restrict__ out, int n_img, int H,
                                       int W, float3 mean, float3 inv_std) {
+  pdl_trigger();
+  pdl_wait();
   const int quads_per_row = W / 4 + 2;
   const long long total = static_cast<long long>(n_img) * H * quads_per_row;
   const long long plane = static_cast<long long>(H) * W;
@@ -93,6 +97,8 @@ __global__ void preprocess_f32_kernel(const float* __restrict__ in, act_t* __res
 // 3x3 stride-2 pad-1 max-pool, NHWC act_t. One thread = 8 channels (16 B) of one output pixel.
 __global__ void maxpool3x3s2_kernel(const act_t* __restrict__ in, act_t* __restrict__ out, int n_img,
                                     int H, int W, int C) {
+  pdl_trigger();
+  pdl_wait();
   const int OH = (H + 1) / 2, OW = (W + 1) / 2, CV = C / 8;
   const long long total = static_cast<long long>(n_img) * OH * OW * CV;
   for (long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; idx < total;
@@ -129,6 +135,8 @@ __global__ void layernorm512_kernel(const float* __restrict__ x_in, const float*
                                     const float* __restrict__ beta, const float* __restrict__ pos, int L,
                                     float* __restrict__ y_f32, act_t* __restrict__ y_act,
                                     act_t* __restrict__ ypos_act, long long rows, int do_norm, float eps) {
+  pdl_trigger();
+  pdl_wait();
   const int lane = threadIdx.x & 31;
   const long long warp_global = (blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x) >> 5;
   const long long warps_total = (static_cast<long long>(gridDim.x) * blockDim.x) >> 5;
@@ -194,6 +202,8 @@ __global__ void layernorm512_kernel(const float* __restrict__ x_in, const float*
 __global__ void act_extra_tokens_kernel(const float* __restrict__ qpos, int Ds, const float* __restrict__ latent_bias,
                                         const float* __restrict__ w_state,  // [512, Ds]
                                         const float* __restrict__ b_state, float* __restrict__ x_f32, int L) {
+  pdl_trigger();
+  pdl_wait();
   const int b = blockIdx.x;
   for (int c = threadIdx.x; c < kD; c += blockDim.x) {
     float acc = b_state[c];
@@ -210,6 +220,8 @@ __global__ void act_head_kernel(const float* __restrict__ x_in, const float* __r
                                 const float* __restrict__ w_head,  // [Da, 512]
                                 const float* __restrict__ b_head, float* __restrict__ a_hat, long long rows, int Da,
                                 float eps) {
+  pdl_trigger();
+  pdl_wait();
   const int lane = threadIdx.x & 31;
   const long long warp_global = (blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x) >> 5;
   const long long warps_total = (static_cast<long long>(gridDim.x) * blockDim.x) >> 5;
@@ -283,6 +295,8 @@ __global__ void ensemble_step_kernel(float* __restrict__ ring, const float* __re
                                      const double* __restrict__ wtab, DenormParams dn, double* __restrict__ action_out,
                                      float* __restrict__ action_out_f32, double* __restrict__ action_norm_out, int C,
                                      int Da, int use_smem) {
+  pdl_trigger();
+  pdl_wait();
   const int b = blockIdx.x;
   int n = step[b];
   if (reset != nullptr && reset[b]) n = 0;
@@ -336,6 +350,8 @@ __global__ void ensemble_step_kernel(float* __restrict__ ring, const float* __re
 __global__ void normalize_state_kernel(const double* __restrict__ x, const double* __restrict__ p0,
                                        const double* __restrict__ p1, double out_min, int type,
                                        float* __restrict__ y, long long total, int D) {
+  pdl_trigger();
+  pdl_wait();
   for (long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; idx < total;
        idx += static_cast<long long>(gridDim.x) * blockDim.x) {
     const int d = static_cast<int>(idx % D);
@@ -349,6 +365,8 @@ __global__ void normalize_state_kernel(const double* __restrict__ x, const doubl
 // denormalize_data on the device for plain (non-ensembled) actions: fp64 in/out.
 __global__ void denormalize_kernel(const double* __restrict__ x, DenormParams dn, double* __restrict__ y,
                                    long long total, int D) {
+  pdl_trigger();
+  pdl_wait();
   for (long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; idx < total;
        idx += static_cast<long long>(gridDim.x) * blockDim.x) {
     const int d = static_cast<int>(idx % D);

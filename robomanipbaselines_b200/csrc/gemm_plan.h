@@ -9,6 +9,7 @@
 
 #include "conv_halo.cuh"
 #include "gemm_tc.cuh"
+#include "launch.h"
 #include "tma_host.h"
 
 namespace rmb {
@@ -248,8 +249,8 @@ inline cudaError_t launch_gemm_instance(const GemmPlan& g, int num_sms, cudaStre
     max_pairs = PAIR ? max_active_pairs(kern, S::kTotal, num_sms) : 0;
     attr_set = true;
   }
-  kern<<<gemm_grid(g, num_sms, max_pairs), kGemmThreads, S::kTotal, stream>>>(g.ta, g.tb, g.tma_out ? g.tout : g.ta, g.p);
-  return cudaGetLastError();
+  return launch_pdl(kern, dim3(gemm_grid(g, num_sms, max_pairs)), dim3(kGemmThreads), S::kTotal, stream, g.ta, g.tb,
+                    g.tma_out ? g.tout : g.ta, g.p);
 }
 
 // epilogue modes in use: act out (+ act residual) for the convs and QKV / FFN-up projections; fp32 out (+ fp32
@@ -438,8 +439,7 @@ inline cudaError_t launch_halo_instance(const HaloPlan& g, int num_sms, cudaStre
   }
   const long long tiles = 1ll * g.hp.g.tiles_w * g.hp.g.tiles_h * g.hp.g.tiles_b;
   const int grid = static_cast<int>(std::min<long long>(tiles, num_sms));
-  conv_halo_kernel<BK, RES><<<grid, kGemmThreads, g.smem, stream>>>(g.ta, g.tb, g.tout, g.tres, g.hp);
-  return cudaGetLastError();
+  return launch_pdl(conv_halo_kernel<BK, RES>, dim3(grid), dim3(kGemmThreads), g.smem, stream, g.ta, g.tb, g.tout, g.tres, g.hp);
 }
 
 inline cudaError_t launch_halo(const HaloPlan& g, int num_sms, cudaStream_t stream) {

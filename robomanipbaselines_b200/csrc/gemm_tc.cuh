@@ -299,6 +299,7 @@ __device__ __forceinline__ void gemm_tc_body(const CUtensorMap& tmap_a, const CU
                                              const GemmParams& p) {
   static_assert(BLOCK_K == 64 || BLOCK_K == 32, "BLOCK_K selects the 128B / 64B swizzle");
   static_assert(BLOCK_N == 64 || BLOCK_N == 128 || BLOCK_N == 256, "BLOCK_N");
+  pdl_trigger();
   using S = GemmSmem<BLOCK_N, BLOCK_K, STAGES, PAIR, EPI>;
   constexpr uint32_t kSwizzleLayout = (BLOCK_K == 64) ? 2u : 4u;   // SWIZZLE_128B : SWIZZLE_64B
   constexpr uint32_t kSBO = 8u * BLOCK_K * 2u;                      // 8-row core-matrix group stride
@@ -335,6 +336,7 @@ __device__ __forceinline__ void gemm_tc_body(const CUtensorMap& tmap_a, const CU
   if (PAIR) cluster_sync_all(); else __syncthreads();   // PAIR: the peer's barriers are live before anything lands on them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
+  pdl_wait();                                           // everything above ran under the previous kernel's tail
 
   const int rows_per_tile = p.box_w * p.box_h * p.box_b;
   const int num_kb = p.num_taps * p.chunks_per_tap;
