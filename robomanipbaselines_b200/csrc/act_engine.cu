@@ -573,6 +573,7 @@ static int forward_impl(rmb_act_engine_t* e, const void* d_images, int image_for
   if (!e->finalized) return fail("rmb_act_forward: weights not finalized");
   if (batch < 1 || batch > e->cfg.max_batch) return fail("rmb_act_forward: batch out of range");
   if (image_format != 0 && image_format != 1) return fail("rmb_act_forward: image_format must be 0 (u8 HWC) or 1 (f32 CHW)");
+  PdlScope pdl;   // every launch below is a pdl_wait()-aware kernel (launch.h)
   rmb_act_engine::BatchPlans* bp = nullptr;
   if (int r = build_plans(e, batch, &bp)) return r;
   const rmb_act_config_t& c = e->cfg;
@@ -756,6 +757,7 @@ int rmb_ensemble_step(float* d_ring, const float* d_chunks, int32_t* d_step, con
   if (batch < 1 || C < 1 || Da < 1 || Da > 128) return fail("rmb_ensemble_step: bad sizes");
   if (norm_type != 0 && norm_type != 1) return fail("rmb_ensemble_step: norm_type must be 0 (gaussian) or 1 (limits)");
   DenormParams dn{d_p0, d_p1, out_min, norm_type};
+  PdlScope pdl;
   const size_t diag_bytes = static_cast<size_t>(C) * Da * sizeof(float);
   const int use_smem = diag_bytes <= 48 * 1024 ? 1 : 0;
   RMB_CUDA(launch_pdl(ensemble_step_kernel, dim3(batch), dim3(128), use_smem ? diag_bytes : 0, static_cast<cudaStream_t>(stream_), d_ring, d_chunks, d_step, d_reset, d_wtab, dn, d_action, d_action_f32, d_action_norm, C, Da, use_smem));
@@ -767,6 +769,7 @@ int rmb_normalize(const double* d_x, int norm_type, const double* d_p0, const do
   if (!d_x || !d_p0 || !d_p1 || !d_y) return fail("rmb_normalize: null argument");
   if (norm_type != 0 && norm_type != 1) return fail("rmb_normalize: norm_type must be 0 or 1");
   if (rows * D == 0) return 0;
+  PdlScope pdl;
   RMB_CUDA(launch_pdl(normalize_state_kernel, dim3(grid_for(rows * D, 256, 148)), dim3(256), 0, static_cast<cudaStream_t>(stream_), d_x, d_p0, d_p1, out_min, norm_type, d_y, rows * D, D));
   return 0;
 }
