@@ -245,7 +245,7 @@ int rmb_imgenc_encode(rmb_imgenc_engine_t* e, const float* d_images, float* d_ou
     const int H = e->Ha[lv], W = e->Wa[lv], Hv = e->Hv[lv], Wv = e->Wv[lv];
     const int nchunk = std::max(1, std::min(kImgencMaxChunks, (Hv * Wv * C / 16 + 8191) / 8192));
     gn2d_stats_kernel<<<dim3(nchunk, NI), 256, 0, s>>>(raw, e->partial, H, W, Hv, Wv, C, nchunk);
-    const int napply = std::max(1, std::min(256, (H * W * (C / 8) + 2047) / 2048));
+    const int napply = std::max(1, std::min(256, (H * W * (C / 8) + 8191) / 8192));   // 32 x 16 B per thread: the per-CTA statistics prologue is amortised
     gn2d_apply_kernel<<<dim3(napply, NI), 256, 0, s>>>(raw, e->partial, nchunk, w.g, w.b, res, out, H, W, Hv, Wv, C, relu ? 1 : 0, napply);
   };
 
