@@ -74,7 +74,8 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
   uint64_t* o_bar = bars + 6;           // O += PV complete
   uint64_t* sc_bar = bars + 7;          // S read out of TMEM by the eight softmax warps
   uint64_t* pr_bar = bars + 8;          // P tile written by the eight softmax warps
-  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 9);
+  uint64_t* kz_bar = bars + 9;          // [6] K blocks of the max sweep (fast path: every block has its own buffer)
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 15);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int quarter = warp & 3, half = warp >> 2;
@@ -84,6 +85,11 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
   const int b = blockIdx.x / (p.n_q_tiles * p.n_heads);
   const int nkt = (p.Lk + 127) / 128;
   const int total = 2 * nkt;
+  // The max sweep does almost no arithmetic per block, so with two K stages it runs at the latency of a TMA load per
+  // block. V and P buffers are idle until the second sweep: with <= 6 key blocks every block of the max sweep gets its
+  // own 16 KB buffer (K0 K1 V0 V1 P0 P1 are contiguous) and all of them are requested up front; blocks 0 and 1 are
+  // still in K0 / K1 when the second sweep starts.
+  const bool fast = nkt <= 6;
 
   if (tid == 256) {   // issuer thread: barriers, then Q and the first two K blocks go out under the TMEM allocation + CTA sync
     mbar_init(q_bar, 1);
@@ -91,14 +97,22 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
     mbar_init(&v_bar[0], 1); mbar_init(&v_bar[1], 1);
     mbar_init(s_bar, 1); mbar_init(o_bar, 1);
     mbar_init(sc_bar, 8); mbar_init(pr_bar, 8);
+    for (int j = 0; j < 6; ++j) mbar_init(&kz_bar[j], 1);
     fence_mbar_init();
     pdl_wait();                                                      // Q / K / V are the previous kernels' outputs
     mbar_arrive_expect_tx(q_bar, 16384u);
     tma_load_3d(sQ, &tmap_q, q_bar, p.q_col0 + head * 64, qt * 128, p.q_shared ? 0 : b);
-    mbar_arrive_expect_tx(&k_bar[0], 16384u);
-    tma_load_3d(sK, &tmap_k, &k_bar[0], p.k_col0 + head * 64, 0, b);
-    mbar_arrive_expect_tx(&k_bar[1], 16384u);                        // total >= 2 always: block 1, or block 0 of sweep 1
-    tma_load_3d(sK + 16384, &tmap_k, &k_bar[1], p.k_col0 + head * 64, (1 % nkt) * 128, b);
+    if (fast) {
+      for (int j = 0; j < nkt; ++j) {
+        mbar_arrive_expect_tx(&kz_bar[j], 16384u);
+        tma_load_3d(sK + j * 16384, &tmap_k, &kz_bar[j], p.k_col0 + head * 64, j * 128, b);
+      }
+    } else {
+      mbar_arrive_expect_tx(&k_bar[0], 16384u);
+      tma_load_3d(sK, &tmap_k, &k_bar[0], p.k_col0 + head * 64, 0, b);
+      mbar_arrive_expect_tx(&k_bar[1], 16384u);                      // total >= 2 always
+      tma_load_3d(sK + 16384, &tmap_k, &k_bar[1], p.k_col0 + head * 64, (1 % nkt) * 128, b);
+    }
   }
   if (warp == 0) { __syncwarp(); tmem_alloc(tmem_ptr_smem, 256); tmem_relinquish(); }
   tc_fence_before();
@@ -125,8 +139,17 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
     tma_load_3d(sV + st * 16384, &tmap_v, &v_bar[st], p.v_col0 + head * 64, kt * 128, b);
   };
   auto issue_s = [&](int g) {
-    const int st = g & 1;
-    mbar_wait(&k_bar[st], (g >> 1) & 1);
+    int st = g & 1;
+    if (!fast) {
+      mbar_wait(&k_bar[st], (g >> 1) & 1);
+    } else if (g < nkt) {
+      st = g;                                  // max sweep: block g lives in buffer g
+      mbar_wait(&kz_bar[g], 0);
+    } else {
+      const int kt = g - nkt;                  // second sweep: blocks 0, 1 are resident, later ones come through the ring
+      st = kt & 1;
+      if (kt >= 2) mbar_wait(&k_bar[st], ((kt >> 1) - 1) & 1);
+    }
     tc_fence_after();
     const uint64_t dq = make_smem_desc(smem_u32(sQ), 0, 1024, 2);
     const uint64_t dk = make_smem_desc(smem_u32(sK + st * 16384), 0, 1024, 2);
@@ -155,7 +178,13 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
         mbar_wait(sc_bar, g & 1);              // S(g) is in registers in all eight warps
         tc_fence_after();
         if (g + 1 < total) issue_s(g + 1);     // runs under this block's softmax arithmetic
-        if (g + 2 < total) load_k(g + 2);      // stage g & 1: S(g) is complete
+        if (!fast) {
+          if (g + 2 < total) load_k(g + 2);    // stage g & 1: S(g) is complete
+        } else if (g >= nkt && g + 2 < total) {
+          const int kt2 = g + 2 - nkt, st = kt2 & 1;   // second sweep, block kt2 -> the stage S(g) has just finished with
+          mbar_arrive_expect_tx(&k_bar[st], 16384u);
+          tma_load_3d(sK + st * 16384, &tmap_k, &k_bar[st], p.k_col0 + head * 64, kt2 * 128, b);
+        }
         if (g == nkt - 1) load_v(0);
         if (g >= nkt) {
           const int kt = g - nkt;
@@ -184,15 +213,14 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(sc_bar);        // 8 arrivals: the S buffer may be overwritten
+      if (ragged) {                              // keys past Lk (TMA zero fill) drop out of both the max and the sum
+#pragma unroll
+        for (int i = 0; i < 64; ++i)
+          if (kcol0 + i >= p.Lk) v[i] = 0xff800000u;   // -inf: exp2 gives exactly 0
+      }
       if (sweep == 0) {
-        if (ragged) {
 #pragma unroll
-          for (int i = 0; i < 64; ++i)
-            if (kcol0 + i < p.Lk) row_max = fmaxf(row_max, __uint_as_float(v[i]));
-        } else {
-#pragma unroll
-          for (int i = 0; i < 64; i += 2) row_max = max3(row_max, __uint_as_float(v[i]), __uint_as_float(v[i + 1]));
-        }
+        for (int i = 0; i < 64; i += 2) row_max = max3(row_max, __uint_as_float(v[i]), __uint_as_float(v[i + 1]));
         if (kt == nkt - 1) {                     // exact row maximum over both column halves
           red_max[half * 128 + row] = row_max;
           named_bar_sync(1, 256);
@@ -201,22 +229,12 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
         }
       } else {
         uint32_t pk[32];
-        if (ragged) {
 #pragma unroll
-          for (int i = 0; i < 64; i += 2) {
-            const float p0 = (kcol0 + i < p.Lk) ? fast_exp2(fmaf(__uint_as_float(v[i]), p.scale_log2e, -mscaled)) : 0.f;
-            const float p1 = (kcol0 + i + 1 < p.Lk) ? fast_exp2(fmaf(__uint_as_float(v[i + 1]), p.scale_log2e, -mscaled)) : 0.f;
-            row_sum += p0 + p1;
-            pk[i >> 1] = pack_act2(p0, p1);
-          }
-        } else {
-#pragma unroll
-          for (int i = 0; i < 64; i += 2) {
-            const float p0 = fast_exp2(fmaf(__uint_as_float(v[i]), p.scale_log2e, -mscaled));
-            const float p1 = fast_exp2(fmaf(__uint_as_float(v[i + 1]), p.scale_log2e, -mscaled));
-            row_sum += p0 + p1;
-            pk[i >> 1] = pack_act2(p0, p1);
-          }
+        for (int i = 0; i < 64; i += 2) {
+          const float p0 = fast_exp2(fmaf(__uint_as_float(v[i]), p.scale_log2e, -mscaled));
+          const float p1 = fast_exp2(fmaf(__uint_as_float(v[i + 1]), p.scale_log2e, -mscaled));
+          row_sum += p0 + p1;
+          pk[i >> 1] = pack_act2(p0, p1);
         }
         if (kt > 0) {                            // PV of the previous block has finished reading the P tile
           mbar_wait(o_bar, (kt - 1) & 1);
