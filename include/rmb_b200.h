@@ -50,6 +50,13 @@ int rmb_check_device(int dev);
  * clear != 0 resets the flag. Results produced while the flag is set are invalid. */
 int rmb_device_fault(int clear);
 
+/* Saturation diagnostics (fp16 build: conversions clamp to +-65504 instead of overflowing to inf). With check mode on,
+ * every 16-bit tensor a forward of this engine stores is scanned right after the launch that wrote it and elements at
+ * the clamp value (bf16 build: inf / nan) are added to a per-process device counter. Off by default (the timed path
+ * launches nothing extra). rmb_saturation_count synchronises the device and returns the counter (clear != 0 resets). */
+int rmb_act_set_check_saturation(rmb_act_engine_t* e, int on);
+int64_t rmb_saturation_count(int clear);
+
 /* ---- engine lifetime: replaces ACTPolicy.__init__ (third_party/act/policy.py:10-16) + RolloutBase.load_ckpt
  *      (robo_manip_baselines/common/base/RolloutBase.py:376-385) */
 int rmb_act_engine_create(const rmb_act_config_t* cfg, rmb_act_engine_t** out);
@@ -283,6 +290,26 @@ int rmb_pointcloud_from_depth(const float* d_depth, const uint8_t* d_rgb, const 
 int rmb_resize_u8_bilinear(const uint8_t* d_src, int n, int H, int W, int H2, int W2, int out_mode, float scale,
                            float offset, void* d_dst, void* stream);
 int rmb_resize_f32_bilinear(const float* d_src, int n, int H, int W, int H2, int W2, float* d_dst, void* stream);
+
+/* ---- Per-episode rollout state of the diffusion policies on the device (B episodes at once).
+ * rmb_obs_ring_push: the n_obs_steps observation buffers of RolloutDiffusionPolicy.get_state / get_images
+ * (policy/diffusion_policy/RolloutDiffusionPolicy.py:87-143) and RolloutDiffusionPolicy3d.get_state / get_pointcloud
+ * (policy/diffusion_policy_3d/RolloutDiffusionPolicy3d.py:103-171). d_buf [batch, n_obs_steps, row_bytes],
+ * d_new [batch, row_bytes], d_mode uint8 [batch]: 0 = untouched (episode does not call the policy at this step),
+ * 1 = first call since reset (every slot <- new), 2 = later call (pop(0) + append). row_bytes % 4 == 0. */
+int rmb_obs_ring_push(void* d_buf, const void* d_new, const uint8_t* d_mode, int batch, int n_obs_steps,
+                      int64_t row_bytes, void* stream);
+/* d_dst row i <- d_src row d_idx[i] (compacts the episodes whose action FIFO is empty into a dense sub-batch). */
+int rmb_gather_rows(const void* d_src, const int32_t* d_idx, void* d_dst, int n_rows, int64_t row_bytes, void* stream);
+/* The float64 action FIFO of infer_policy (RolloutDiffusionPolicy.py:66-85, RolloutDiffusionPolicy3d.py:83-101):
+ * d_fifo float64 [batch, n_action_steps, Da], d_pos int32 [batch] read position (n_action_steps = empty).
+ * d_sub_row int32 [batch] or NULL: >= 0 -> the episode called the policy and its FIFO is refilled from
+ * d_act_new + d_sub_row[b] * act_row_stride (float32 [n_action_steps, Da], cast to float64) with position 0.
+ * Then one pop(0) per episode + denormalize_data (norm parameters as rmb_denormalize) -> d_action float64 [batch, Da];
+ * d_action_norm (or NULL) gets the popped, still normalised action. */
+int rmb_action_fifo_step(double* d_fifo, int32_t* d_pos, const float* d_act_new, int64_t act_row_stride,
+                         const int32_t* d_sub_row, int norm_type, const double* d_p0, const double* d_p1, double out_min,
+                         double* d_action, double* d_action_norm, int batch, int n_action_steps, int Da, void* stream);
 
 #ifdef __cplusplus
 }

@@ -6,10 +6,14 @@ numpy-f64 restatement of the host side of the reference's ACT rollout step:
                                            -- robo_manip_baselines/policy/act/RolloutAct.py:62-101
   * RolloutBase.get_state / get_images     -- robo_manip_baselines/common/base/RolloutBase.py:463-490
 
-Parity pinned: tests/golden/make_golden.py executes the reference's own RolloutAct.infer_policy /
+Parity pinned (ACT): tests/golden/make_golden.py executes the reference's own RolloutAct.infer_policy /
 normalize_data / denormalize_data (imported from /root/reference with stub modules for the GUI / robotics
 dependencies) on seeded inputs and stores the results in tests/golden/rollout_act_golden.npz; tests/test_oracle.py
 checks this restatement against those vectors bit-for-bit.
+Parity pinned (Diffusion Policy / DP3 glue): tests/golden/make_dp_rollout_golden.py executes the reference's own
+RolloutDiffusionPolicy(3d).infer_policy / get_state / get_images / get_pointcloud on a stand-in `self` with a recording
+fake predict_action; tests/test_oracle.py replays DiffusionRolloutOracle + dp_get_image / pointcloud_oracle against
+tests/golden/dp_rollout_golden.npz bit-for-bit (policy inputs at every inference, inference steps, float64 actions).
 """
 import numpy as np
 
@@ -106,6 +110,24 @@ def get_images(rgb_images):
     images = np.moveaxis(images, -1, -3)
     # v2.ToDtype(float32, scale=True) multiplies by 1/255 in float32 (RolloutBase.py:353,488)
     return (images.astype(np.float32) * np.float32(1.0 / 255.0))[np.newaxis]
+
+
+def dp_get_image(rgb_image, image_size):
+    """RolloutDiffusionPolicy.get_images (:113-125) for one camera frame: cv2.resize (the reference's own dependency) ->
+    HWC to CHW -> uint8 to float32 with 1/255 scaling (v2.ToDtype(scale=True), RolloutBase.py:353) -> image * 2.0 - 1.0,
+    all in float32. uint8 (H, W, 3) -> float32 (3, h, w)."""
+    import cv2
+
+    image = cv2.resize(rgb_image, tuple(image_size))
+    image = np.moveaxis(image, -1, -3).astype(np.float32) * np.float32(1.0 / 255.0)
+    return image * np.float32(2.0) - np.float32(1.0)
+
+
+def dp3_resize(rgb_image, depth_image, image_size):
+    """RolloutDiffusionPolicy3d.get_pointcloud's two cv2.resize calls (:134-137)."""
+    import cv2
+
+    return cv2.resize(rgb_image, tuple(image_size)), cv2.resize(depth_image, tuple(image_size))
 
 
 class DiffusionRolloutOracle:

@@ -8,7 +8,12 @@ import os
 from ctypes import POINTER, c_char_p, c_double, c_float, c_int, c_int32, c_int64, c_uint8, c_void_p
 
 _PKG_DIR = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_PKG_DIR, "librmb_b200.so")
+# Product default: the fp16-operand build. RMB_LIB_DTYPE=bf16 (read once, at the first load) selects the bf16-operand
+# build of the same sources instead (librmb_b200_bf16.so); one process uses exactly one of them.
+LIB_DTYPE = os.environ.get("RMB_LIB_DTYPE", "fp16")
+if LIB_DTYPE not in ("fp16", "bf16"):
+    raise ValueError(f"RMB_LIB_DTYPE must be fp16 or bf16, got {LIB_DTYPE!r}")
+LIB_PATH = os.path.join(_PKG_DIR, "librmb_b200.so" if LIB_DTYPE == "fp16" else "librmb_b200_bf16.so")
 
 
 class RmbError(RuntimeError):
@@ -88,6 +93,8 @@ SIGNATURES = {
     "rmb_act_dtype": (c_char_p, []),
     "rmb_check_device": (c_int, [c_int]),
     "rmb_device_fault": (c_int, [c_int]),
+    "rmb_act_set_check_saturation": (c_int, [c_void_p, c_int]),
+    "rmb_saturation_count": (c_int64, [c_int]),
     "rmb_act_engine_create": (c_int, [POINTER(ActConfig), POINTER(c_void_p)]),
     "rmb_act_engine_destroy": (None, [c_void_p]),
     "rmb_act_load_tensor": (c_int, [c_void_p, c_char_p, c_void_p, c_int64]),
@@ -144,6 +151,10 @@ SIGNATURES = {
     "rmb_pointcloud_scratch_bytes": (c_int64, [c_int, c_int, c_int, c_int]),
     "rmb_pointcloud_from_depth": (c_int, [c_void_p, c_void_p, POINTER(PointcloudParams), c_void_p, c_void_p, c_void_p,
                                           c_void_p, c_int, c_void_p]),
+    "rmb_obs_ring_push": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int64, c_void_p]),
+    "rmb_gather_rows": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int64, c_void_p]),
+    "rmb_action_fifo_step": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int, c_void_p, c_void_p,
+                                     c_double, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
 }
 
 _lib = None

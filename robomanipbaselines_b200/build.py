@@ -5,9 +5,10 @@ import sys
 
 PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG_DIR, "csrc")
-LIB_PATH = os.path.join(PKG_DIR, "librmb_b200.so")
+LIB_PATH = os.path.join(PKG_DIR, "librmb_b200.so")             # product default: IEEE fp16 operands
+LIB_PATH_BF16 = os.path.join(PKG_DIR, "librmb_b200_bf16.so")   # same sources with -DRMB_ACT_BF16 (RMB_LIB_DTYPE=bf16)
 SOURCES = ["act_engine.cu"]
-HEADERS = ["ptx.cuh", "gemm_tc.cuh", "gemm_plan.h", "tma_host.h", "attention_tc.cuh", "elementwise.cuh", "conv_halo.cuh", "diffusion_kernels.cuh", "diffusion_engine.cuh", "imgenc_engine.cuh", "gemm_gn.cuh", "pointcloud.cuh", "resize.cuh"]
+HEADERS = ["ptx.cuh", "gemm_tc.cuh", "gemm_plan.h", "tma_host.h", "attention_tc.cuh", "elementwise.cuh", "conv_halo.cuh", "diffusion_kernels.cuh", "diffusion_engine.cuh", "imgenc_engine.cuh", "gemm_gn.cuh", "pointcloud.cuh", "resize.cuh", "rollout_glue.cuh", "launch.h"]
 
 
 def _nvcc():
@@ -17,35 +18,43 @@ def _nvcc():
     return "nvcc"
 
 
-def needs_build():
-    if not os.path.exists(LIB_PATH):
+def needs_build(lib_path=LIB_PATH):
+    if not os.path.exists(lib_path):
         return True
-    t = os.path.getmtime(LIB_PATH)
+    t = os.path.getmtime(lib_path)
     deps = [os.path.join(CSRC, f) for f in SOURCES + HEADERS]
     deps.append(os.path.join(PKG_DIR, "..", "include", "rmb_b200.h"))
     return any(os.path.getmtime(d) > t for d in deps if os.path.exists(d))
 
 
-def build(force=False, verbose=True):
-    """Compile csrc/*.cu for sm_100a into librmb_b200.so (cross-compiles without a GPU)."""
-    if not force and not needs_build():
-        return LIB_PATH
-    cmd = [
+def _cmd(lib_path, bf16, verbose):
+    return [
         _nvcc(), "-shared", "-Xcompiler", "-fPIC", "-O3", "-std=c++17", "-lineinfo",
         "-gencode", "arch=compute_100a,code=sm_100a",
         "-Xptxas", "-v" if verbose else "-O3",
-        "-o", LIB_PATH,
-    ] + [os.path.join(CSRC, s) for s in SOURCES]
-    res = subprocess.run(cmd, capture_output=True, text=True)
-    if res.returncode != 0:
-        sys.stderr.write(res.stdout + res.stderr)
-        raise RuntimeError("nvcc failed building librmb_b200.so")
-    if verbose:
-        log = os.path.join(PKG_DIR, "build_ptxas.log")
-        with open(log, "w") as f:
-            f.write(res.stdout + res.stderr)
+    ] + (["-DRMB_ACT_BF16"] if bf16 else []) + ["-o", lib_path] + [os.path.join(CSRC, s) for s in SOURCES]
+
+
+def build(force=False, verbose=True, bf16_too=True):
+    """Compile csrc/*.cu for sm_100a into librmb_b200.so and (bf16_too) librmb_b200_bf16.so, side by side
+    (cross-compiles without a GPU; the two nvcc runs go in parallel)."""
+    jobs = []
+    for lib_path, bf16 in ((LIB_PATH, False), (LIB_PATH_BF16, True)):
+        if bf16 and not bf16_too:
+            continue
+        if force or needs_build(lib_path):
+            jobs.append((lib_path, bf16, subprocess.Popen(_cmd(lib_path, bf16, verbose), stdout=subprocess.PIPE,
+                                                           stderr=subprocess.STDOUT, text=True)))
+    for lib_path, bf16, proc in jobs:
+        out, _ = proc.communicate()
+        if proc.returncode != 0:
+            sys.stderr.write(out)
+            raise RuntimeError(f"nvcc failed building {os.path.basename(lib_path)}")
+        if verbose:
+            with open(os.path.join(PKG_DIR, "build_ptxas_bf16.log" if bf16 else "build_ptxas.log"), "w") as f:
+                f.write(out)
     return LIB_PATH
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv))
+    print(build(force="--force" in sys.argv, bf16_too="--no-bf16" not in sys.argv))

@@ -85,3 +85,45 @@ def synthetic_act_observations(batch, num_cams, img_h, img_w, state_dim, seed=1)
     images = rng.integers(0, 256, size=(batch, num_cams, img_h, img_w, 3), dtype=np.uint8)
     state = rng.standard_normal(size=(batch, state_dim))
     return images, state
+
+
+def default_init_tensor(key, shape, seed=0):
+    """The distributions PyTorch / the reference give a freshly constructed ACTPolicy (BASELINE.json: "random-init
+    weights"): torchvision resnet18 convs kaiming_normal(fan_out, relu); FrozenBatchNorm2d buffers weight 1, bias 0,
+    mean 0, var 1 (third_party/act/detr/models/backbone.py:30-36); every >= 2-D transformer parameter xavier_uniform
+    (third_party/act/detr/models/transformer.py:44-47); nn.Linear / Conv2d elsewhere kaiming_uniform(a = sqrt 5) with
+    U(+-1/sqrt(fan_in)) biases; nn.Embedding N(0, 1); LayerNorm 1 / 0. Same distributions, own RNG stream."""
+    shape = tuple(int(s) for s in shape)
+    g = _gen("default." + key, seed)
+    if ".bn" in key or ".downsample.1." in key:
+        if key.endswith("weight") or key.endswith("running_var"):
+            return torch.ones(shape)
+        return torch.zeros(shape)
+    if "backbones" in key and len(shape) == 4:
+        fan_out = shape[0] * shape[2] * shape[3]
+        return torch.randn(shape, generator=g) * (2.0 / fan_out) ** 0.5
+    if ".norm" in key:
+        return torch.ones(shape) if key.endswith("weight") else torch.zeros(shape)
+    in_transformer = ".transformer." in key or key.startswith("model.encoder.")
+    if in_transformer and len(shape) >= 2:
+        bound = (6.0 / (shape[0] + shape[1])) ** 0.5
+        return (torch.rand(shape, generator=g) * 2 - 1) * bound
+    if in_transformer and key.endswith("in_proj_bias"):
+        return torch.zeros(shape)
+    if in_transformer and key.endswith("out_proj.bias"):
+        return torch.zeros(shape)
+    if "embed" in key and len(shape) == 2:
+        return torch.randn(shape, generator=g)
+    if len(shape) >= 2:
+        fan_in = int(np.prod(shape[1:]))
+        bound = (1.0 / fan_in) ** 0.5                      # kaiming_uniform(a = sqrt(5)) == U(+-1/sqrt(fan_in))
+        return (torch.rand(shape, generator=g) * 2 - 1) * bound
+    if key.endswith("pos_table"):
+        return torch.zeros(shape)
+    # biases of Linear / Conv layers: U(+-1/sqrt(fan_in)); fan_in is not recoverable from a 1-D shape alone, and the
+    # scale of a bias does not condition the network: use the hidden width
+    return (torch.rand(shape, generator=g) * 2 - 1) * (1.0 / 512) ** 0.5
+
+
+def default_init_state_dict(shapes, seed=0):
+    return {k: default_init_tensor(k, s, seed) for k, s in shapes.items()}

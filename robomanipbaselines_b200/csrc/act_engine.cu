@@ -93,6 +93,7 @@ struct rmb_act_engine {
   rmb_act_config_t cfg;
   int num_sms = 148;
   bool finalized = false;
+  bool check_saturation = false;   // diagnostic mode: scan every 16-bit tensor a forward stores (rmb_act_set_check_saturation)
   std::unordered_map<std::string, std::vector<float>> host_w;
   std::vector<void*> allocs;
 
@@ -561,6 +562,45 @@ double rmb_act_forward_flops(const rmb_act_engine_t* e, int batch) {
   return f;
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// Saturation diagnostics. fp16 conversions on this path clamp to +-65504 (cvt.satfinite) instead of producing inf, so
+// a checkpoint whose activations leave the fp16 range would be silently wrong. In check mode every 16-bit tensor that
+// a forward stores is scanned right after the launch that wrote it, and elements at the clamp value (fp16: |v| ==
+// 65504; bf16: inf / nan, it has fp32's range) are counted into a device counter read by rmb_saturation_count().
+// Off by default: the timed path launches nothing extra.
+__device__ unsigned long long g_rmb_sat_count = 0ull;
+__global__ void sat_scan_kernel(const uint16_t* __restrict__ p, long long n) {
+  unsigned int local = 0;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const uint16_t v = p[i];
+#ifdef RMB_ACT_BF16
+    local += ((v & 0x7f80u) == 0x7f80u) ? 1u : 0u;
+#else
+    local += ((v & 0x7fffu) >= 0x7bffu) ? 1u : 0u;
+#endif
+  }
+  for (int o = 16; o > 0; o >>= 1) local += __shfl_xor_sync(0xffffffffu, local, o);
+  if ((threadIdx.x & 31) == 0 && local != 0) atomicAdd(&g_rmb_sat_count, static_cast<unsigned long long>(local));
+}
+
+int rmb_act_set_check_saturation(rmb_act_engine_t* e, int on) {
+  if (!e) return fail("rmb_act_set_check_saturation: null engine");
+  e->check_saturation = on != 0;
+  return 0;
+}
+
+int64_t rmb_saturation_count(int clear) {
+  unsigned long long v = 0;
+  RMB_CUDA(cudaDeviceSynchronize());
+  RMB_CUDA(cudaMemcpyFromSymbol(&v, g_rmb_sat_count, sizeof(v)));
+  if (clear) {
+    const unsigned long long zero = 0;
+    RMB_CUDA(cudaMemcpyToSymbol(g_rmb_sat_count, &zero, sizeof(zero)));
+  }
+  return static_cast<int64_t>(v);
+}
+
 // One record per kernel launch of a forward (filled by rmb_act_forward_profile).
 struct LaunchProf {
   std::vector<cudaEvent_t> ev;      // 2 per launch
@@ -604,18 +644,25 @@ static int forward_impl(rmb_act_engine_t* e, const void* d_images, int image_for
     const double K = (double)g.p.num_taps * g.p.chunks_per_tap * g.block_k;
     return a_bytes + N * K * 2 + rows * N * (g.p.out_f32 ? 4 : 2) + (g.p.residual ? rows * N * (g.p.res_f32 ? 4 : 2) : 0);
   };
+  // check mode: count clamped values in the 16-bit tensor the launch just stored
+  auto scan = [&](const void* ptr, long long n_elems) {
+    if (!e->check_saturation || n_elems <= 0) return;
+    sat_scan_kernel<<<grid_for(n_elems, 256, sms), 256, 0, s>>>(static_cast<const uint16_t*>(ptr), n_elems);
+  };
   auto run_halo = [&](const char* name, const HaloPlan& g, double a_bytes) -> int {
     const double rows = (double)g.hp.g.W * g.hp.g.H * g.hp.g.B;
     const double K = (double)g.hp.n_taps * g.block_k;
     begin(name, "conv_halo_kernel", (double)g.flops, a_bytes + 64 * K * 2 + rows * 64 * 2 + (g.hp.g.residual ? rows * 64 * 2 : 0));
     RMB_CUDA(launch_halo(g, sms, s));
     end();
+    scan(g.hp.g.out, (long long)rows * 64);
     return 0;
   };
   auto run_gemm = [&](const char* name, const GemmPlan& g, double a_bytes) -> int {
     begin(name, g.pair ? "gemm_tc_pair_kernel" : "gemm_tc_kernel", (double)g.flops, gemm_bytes(g, a_bytes));
     RMB_CUDA(launch_gemm(g, sms, s));
     end();
+    if (!g.p.out_f32 && g.p.remap_ncam == 0) scan(g.p.out, (long long)g.p.W * g.p.H * g.p.B * g.p.ld_out);
     return 0;
   };
 #define RMB_RUN(x) do { if (int _r = (x)) return _r; } while (0)
@@ -631,6 +678,7 @@ static int forward_impl(rmb_act_engine_t* e, const void* d_images, int image_for
       RMB_CUDA(launch_pdl(preprocess_f32_kernel, dim3(grid_for(items, 256, sms)), dim3(256), 0, s, static_cast<const float*>(d_images), e->x0, NI, H, W, mean, istd));
     }
     end();
+    scan(e->x0, (long long)NI * H * (W + 8) * 4);
   }
   RMB_RUN(run_halo("stem conv7x7/2", bp->stem, (double)NI * H * (W + 8) * 8));
   {
@@ -888,3 +936,4 @@ int rmb_layernorm512(const float* d_x, const float* d_gamma, const float* d_beta
 #include "imgenc_engine.cuh"
 #include "pointcloud.cuh"
 #include "resize.cuh"
+#include "rollout_glue.cuh"

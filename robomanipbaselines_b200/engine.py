@@ -80,20 +80,34 @@ class ActEngine:
         return out, [dict(name=recs[i].name.decode(), kernel=recs[i].kernel.decode(), ms=recs[i].ms,
                           flops=recs[i].flops, bytes=recs[i].bytes) for i in range(n)]
 
+    def check_saturation(self, on=True):
+        """Diagnostic mode: scan every 16-bit tensor a forward stores for values at the fp16 clamp (+-65504; bf16
+        build: inf / nan). Read the count with saturation_count(). Off by default (costs extra launches)."""
+        check(self.lib.rmb_act_set_check_saturation(self._h, int(bool(on))), "rmb_act_set_check_saturation")
+
+    def saturation_count(self, clear=True):
+        return check(self.lib.rmb_saturation_count(int(bool(clear))), "rmb_saturation_count")
+
     def debug_read(self, which, batch):
         L = 2 + (self.cfg.img_h // 32) * (self.cfg.img_w // 32) * self.cfg.num_cams
         out = torch.empty(batch, L, 512, device=self.device)
         check(self.lib.rmb_act_debug_read(self._h, which, ptr(out), batch, cur_stream()), "rmb_act_debug_read")
         return out
 
-    def close(self):
+    def close(self, check_fault=True):
+        """Destroy the engine. A kernel fault recorded while it was alive (results were garbage) is raised here at the
+        latest, so that it cannot go unnoticed."""
         if getattr(self, "_h", None) is not None and self._h.value:
+            fault = self.lib.rmb_device_fault(1) if check_fault else 0
             self.lib.rmb_act_engine_destroy(self._h)
             self._h = ctypes.c_void_p()
+            if fault > 0:
+                raise _lib.RmbError("ActEngine.close: a kernel recorded a device fault (mbarrier timeout) while this "
+                                    "engine was in use; its results are invalid")
 
     def __del__(self):
         try:
-            self.close()
+            self.close(check_fault=False)
         except Exception:
             pass
 

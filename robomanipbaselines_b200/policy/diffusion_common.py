@@ -101,8 +101,32 @@ class DiffusionPolicyBase(nn.Module):
         self.use_cuda_graph = True
         self._graphs = {}
 
+    # Keys the upstream classes carry but that hold no arithmetic the engine needs (public upstream layout; the sources
+    # are not in the reference mount, so this list is part of the "parity unpinned" hypothesis):
+    #   ModuleAttrMixin._dummy_variable on the policy and its mask generator; LinearNormalizer.params_dict.* (RMB
+    #   normalises outside the policy: RolloutDiffusionPolicy.py:95,123); robomimic SpatialSoftmax's persistent buffers
+    #   (temperature, pos_x, pos_y), which exist twice per camera (VisualCore registers `pool` and `nets.1`).
+    INERT_KEYS = ("_dummy_variable", "mask_generator._dummy_variable")
+    INERT_PREFIXES = ("normalizer.",)
+    INERT_SUFFIXES = (".pool.pos_x", ".pool.pos_y", ".nets.1.pos_x", ".nets.1.pos_y")
+    TEMPERATURE_SUFFIXES = (".pool.temperature", ".nets.1.temperature")
+
+    def strip_inert_keys(self, state_dict):
+        """RolloutBase.load_ckpt calls load_state_dict(strict=True) on a reference checkpoint (RolloutBase.py:376-385):
+        drop the inert upstream entries first so that strictness still guards every tensor the engine uses."""
+        out = {}
+        for k, v in state_dict.items():
+            if k in self.INERT_KEYS or k.startswith(self.INERT_PREFIXES) or k.endswith(self.INERT_SUFFIXES):
+                continue
+            if k.endswith(self.TEMPERATURE_SUFFIXES):
+                if abs(float(torch.as_tensor(v).reshape(-1)[0]) - 1.0) > 1e-6:
+                    raise NotImplementedError(f"{k} = {float(v.reshape(-1)[0])}: the engine's SpatialSoftmax assumes temperature 1")
+                continue
+            out[k] = v
+        return out
+
     def load_state_dict(self, state_dict, strict=True, **kw):
-        out = super().load_state_dict(state_dict, strict=strict, **kw)
+        out = super().load_state_dict(self.strip_inert_keys(state_dict), strict=strict, **kw)
         self._invalidate()
         return out
 

@@ -19,6 +19,7 @@ STUB_TOPLEVEL = (
     "pynput", "tensorboard", "tqdm_stub_never", "schedule", "pytorch3d", "sentence_transformers", "diffusers",
     "robomimic", "zarr", "hydra", "omegaconf", "gello", "isaacgym", "pyrealsense2", "serial", "rtde_control",
     "rtde_receive", "xarm", "dm_control", "einops_stub_never", "numcodecs", "av", "imageio",
+    "diffusion_policy", "diffusion_policy_3d",
 )
 
 

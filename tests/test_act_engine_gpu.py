@@ -151,3 +151,93 @@ def test_engine_rejects_bad_input(cuda):
     eng = pol.engine_for(case["batch"], case["img_h"], case["img_w"], cuda)
     with pytest.raises(ValueError):
         eng.forward(torch.zeros(3, 2, 64, 96, 4, dtype=torch.uint8, device=cuda), torch.from_numpy(qpos).to(cuda))
+
+
+def test_no_temp_ensem_fifo_is_per_episode(cuda):
+    """--no_temp_ensem with STAGGERED resets (RolloutAct.py:70,86-87 keeps one policy_action_buf per episode): an episode
+    that is reset gets a fresh inference, the others keep popping their own chunk. Actions bit-exact vs the pinned
+    oracle fed with the engine's chunks; the policy runs only for the episodes whose chunk is used up."""
+    from oracle import rollout_oracle
+    from robomanipbaselines_b200.common.batched_rollout import BatchedRollout
+
+    case = dict(ACT_CASES["small"], batch=3)
+    pol = _policy(case, max_batch=3)
+    B, C, Da, Ds = 3, case["chunk_size"], case["action_dim"], case["state_dim"]
+    meta = {"data": {"chunk_size": C}, "state": synthetic_norm_stats(Ds, 1), "action": synthetic_norm_stats(Da, 2)}
+    br = BatchedRollout(pol, B, meta, device="cuda:0", no_temp_ensem=True)
+    oracles = [rollout_oracle.ActRolloutOracle(C, Da, meta["action"], no_temp_ensem=True) for _ in range(B)]
+    rng = np.random.default_rng(8)
+    br.reset()
+    expected_inferences = 0
+    for t in range(27):
+        if t == 4:
+            br.reset([False, True, False]); oracles[1].reset()
+        if t == 17:
+            br.reset([True, False, False]); oracles[0].reset()
+        imgs = rng.integers(0, 256, size=(B, case["num_cams"], case["img_h"], case["img_w"], 3), dtype=np.uint8)
+        raw = rng.standard_normal(size=(B, Ds))
+        need = [o.needs_inference() for o in oracles]
+        expected_inferences += int(any(need))
+        d_img, d_raw = torch.from_numpy(imgs).to(cuda), torch.from_numpy(raw).to(cuda)
+        act = br.infer(d_img, d_raw).cpu().numpy()
+        if any(need):
+            # the chunk an episode received must be what the engine computes for that episode alone (batch invariance)
+            qpos = torch.from_numpy(np.concatenate([rollout_oracle.get_state(raw[b], meta["state"]) for b in range(B)])).to(cuda)
+            solo = pol(qpos, d_img).cpu().numpy()
+        for b in range(B):
+            if need[b]:
+                assert np.array_equal(br.fifo[b].cpu().numpy(), solo[b].astype(np.float64)), (t, b)
+            assert np.array_equal(act[b], oracles[b].step(solo[b] if need[b] else None)), (t, b)
+        assert np.array_equal(br.fifo_pos.cpu().numpy(), br._host_pos)
+    assert br.n_inferences == expected_inferences
+
+
+def test_bench_batch_matches_reference_golden(cuda):
+    """BASELINE configs[1] exactly as bench.py runs it: 256 episodes, 2 cameras 480x640. The two golden episodes sit in
+    rows 0 and 255 (first tile of the first CTA, ragged last wave): chunk within tolerance of the reference's DETRVAE
+    and bit-identical to the 2-episode launch (many tiles per persistent CTA, both TMEM accumulators in flight)."""
+    case = ACT_CASES["c1_2cam"]
+    gold = np.load(os.path.join(GOLD, "act_golden_c1_2cam.npz"))
+    qpos, img = act_inputs(case)
+    B = 256
+    g = torch.Generator(device="cuda").manual_seed(5)
+    di = torch.randint(0, 256, (B,) + img.shape[1:], device=cuda, dtype=torch.uint8, generator=g)
+    dq = torch.randn(B, case["state_dim"], device=cuda, generator=g)
+    di[0], di[255] = torch.from_numpy(img[0]).to(cuda), torch.from_numpy(img[1]).to(cuda)
+    dq[0], dq[255] = torch.from_numpy(qpos[0]).to(cuda), torch.from_numpy(qpos[1]).to(cuda)
+    pol = _policy(case, max_batch=B)
+    full = pol(dq, di).clone()
+    pair = pol(dq[[0, 255]].contiguous(), di[[0, 255]].contiguous()).clone()
+    mid = pol(dq[100:103].contiguous(), di[100:103].contiguous()).clone()
+    torch.cuda.synchronize()
+    assert torch.isfinite(full).all()
+    err = np.abs(full[[0, 255]].cpu().numpy() - gold["a_hat"]).max()
+    print(f"[act bench batch] golden episodes at rows 0 / 255 of a 256-episode batch: max-abs err {err:.3e}")
+    assert err <= ACTION_TOL
+    assert torch.equal(full[[0, 255]], pair)
+    assert torch.equal(full[100:103], mid)
+
+
+def test_cuda_graph_recaptured_when_engine_is_rebuilt(cuda):
+    """A captured policy-step graph pins the engine's workspace. When another user of the same ACTPolicy makes it
+    rebuild its engine (larger batch), the next infer() must recapture instead of replaying into freed memory."""
+    from robomanipbaselines_b200.common.batched_rollout import BatchedRollout
+
+    case = dict(ACT_CASES["small"], batch=2)
+    pol = _policy(case, max_batch=2)
+    B, C, Da, Ds = 2, case["chunk_size"], case["action_dim"], case["state_dim"]
+    meta = {"data": {"chunk_size": C}, "state": synthetic_norm_stats(Ds, 1), "action": synthetic_norm_stats(Da, 2)}
+    br = BatchedRollout(pol, B, meta, device="cuda:0", use_cuda_graph=True)
+    ref = BatchedRollout(pol, B, meta, device="cuda:0", use_cuda_graph=False)
+    rng = np.random.default_rng(2)
+    br.reset(); ref.reset()
+    for t in range(4):
+        imgs = torch.from_numpy(rng.integers(0, 256, size=(B, case["num_cams"], case["img_h"], case["img_w"], 3), dtype=np.uint8)).to(cuda)
+        raw = torch.from_numpy(rng.standard_normal(size=(B, Ds))).to(cuda)
+        if t == 2:      # someone else grows the policy's engine: the old one (and its workspace) is destroyed
+            big_q = torch.zeros(5, Ds, device=cuda)
+            big_i = torch.zeros((5,) + tuple(imgs.shape[1:]), device=cuda, dtype=torch.uint8)
+            pol(big_q, big_i)
+        a = br.infer(imgs, raw).clone()
+        b = ref.infer(imgs, raw).clone()
+        assert torch.equal(a, b), t

@@ -88,6 +88,31 @@ def test_policy_mirrors_have_upstream_state_dict_layout():
     for cam in ("front_rgb_image", "side_rgb_image"):
         want.update({f"obs_encoder.obs_nets.{cam}.{k}": v for k, v in enc.items()})
     assert {k: tuple(v.shape) for k, v in dp.state_dict().items()} == want
+    # A checkpoint written by the upstream classes also carries entries with no arithmetic behind them (public
+    # upstream layout: ModuleAttrMixin._dummy_variable on the policy and its mask generator, LinearNormalizer params,
+    # robomimic SpatialSoftmax's persistent buffers, twice per camera). RolloutBase.load_ckpt loads with strict=True
+    # (common/base/RolloutBase.py:376-385): those keys must not make the load fail, a real missing key still must.
+    sd = {k: torch.randn_like(v) for k, v in dp.state_dict().items()}
+    sd.update({"_dummy_variable": torch.zeros(0), "mask_generator._dummy_variable": torch.zeros(0),
+               "normalizer.params_dict.action.scale": torch.ones(7), "normalizer.params_dict.action.offset": torch.zeros(7)})
+    for cam in ("front_rgb_image", "side_rgb_image"):
+        for pool in ("pool", "nets.1"):
+            sd[f"obs_encoder.obs_nets.{cam}.{pool}.temperature"] = torch.ones(1)
+            sd[f"obs_encoder.obs_nets.{cam}.{pool}.pos_x"] = torch.zeros(1, 63)
+            sd[f"obs_encoder.obs_nets.{cam}.{pool}.pos_y"] = torch.zeros(1, 63)
+    dp.load_state_dict(sd, strict=True)
+    assert torch.equal(dp.state_dict()["model.final_conv.1.bias"], sd["model.final_conv.1.bias"])
+    bad = dict(sd)
+    bad["obs_encoder.obs_nets.front_rgb_image.pool.temperature"] = torch.full((1,), 0.5)
+    with pytest.raises(NotImplementedError):
+        dp.load_state_dict(bad, strict=True)
+    missing = {k: v for k, v in sd.items() if k != "model.final_conv.1.bias"}
+    with pytest.raises(RuntimeError):
+        dp.load_state_dict(missing, strict=True)
+    sd3 = {k: torch.randn_like(v) for k, v in dp3.state_dict().items()}
+    sd3.update({"_dummy_variable": torch.zeros(0), "mask_generator._dummy_variable": torch.zeros(0),
+                "normalizer.params_dict.point_cloud.scale": torch.ones(6)})
+    dp3.load_state_dict(sd3, strict=True)
     with pytest.raises(RuntimeError):          # no CPU fallback
         dp3.predict_action({"state": torch.zeros(1, 2, 7), "point_cloud": torch.zeros(1, 2, 1024, 6)})
     with pytest.raises(NotImplementedError):

@@ -103,3 +103,70 @@ def test_pointcloud_oracle_matches_reference_golden(name):
     assert idx[0] == 0 and len(set(idx.tolist())) == 32            # distinct points, start index 0
     few = po.farthest_point_sampling(g[name + "_cropped"][:5], 8)
     assert sorted(few[:5].tolist()) == [0, 1, 2, 3, 4] and (few[5:] == -1).all()
+
+
+def _dp_golden_stats(g, prefix, norm):
+    s = {k: g[f"{prefix}_{k}"] for k in ("mean", "std", "min", "range")}
+    s["norm_config"] = {"type": "limits", "out_min": -1.0, "out_max": 1.0} if norm == "limits" else {"type": "gaussian"}
+    return s
+
+
+@pytest.mark.parametrize("norm", ["gaussian", "limits"])
+def test_dp_rollout_oracle_matches_reference_golden(norm):
+    """DiffusionRolloutOracle + dp_get_image vs the reference's own RolloutDiffusionPolicy.infer_policy / get_state /
+    get_images run (tests/golden/make_dp_rollout_golden.py): every policy input and every action bit-for-bit."""
+    g = np.load(os.path.join(GOLD, "dp_rollout_golden.npz"))
+    p = f"dp_{norm}"
+    sstats, astats = _dp_golden_stats(g, f"{p}_state", norm), _dp_golden_stats(g, f"{p}_action", norm)
+    raw, imgs, fake = g[f"{p}_raw_states"], g[f"{p}_images_u8"], g[f"{p}_fake_actions"]
+    h, w = g[f"{p}_in_front"].shape[-2:]
+    o = rollout_oracle.DiffusionRolloutOracle(g[f"{p}_in_state"].shape[1], sstats, astats)
+    steps, k = [], 0
+    for t in range(raw.shape[0]):
+        if o.needs_inference():
+            obs = o.push_obs(raw[t], front=rollout_oracle.dp_get_image(imgs[t, 0], (w, h)),
+                             side=rollout_oracle.dp_get_image(imgs[t, 1], (w, h)))
+            assert np.array_equal(obs["state"], g[f"{p}_in_state"][k])
+            assert np.array_equal(obs["front"], g[f"{p}_in_front"][k])
+            assert np.array_equal(obs["side"], g[f"{p}_in_side"][k])
+            steps.append(t)
+            a = o.step(fake[k])
+            k += 1
+        else:
+            a = o.step()
+        assert np.array_equal(a, g[f"{p}_actions"][t]), t
+    assert steps == list(g[f"{p}_infer_steps"])
+
+
+@pytest.mark.parametrize("norm", ["gaussian", "limits"])
+def test_dp3_rollout_oracle_matches_reference_golden(norm):
+    """Same for RolloutDiffusionPolicy3d (get_pointcloud: cv2.resize x2 -> back-projection -> crop -> [FPS stand-in of
+    the golden run: first num_points rows] -> normalize_data -> float32 ring buffer)."""
+    from oracle import pointcloud_oracle as pco
+
+    g = np.load(os.path.join(GOLD, "dp_rollout_golden.npz"))
+    p = f"dp3_{norm}"
+    sstats, astats = _dp_golden_stats(g, f"{p}_state", norm), _dp_golden_stats(g, f"{p}_action", norm)
+    pstats = _dp_golden_stats(g, f"{p}_pointcloud", norm)
+    raw, rgb, depth, fake = g[f"{p}_raw_states"], g[f"{p}_rgb"], g[f"{p}_depth"], g[f"{p}_fake_actions"]
+    n_points = g[f"{p}_in_pc"].shape[2]
+    size = (12, 10)                                   # make_dp_rollout_golden.PC_SIZE (W, H)
+    o = rollout_oracle.DiffusionRolloutOracle(g[f"{p}_in_state"].shape[1], sstats, astats)
+    steps, k = [], 0
+    for t in range(raw.shape[0]):
+        if o.needs_inference():
+            r, d = rollout_oracle.dp3_resize(rgb[t], depth[t], size)
+            pc = np.concatenate(pco.convert_depth_image_to_pointcloud(d, float(g[f"{p}_fovy"][0]), r), axis=1)
+            pc = pco.crop_pointcloud_bb(pc, [-0.6, -0.6, 0.3], [0.6, 0.6, 1.7])
+            pc = pc[:n_points] if len(pc) >= n_points else np.concatenate([pc, np.zeros((n_points - len(pc), 6))])
+            pc = rollout_oracle.normalize_data(pc, pstats).astype(np.float32)
+            obs = o.push_obs(raw[t], point_cloud=pc)
+            assert np.array_equal(obs["state"], g[f"{p}_in_state"][k])
+            assert np.array_equal(obs["point_cloud"], g[f"{p}_in_pc"][k])
+            steps.append(t)
+            a = o.step(fake[k])
+            k += 1
+        else:
+            a = o.step()
+        assert np.array_equal(a, g[f"{p}_actions"][t]), t
+    assert steps == list(g[f"{p}_infer_steps"])
