@@ -96,6 +96,14 @@ double rmb_act_forward_flops(const rmb_act_engine_t* e, int batch);
  * tokens [batch, L, 512], 1 = encoder memory [batch, L, 512]. Returns number of floats, <0 on error. */
 int64_t rmb_act_debug_read(rmb_act_engine_t* e, int which, float* d_out, int batch, void* stream);
 
+/* Opt-in debug output for RolloutAct.draw_plot (policy/act/RolloutAct.py:36-43,115-125): the head-averaged
+ * self-attention map (L, L) of every encoder layer for ONE episode of the batch -- what the reference's forward hook
+ * keeps as `correlation_mat` (nn.MultiheadAttention's averaged attn_output_weights[0]). on != 0: every following
+ * rmb_act_forward also launches one small kernel per encoder layer; off (default): nothing extra is launched.
+ * rmb_act_read_attention_maps copies float32 [enc_layers, L, L] of the last forward to d_out; returns floats, <0 error. */
+int rmb_act_set_attention_debug(rmb_act_engine_t* e, int on, int episode);
+int64_t rmb_act_read_attention_maps(rmb_act_engine_t* e, float* d_out, void* stream);
+
 /* ---- RolloutAct.infer_policy temporal ensembling + denormalize_data
  *      (robo_manip_baselines/policy/act/RolloutAct.py:68-101; common/utils/DataUtils.py:26-40)
  * d_ring  float32 [batch, C, C, Da]   slot (n mod C) holds the chunk of policy call n

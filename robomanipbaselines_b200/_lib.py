@@ -93,6 +93,8 @@ SIGNATURES = {
     "rmb_act_dtype": (c_char_p, []),
     "rmb_check_device": (c_int, [c_int]),
     "rmb_device_fault": (c_int, [c_int]),
+    "rmb_act_set_attention_debug": (c_int, [c_void_p, c_int, c_int]),
+    "rmb_act_read_attention_maps": (c_int64, [c_void_p, c_void_p, c_void_p]),
     "rmb_act_set_check_saturation": (c_int, [c_void_p, c_int]),
     "rmb_saturation_count": (c_int64, [c_int]),
     "rmb_act_engine_create": (c_int, [POINTER(ActConfig), POINTER(c_void_p)]),

@@ -93,6 +93,9 @@ struct rmb_act_engine {
   rmb_act_config_t cfg;
   int num_sms = 148;
   bool finalized = false;
+  bool attn_debug = false;          // opt-in: head-averaged encoder attention maps of one episode (RolloutAct.draw_plot)
+  int attn_debug_episode = 0;
+  float* attn_maps = nullptr;       // [enc_layers, L, L]
   bool check_saturation = false;   // diagnostic mode: scan every 16-bit tensor a forward stores (rmb_act_set_check_saturation)
   std::unordered_map<std::string, std::vector<float>> host_w;
   std::vector<void*> allocs;
@@ -563,6 +566,73 @@ double rmb_act_forward_flops(const rmb_act_engine_t* e, int batch) {
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
+// Debug output for RolloutAct.draw_plot (robo_manip_baselines/policy/act/RolloutAct.py:36-43,115-125): the reference
+// hooks every encoder layer's nn.MultiheadAttention and keeps `attn_output_weights[0]`, the head-AVERAGED softmax map
+// (L, L) of episode 0 (need_weights=True, average_attn_weights=True). The engine's attention kernel never materialises
+// the map; with the debug switch on, this kernel recomputes it for ONE episode from the layer's Q / K projections
+// (one CTA per query row, warp h = head h). Off in the timed path.
+__global__ void attn_map_kernel(const act_t* __restrict__ qk, int ld, int L, float scale, float* __restrict__ out) {
+  extern __shared__ float am_smem[];
+  float* q = am_smem;                 // [512]
+  float* sc = am_smem + 512;          // [8][L]
+  const int i = blockIdx.x;
+  const act_t* qrow = qk + static_cast<long long>(i) * ld;
+  for (int c = threadIdx.x; c < 512; c += blockDim.x) q[c] = static_cast<float>(qrow[c]);
+  __syncthreads();
+  for (int idx = threadIdx.x; idx < 8 * L; idx += blockDim.x) {
+    const int h = idx / L, j = idx - h * L;
+    const act_t* krow = qk + static_cast<long long>(j) * ld + 512 + h * 64;
+    float acc = 0.f;
+#pragma unroll 8
+    for (int d = 0; d < 64; ++d) acc += q[h * 64 + d] * static_cast<float>(krow[d]);
+    sc[idx] = acc * scale;
+  }
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (warp < 8) {
+    float* s = sc + warp * L;
+    float mx = -INFINITY;
+    for (int j = lane; j < L; j += 32) mx = fmaxf(mx, s[j]);
+    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    float sum = 0.f;
+    for (int j = lane; j < L; j += 32) { const float ev = expf(s[j] - mx); s[j] = ev; sum += ev; }
+    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    const float inv = 1.0f / sum;
+    for (int j = lane; j < L; j += 32) s[j] *= inv;
+  }
+  __syncthreads();
+  for (int j = threadIdx.x; j < L; j += blockDim.x) {
+    float acc = 0.f;
+#pragma unroll
+    for (int h = 0; h < 8; ++h) acc += sc[h * L + j];
+    out[static_cast<long long>(i) * L + j] = acc * 0.125f;
+  }
+}
+
+int rmb_act_set_attention_debug(rmb_act_engine_t* e, int on, int episode) {
+  if (!e) return fail("rmb_act_set_attention_debug: null engine");
+  if (!e->finalized) return fail("rmb_act_set_attention_debug: weights not finalized");
+  if (episode < 0 || episode >= e->cfg.max_batch) return fail("rmb_act_set_attention_debug: episode out of range");
+  if (on && e->attn_maps == nullptr) {
+    RMB_CUDA(cudaSetDevice(e->cfg.device));
+    e->attn_maps = e->dalloc<float>((size_t)e->cfg.enc_layers * e->L * e->L);
+    if (!e->attn_maps) return fail("rmb_act_set_attention_debug: cudaMalloc failed");
+    RMB_CUDA(cudaMemset(e->attn_maps, 0, (size_t)e->cfg.enc_layers * e->L * e->L * sizeof(float)));
+  }
+  e->attn_debug = on != 0;
+  e->attn_debug_episode = episode;
+  return 0;
+}
+
+int64_t rmb_act_read_attention_maps(rmb_act_engine_t* e, float* d_out, void* stream_) {
+  if (!e || !d_out) return fail("rmb_act_read_attention_maps: null argument");
+  if (e->attn_maps == nullptr) return fail("rmb_act_read_attention_maps: attention debug output was never switched on");
+  const int64_t n = (int64_t)e->cfg.enc_layers * e->L * e->L;
+  RMB_CUDA(cudaMemcpyAsync(d_out, e->attn_maps, n * sizeof(float), cudaMemcpyDeviceToDevice, static_cast<cudaStream_t>(stream_)));
+  return n;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
 // Saturation diagnostics. fp16 conversions on this path clamp to +-65504 (cvt.satfinite) instead of producing inf, so
 // a checkpoint whose activations leave the fp16 range would be silently wrong. In check mode every 16-bit tensor that
 // a forward stores is scanned right after the launch that wrote it, and elements at the clamp value (fp16: |v| ==
@@ -721,6 +791,14 @@ static int forward_impl(rmb_act_engine_t* e, const void* d_images, int image_for
     auto& pl = bp->enc[l];
     char nm[48];
     snprintf(nm, sizeof(nm), "enc%d QK proj", l); RMB_RUN(run_gemm(nm, pl.qk, tokb));
+    if (e->attn_debug && e->attn_debug_episode < batch) {
+      const size_t smem = (512 + 8 * (size_t)L) * sizeof(float);
+      static bool am_attr = false;
+      if (!am_attr) { RMB_CUDA(cudaFuncSetAttribute(attn_map_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)); am_attr = true; }
+      if (smem > 200 * 1024) return fail("attention debug output: sequence too long for the debug kernel");
+      attn_map_kernel<<<L, 256, smem, s>>>(e->qk + (size_t)e->attn_debug_episode * L * 1024, 1024, L, 0.125f,
+                                           e->attn_maps + (size_t)l * L * L);
+    }
     snprintf(nm, sizeof(nm), "enc%d V proj", l); RMB_RUN(run_gemm(nm, pl.v, tokb));
     snprintf(nm, sizeof(nm), "enc%d self-attention", l);
     begin(nm, "attention_tc_kernel", attn_flops, attn_bytes);

@@ -80,6 +80,21 @@ class ActEngine:
         return out, [dict(name=recs[i].name.decode(), kernel=recs[i].kernel.decode(), ms=recs[i].ms,
                           flops=recs[i].flops, bytes=recs[i].bytes) for i in range(n)]
 
+    @property
+    def seq_len(self):
+        return 2 + (self.cfg.img_h // 32) * (self.cfg.img_w // 32) * self.cfg.num_cams
+
+    def attention_debug(self, on=True, episode=0):
+        """Opt-in: keep the head-averaged encoder self-attention maps of one episode (RolloutAct.draw_plot)."""
+        check(self.lib.rmb_act_set_attention_debug(self._h, int(bool(on)), int(episode)), "rmb_act_set_attention_debug")
+
+    def attention_maps(self):
+        """float32 (enc_layers, L, L) of the last forward (attention_debug must be on)."""
+        L = self.seq_len
+        out = torch.empty(self.cfg.enc_layers, L, L, device=self.device)
+        check(self.lib.rmb_act_read_attention_maps(self._h, ptr(out), cur_stream()), "rmb_act_read_attention_maps")
+        return out
+
     def check_saturation(self, on=True):
         """Diagnostic mode: scan every 16-bit tensor a forward stores for values at the fp16 clamp (+-65504; bf16
         build: inf / nan). Read the count with saturation_count(). Off by default (costs extra launches)."""

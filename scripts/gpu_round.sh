@@ -25,6 +25,9 @@ ENGINE_RC=$?
 run t_diffusion 900 $PT tests/test_diffusion_gpu.py
 run t_pointcloud 300 $PT tests/test_pointcloud_gpu.py
 run t_resize 300 $PT tests/test_resize_gpu.py
+run t_glue 300 $PT tests/test_rollout_glue_gpu.py
+run t_classes 600 $PT tests/test_rollout_classes_gpu.py
+run t_dtype 900 $PT tests/test_dtype_builds_gpu.py
 if [ "$1" != "--no-bench" ] && [ $ENGINE_RC -eq 0 ]; then
   run smoke 300 python -c "import __graft_entry__ as g; g.smoke()"
   run bench 900 python bench.py --steps 5 --warmup 3

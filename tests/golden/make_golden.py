@@ -46,8 +46,14 @@ def make_act_case(name, case):
     enc = ref.model.transformer.encoder
     h1 = enc.register_forward_pre_hook(lambda m, a: taps.__setitem__("src_tokens", a[0].detach().permute(1, 0, 2).contiguous()))
     h2 = enc.register_forward_hook(lambda m, a, o: taps.__setitem__("memory", o.detach().permute(1, 0, 2).contiguous()))
+    # the hook RolloutAct.setup_policy registers (policy/act/RolloutAct.py:36-43), here keeping every episode's map
+    attn = []
+    hooks = [layer.self_attn.register_forward_hook(lambda _l, _i, _o: attn.append(_o[1].detach().numpy().copy()))
+             for layer in enc.layers]
     a_hat = ref(torch.from_numpy(qpos), image)
     h1.remove(); h2.remove()
+    for h in hooks:
+        h.remove()
     out = {
         "a_hat": a_hat.numpy(),
         "weight_checksum": np.array([float(sum(v.double().abs().sum() for v in sd.values()))]),
@@ -57,6 +63,7 @@ def make_act_case(name, case):
     if case.get("store_taps"):
         out["src_tokens"] = taps["src_tokens"].numpy()
         out["memory"] = taps["memory"].numpy()
+        out["attn_maps"] = np.stack(attn)            # (enc_layers, B, L, L) head-averaged attention weights
     else:  # large case: keep the fixture small, store per-token statistics only
         out["memory_token_mean"] = taps["memory"].mean(-1).numpy()
         out["src_token_mean"] = taps["src_tokens"].mean(-1).numpy()
@@ -132,6 +139,9 @@ def make_rollout_golden():
 
 
 if __name__ == "__main__":
-    make_rollout_golden()
+    only = sys.argv[1:]                              # e.g. `make_golden.py small` regenerates one fixture
+    if not only or "rollout" in only:
+        make_rollout_golden()
     for name, case in ACT_CASES.items():
-        make_act_case(name, case)
+        if not only or name in only:
+            make_act_case(name, case)
