@@ -35,6 +35,13 @@ typedef struct rmb_act_config {
   int32_t dec_layers;       /* 7 -- only layer 0 is live at inference (detr_vae.py:142 takes hs[0]) */
   int32_t chunk_size;       /* num_queries (100) */
   int32_t device;           /* CUDA device ordinal */
+  /* MT-ACT (policy/mt_act; the task-conditioned DETRVAE lives in the un-vendored third_party/roboagent: ARCHITECTURE
+   * HYPOTHESIS, parity unpinned): */
+  int32_t multi_task;       /* 1: ResNet blocks of layers 2..4 are FiLM-modulated by the projected task embedding */
+  int32_t task_emb_dim;     /* 384 (all-MiniLM-L6-v2, policy/mt_act/RolloutMtAct.py:54-56); multiple of 64 */
+  int32_t task_token;       /* 1: the projected task embedding is also a third prefix token (L = 3 + ...). Default 0:
+                             * RolloutMtAct.draw_plot reshapes correlation_mat[2:, 1] to (15, 20 Ncam)
+                             * (policy/mt_act/RolloutMtAct.py:147-155), which only fits L = 2 + 300 Ncam */
 } rmb_act_config_t;
 
 /* Last error message of the library (per process). */
@@ -68,6 +75,12 @@ int rmb_act_load_tensor(rmb_act_engine_t* e, const char* name, const float* host
 /* Fold FrozenBatchNorm2d into the conv weights, precompute the input-independent tensors (sine position table,
  * latent token, decoder query projection), upload 16-bit weights. Must be called once after all tensors are loaded. */
 int rmb_act_finalize(rmb_act_engine_t* e);
+
+/* ---- MT-ACT: `task_emb=` of ACTPolicy.__call__ (policy/mt_act/RolloutMtAct.py:84-85). d_task_emb float32
+ * [batch, task_emb_dim], one sentence embedding per episode. Computes proj_text_emb and the FiLM gamma / beta of every
+ * conditioned ResNet block ONCE; they stay resident in the engine until the next call (the reference caches the
+ * embedding per task text the same way, RolloutMtAct.py:115-120), so a policy step launches nothing extra. */
+int rmb_act_set_task_embedding(rmb_act_engine_t* e, const float* d_task_emb, int batch, void* stream);
 
 /* ---- ACTPolicy.__call__ inference branch (third_party/act/policy.py:18-38) -> DETRVAE.forward
  *      (third_party/act/detr/models/detr_vae.py:89-150), for `batch` episodes at once.
@@ -140,6 +153,10 @@ int rmb_gemm(const void* d_A, const void* d_Wt, const float* d_bias, const void*
 /* NHWC act conv k in {1,3}, stride in {1,2}, pad k/2; Wt [Cout, k*k*Cin] tap-major; residual/out [B,OH,OW,Cout] act */
 int rmb_conv2d_nhwc(const void* d_in, const void* d_Wt, const float* d_bias, const void* d_residual, void* d_out,
                          int B, int H, int W, int Cin, int Cout, int ksize, int stride, int relu, void* stream);
+/* ResNet stem fused with its max-pool (the kernel the engine launches): same input / weights as rmb_conv1_stem, out
+ * [B, H/4, W/4, 64] act = maxpool3x3s2(relu(conv1 + bias)), bit-identical to rmb_conv1_stem + rmb_maxpool3x3s2_nhwc */
+int rmb_stem_pool(const void* d_in_padded, const void* d_Wt, const float* d_bias, void* d_out, int B, int H, int W,
+                  void* stream);
 /* ResNet stem on the padded NHWC4 input: Wt [64, 7*32] (see gemm_plan.h), out [B, H/2, W/2, 64] act, ReLU */
 int rmb_conv1_stem(const void* d_in_padded, const void* d_Wt, const float* d_bias, void* d_out, int B, int H, int W,
                         void* stream);

@@ -31,8 +31,12 @@ def frozen_bn(x, sd, prefix):
     return x * scale + (b - rm * scale)
 
 
-def resnet18_trunk(x, sd, prefix):
-    """torchvision resnet18 up to layer4 (IntermediateLayerGetter return_layers={'layer4': '0'}, backbone.py:66-71)."""
+def resnet18_trunk(x, sd, prefix, film=None):
+    """torchvision resnet18 up to layer4 (IntermediateLayerGetter return_layers={'layer4': '0'}, backbone.py:66-71).
+
+    film (MT-ACT HYPOTHESIS, parity unpinned -- third_party/roboagent is not in the mount): {layer index 2..4:
+    (B, 2, n_blocks, planes)} per-sample FiLM; block `bi` of that layer applies (1 + gamma) * bn2(conv2(.)) + beta with
+    gamma = film[:, 0, bi], beta = film[:, 1, bi] before the identity branch is added."""
     x = F.conv2d(x, sd[prefix + "conv1.weight"], None, stride=2, padding=3)
     x = F.relu(frozen_bn(x, sd, prefix + "bn1"))
     x = F.max_pool2d(x, kernel_size=3, stride=2, padding=1)
@@ -45,6 +49,9 @@ def resnet18_trunk(x, sd, prefix):
             out = F.relu(frozen_bn(out, sd, p + "bn1"))
             out = F.conv2d(out, sd[p + "conv2.weight"], None, stride=1, padding=1)
             out = frozen_bn(out, sd, p + "bn2")
+            if film is not None and li in film:
+                gamma, beta = film[li][:, 0, bi], film[li][:, 1, bi]
+                out = (1 + gamma[:, :, None, None]) * out + beta[:, :, None, None]
             if (p + "downsample.0.weight") in sd:
                 identity = F.conv2d(x, sd[p + "downsample.0.weight"], None, stride=stride)
                 identity = frozen_bn(identity, sd, p + "downsample.1")
@@ -114,13 +121,20 @@ def decoder_layer(tgt, memory, pos, query_pos, sd, p, nheads):
 
 
 @torch.no_grad()
-def act_forward(sd, cfg, qpos, image, live_only=False, taps=None):
+def act_forward(sd, cfg, qpos, image, live_only=False, taps=None, task_emb=None, task_token=False):
     """a_hat (B, num_queries, action_dim) for qpos (B, Ds) f32 and image (B, Ncam, 3, H, W) f32 in [0, 1].
 
     sd: checkpoint state dict with the reference's `model.` key prefix (fp32 CPU tensors).
     cfg: dict with hidden_dim, nheads, enc_layers, dec_layers, num_queries, camera_names.
     live_only: skip decoder layers >= 1, whose outputs the reference computes and discards (detr_vae.py:142 takes [0]).
     taps: optional dict filled with intermediates ('src_tokens', 'memory', 'attn_l<i>') for debugging.
+    task_emb: MT-ACT only (policy/mt_act/RolloutMtAct.py:84-85): (B or 1, 384) sentence embedding. ARCHITECTURE
+      HYPOTHESIS, PARITY UNPINNED (the task-conditioned DETRVAE is in the un-vendored third_party/roboagent):
+      e = proj_text_emb(task_emb); layers 2..4 of the shared ResNet get per-sample FiLM from
+      backbones.0.0.film_models.{1,2,3} = Linear(512, n_blocks * 2 * planes) viewed as (B, 2, n_blocks, planes);
+      task_token=True additionally makes e a third prefix token (additional_pos_embed then has 3 rows). The default
+      (no token) is what RolloutMtAct.draw_plot implies: correlation_mat[2:, 1] reshaped to (15, 20 * Ncam)
+      (RolloutMtAct.py:147-155) needs L = 2 + 300 * Ncam.
     """
     sd = {k[len("model."):]: v.float() for k, v in sd.items() if k.startswith("model.")}
     nheads, hidden = cfg["nheads"], cfg["hidden_dim"]
@@ -131,9 +145,16 @@ def act_forward(sd, cfg, qpos, image, live_only=False, taps=None):
     image = (image - mean) / std                                               # policy.py:20-22
     latent_sample = torch.zeros(bs, 32)                                        # detr_vae.py:124-125
     latent_input = F.linear(latent_sample, sd["latent_out_proj.weight"], sd["latent_out_proj.bias"])
+    film, task_tok = None, None
+    if task_emb is not None:
+        task_tok = F.linear(task_emb.float().expand(bs, -1), sd["proj_text_emb.weight"], sd["proj_text_emb.bias"])
+        film = {}
+        for i, planes in ((1, 128), (2, 256), (3, 512)):
+            g = F.linear(task_tok, sd[f"backbones.0.0.film_models.{i}.weight"], sd[f"backbones.0.0.film_models.{i}.bias"])
+            film[i + 1] = g.view(bs, 2, 2, planes)
     feats, poss = [], []
     for cam in range(ncam):                                                    # detr_vae.py:131-136 (shared backbone)
-        f = resnet18_trunk(image[:, cam], sd, "backbones.0.0.body.")
+        f = resnet18_trunk(image[:, cam], sd, "backbones.0.0.body.", film)
         poss.append(sine_position_embedding(f.shape[2], f.shape[3], hidden // 2))
         feats.append(F.conv2d(f, sd["input_proj.weight"], sd["input_proj.bias"]))
     proprio_input = F.linear(qpos, sd["input_proj_robot_state.weight"], sd["input_proj_robot_state.bias"])
@@ -145,7 +166,8 @@ def act_forward(sd, cfg, qpos, image, live_only=False, taps=None):
     query_embed = sd["query_embed.weight"].unsqueeze(1).repeat(1, bs, 1)
     additional_pos = sd["additional_pos_embed.weight"].unsqueeze(1).repeat(1, bs, 1)
     pos_embed = torch.cat([additional_pos, pos_embed], dim=0)
-    src = torch.cat([torch.stack([latent_input, proprio_input], dim=0), src], dim=0)
+    prefix = [latent_input, proprio_input] + ([task_tok] if (task_token and task_tok is not None) else [])
+    src = torch.cat([torch.stack(prefix, dim=0), src], dim=0)
     if taps is not None:
         taps["src_tokens"] = src.permute(1, 0, 2).contiguous()
     tgt = torch.zeros_like(query_embed)

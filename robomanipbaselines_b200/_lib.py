@@ -27,7 +27,7 @@ class ActConfig(ctypes.Structure):
         ("max_batch", c_int32), ("num_cams", c_int32), ("img_h", c_int32), ("img_w", c_int32),
         ("state_dim", c_int32), ("action_dim", c_int32), ("hidden_dim", c_int32), ("dim_feedforward", c_int32),
         ("nheads", c_int32), ("enc_layers", c_int32), ("dec_layers", c_int32), ("chunk_size", c_int32),
-        ("device", c_int32),
+        ("device", c_int32), ("multi_task", c_int32), ("task_emb_dim", c_int32), ("task_token", c_int32),
     ]
 
 
@@ -101,6 +101,7 @@ SIGNATURES = {
     "rmb_act_engine_destroy": (None, [c_void_p]),
     "rmb_act_load_tensor": (c_int, [c_void_p, c_char_p, c_void_p, c_int64]),
     "rmb_act_finalize": (c_int, [c_void_p]),
+    "rmb_act_set_task_embedding": (c_int, [c_void_p, c_void_p, c_int, c_void_p]),
     "rmb_act_forward": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int, c_void_p]),
     "rmb_act_forward_profile": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int, c_void_p,
                                         POINTER(LaunchProf), c_int]),
@@ -117,6 +118,7 @@ SIGNATURES = {
                               c_void_p]),
     "rmb_conv2d_nhwc": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int,
                                      c_int, c_int, c_int, c_int, c_void_p]),
+    "rmb_stem_pool": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
     "rmb_conv1_stem": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
     "rmb_maxpool3x3s2_nhwc": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
     "rmb_attention": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_int, c_int, c_void_p, c_int, c_int,

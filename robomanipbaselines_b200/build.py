@@ -32,12 +32,13 @@ def _cmd(lib_path, bf16, verbose):
         _nvcc(), "-shared", "-Xcompiler", "-fPIC", "-O3", "-std=c++17", "-lineinfo",
         "-gencode", "arch=compute_100a,code=sm_100a",
         "-Xptxas", "-v" if verbose else "-O3",
-    ] + (["-DRMB_ACT_BF16"] if bf16 else []) + ["-o", lib_path] + [os.path.join(CSRC, s) for s in SOURCES]
+    ] + (["-DRMB_ACT_BF16"] if bf16 else []) + ["-o", lib_path + ".tmp"] + [os.path.join(CSRC, s) for s in SOURCES]
 
 
-def build(force=False, verbose=True, bf16_too=True):
+def build(force=False, verbose=True, bf16_too=True, stage_only=False):
     """Compile csrc/*.cu for sm_100a into librmb_b200.so and (bf16_too) librmb_b200_bf16.so, side by side
-    (cross-compiles without a GPU; the two nvcc runs go in parallel)."""
+    (cross-compiles without a GPU; the two nvcc runs go in parallel). Each library is written to <name>.tmp and moved
+    into place atomically; stage_only leaves the .tmp files for a later commit_staged()."""
     jobs = []
     for lib_path, bf16 in ((LIB_PATH, False), (LIB_PATH_BF16, True)):
         if bf16 and not bf16_too:
@@ -53,8 +54,19 @@ def build(force=False, verbose=True, bf16_too=True):
         if verbose:
             with open(os.path.join(PKG_DIR, "build_ptxas_bf16.log" if bf16 else "build_ptxas.log"), "w") as f:
                 f.write(out)
+    if not stage_only:
+        commit_staged()
     return LIB_PATH
 
 
+def commit_staged():
+    for lib_path in (LIB_PATH, LIB_PATH_BF16):
+        if os.path.exists(lib_path + ".tmp"):
+            os.replace(lib_path + ".tmp", lib_path)
+
+
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, bf16_too="--no-bf16" not in sys.argv))
+    if "--commit" in sys.argv:
+        commit_staged()
+    else:
+        print(build(force="--force" in sys.argv, bf16_too="--no-bf16" not in sys.argv, stage_only="--stage" in sys.argv))

@@ -93,6 +93,7 @@ class BatchedRollout:
             self._sub_qpos = torch.empty(batch, self.Ds, device=dev, dtype=torch.float32)
             self._all_rows = torch.arange(batch, device=dev, dtype=torch.int32)
         self.n_inferences = 0
+        self._task_emb = None    # MT-ACT: float32 (B or 1, 384) sentence embeddings (set_task_embedding)
         self.use_cuda_graph = (batch <= 8) if use_cuda_graph is None else bool(use_cuda_graph)
         self._graph = None   # (graph, static images, static raw state, image shape, engine)
 
@@ -109,6 +110,24 @@ class BatchedRollout:
             self.reset_mask.fill_(1)
         else:
             self.reset_mask |= torch.as_tensor(mask, device=self.device).to(torch.uint8)
+
+    def set_task_embedding(self, task_emb):
+        """MT-ACT (policy/mt_act/RolloutMtAct.py:84-85): the `task_emb=` every following policy call gets, one row per
+        episode (or one row for all). The engine keeps the projected token / FiLM parameters resident."""
+        if not hasattr(self.policy, "set_task_embedding"):
+            raise ValueError("this policy takes no task embedding")
+        self._task_emb = task_emb.to(self.device, torch.float32)
+
+    def _engine(self, img_h, img_w, rows=None):
+        """The policy's engine for this batch; MT-ACT: with the task embedding of the episodes in `rows` applied."""
+        if self._task_emb is None:
+            if hasattr(self.policy, "set_task_embedding"):
+                raise ValueError("MT-ACT rollout without a task embedding: call set_task_embedding first")
+            return self.policy.engine_for(self.B, img_h, img_w, self.device)
+        if rows is None:
+            return self.policy.set_task_embedding(self._task_emb, self.B, img_h, img_w, self.device)
+        te = self._task_emb if self._task_emb.shape[0] == 1 else self._task_emb.index_select(0, rows.long()).contiguous()
+        return self.policy.set_task_embedding(te, int(rows.numel()), img_h, img_w, self.device)
 
     def normalize_state(self, raw_state):
         """raw_state float64 (B, Ds) on device -> self.qpos float32."""
@@ -133,7 +152,7 @@ class BatchedRollout:
     def _infer_graph(self, images_u8, raw_state):
         key = (tuple(images_u8.shape), images_u8.dtype)
         img_h, img_w = (images_u8.shape[2], images_u8.shape[3]) if images_u8.dtype == torch.uint8 else (images_u8.shape[3], images_u8.shape[4])
-        eng = self.policy.engine_for(self.B, img_h, img_w, self.device)
+        eng = self._engine(img_h, img_w)
         # the captured graph pins the engine's workspace: recapture when the policy rebuilt its engine (another rollout
         # asked for a larger batch / other image size) instead of replaying into freed memory
         if self._graph is None or self._graph[3] != key or self._graph[4] is not eng:
@@ -158,7 +177,7 @@ class BatchedRollout:
     def _infer_eager(self, images_u8, raw_state, clear_reset=True):
         self.normalize_state(raw_state)
         img_h, img_w = (images_u8.shape[2], images_u8.shape[3]) if images_u8.dtype == torch.uint8 else (images_u8.shape[3], images_u8.shape[4])
-        eng = self.policy.engine_for(self.B, img_h, img_w, self.device)
+        eng = self._engine(img_h, img_w)
         eng.forward(images_u8, self.qpos, out=self.chunks)
         self.n_inferences += 1
         check(self.lib.rmb_ensemble_step(ptr(self.ring), ptr(self.chunks), ptr(self.step), ptr(self.reset_mask),
@@ -178,13 +197,13 @@ class BatchedRollout:
             n = int(need.sum())
             self.normalize_state(raw_state)
             img_h, img_w = (images_u8.shape[2], images_u8.shape[3]) if images_u8.dtype == torch.uint8 else (images_u8.shape[3], images_u8.shape[4])
-            eng = self.policy.engine_for(self.B, img_h, img_w, self.device)
             if n == self.B:
-                eng.forward(images_u8, self.qpos, out=self.chunks)
+                self._engine(img_h, img_w).forward(images_u8, self.qpos, out=self.chunks)
                 sub_rows = self._all_rows
             else:
                 idx = np.nonzero(need)[0].astype(np.int32)
                 idx_dev = torch.from_numpy(idx).to(self.device)
+                eng = self._engine(img_h, img_w, rows=idx_dev)
                 if self._sub_images is None or self._sub_images.shape != images_u8.shape or self._sub_images.dtype != images_u8.dtype:
                     self._sub_images = torch.empty_like(images_u8)
                 row_bytes = images_u8[0].numel() * images_u8.element_size()

@@ -102,6 +102,15 @@ struct rmb_act_engine {
 
   // derived
   int Hf = 0, Wf = 0, L = 0, n_img_max = 0;
+  int n_prefix = 2;        // tokens in front of the image tokens: latent, proprio (+ task token if cfg.task_token)
+
+  // ---- MT-ACT (cfg.multi_task): text-conditioned FiLM of the ResNet trunk; ARCHITECTURE HYPOTHESIS, see DESIGN.md
+  static constexpr int kFilmLd = 2 * 2 * (128 + 256 + 512);   // per episode: layers 2..4 x [gamma|beta] x 2 blocks x planes
+  act_t *w_text = nullptr, *w_film = nullptr;                 // proj_text_emb [512, E]; film generators [kFilmLd, 512]
+  float *b_text = nullptr, *b_film = nullptr;
+  act_t *task_emb_act = nullptr, *task_tok_act = nullptr;     // [max_batch, E], [max_batch, 512]
+  float *task_tok = nullptr, *film = nullptr;                 // [max_batch, 512], [max_batch, kFilmLd]
+  int task_batch = 0;                                         // episodes covered by the last rmb_act_set_task_embedding
 
   // ---- device weights
   struct ConvW { act_t* w = nullptr; float* b = nullptr; int cin = 0, cout = 0, k = 0, stride = 1; };
@@ -130,8 +139,10 @@ struct rmb_act_engine {
   act_t *kd = nullptr, *vd = nullptr, *aod = nullptr, *t_b = nullptr, *hd = nullptr;
   float *yd = nullptr, *t_f32 = nullptr, *yd2 = nullptr;
 
+  bool fuse_stem_pool = true;   // RMB_NO_STEM_POOL=1: stem and max-pool as two kernels through a [img, H/2, W/2, 64] buffer
   struct BatchPlans {
     HaloPlan stem;
+    StemPoolPlan stem_pool;
     GemmPlan conv[4][2][2];
     HaloPlan conv_l1[2][2];   // layer1 (Cin = Cout = 64): halo-reuse kernel
     GemmPlan down[4];
@@ -255,6 +266,8 @@ int rmb_act_engine_create(const rmb_act_config_t* cfg, rmb_act_engine_t** out) {
   if (cfg->img_h % 32 != 0 || cfg->img_w % 32 != 0) return fail("image size must be a multiple of 32");
   if (cfg->max_batch < 1 || cfg->num_cams < 1 || cfg->chunk_size < 1 || cfg->enc_layers < 1 || cfg->dec_layers < 1) return fail("bad config");
   if (cfg->state_dim < 1 || cfg->action_dim < 1) return fail("bad state/action dim");
+  if (cfg->multi_task && (cfg->task_emb_dim < 64 || cfg->task_emb_dim % 64 != 0)) return fail("task_emb_dim must be a multiple of 64 (384 for all-MiniLM-L6-v2)");
+  if (!cfg->multi_task && cfg->task_token) return fail("task_token needs multi_task");
   RMB_CUDA(cudaSetDevice(cfg->device));
   if (int r = rmb_check_device(cfg->device)) return r;
   auto* e = new rmb_act_engine();
@@ -262,8 +275,10 @@ int rmb_act_engine_create(const rmb_act_config_t* cfg, rmb_act_engine_t** out) {
   cudaDeviceProp prop;
   cudaGetDeviceProperties(&prop, cfg->device);
   e->num_sms = prop.multiProcessorCount;
+  { const char* ev = getenv("RMB_NO_STEM_POOL"); e->fuse_stem_pool = !(ev != nullptr && ev[0] == '1'); }
   e->Hf = cfg->img_h / 32; e->Wf = cfg->img_w / 32;
-  e->L = 2 + e->Hf * e->Wf * cfg->num_cams;
+  e->n_prefix = 2 + (cfg->task_token ? 1 : 0);
+  e->L = e->n_prefix + e->Hf * e->Wf * cfg->num_cams;
   e->n_img_max = cfg->max_batch * cfg->num_cams;
   *out = e;
   return 0;
@@ -412,7 +427,7 @@ int rmb_act_finalize(rmb_act_engine_t* e) {
     const auto* ws = find_w(e, "model.input_proj_robot_state.weight", (size_t)D * c.state_dim, &err); if (!ws) return fail(err);
     const auto* bs = find_w(e, "model.input_proj_robot_state.bias", D, &err); if (!bs) return fail(err);
     const auto* lb = find_w(e, "model.latent_out_proj.bias", D, &err); if (!lb) return fail(err);
-    const auto* ap = find_w(e, "model.additional_pos_embed.weight", 2 * D, &err); if (!ap) return fail(err);
+    const auto* ap = find_w(e, "model.additional_pos_embed.weight", (size_t)e->n_prefix * D, &err); if (!ap) return fail(err);
     if (!upload_f32(e, *wh, &e->w_head, &err) || !upload_f32(e, *bh, &e->b_head, &err) || !upload_f32(e, *ws, &e->w_state, &err) ||
         !upload_f32(e, *bs, &e->b_state, &err) || !upload_f32(e, *lb, &e->latent_bias, &err))
       return fail(err);
@@ -420,7 +435,7 @@ int rmb_act_finalize(rmb_act_engine_t* e) {
     // (position_encoding.py:30-52) of a (Hf, Wf) map, identical for every camera, cameras folded along width
     // (detr_vae.py:140-141): token 2 + h*(Wf*Ncam) + cam*Wf + w.
     std::vector<float> pos((size_t)e->L * D);
-    for (int i = 0; i < 2 * D; ++i) pos[i] = (*ap)[i];
+    for (int i = 0; i < e->n_prefix * D; ++i) pos[i] = (*ap)[i];
     const float two_pi = 2.0f * 3.14159265358979323846f;
     for (int h = 0; h < e->Hf; ++h)
       for (int w = 0; w < e->Wf; ++w) {
@@ -434,11 +449,36 @@ int rmb_act_finalize(rmb_act_engine_t* e) {
           row[256 + i] = (i % 2 == 0) ? sinf(ax) : cosf(ax);
         }
         for (int cam = 0; cam < c.num_cams; ++cam) {
-          const size_t t = 2 + (size_t)h * (e->Wf * c.num_cams) + (size_t)cam * e->Wf + w;
+          const size_t t = e->n_prefix + (size_t)h * (e->Wf * c.num_cams) + (size_t)cam * e->Wf + w;
           memcpy(&pos[t * D], row, sizeof(row));
         }
       }
     if (!upload_f32(e, pos, &e->pos, &err)) return fail(err);
+  }
+
+  // ---- MT-ACT: text projection and the FiLM generators of layers 2..4 (hypothesised keys, see policy/mt_act/policy.py)
+  if (c.multi_task) {
+    const int E = c.task_emb_dim;
+    const auto* wt = find_w(e, "model.proj_text_emb.weight", (size_t)D * E, &err); if (!wt) return fail(err);
+    const auto* bt = find_w(e, "model.proj_text_emb.bias", D, &err); if (!bt) return fail(err);
+    std::vector<float> wf, bf;
+    const int planes[3] = {128, 256, 512};
+    for (int i = 0; i < 3; ++i) {
+      const std::string p = "model.backbones.0.0.film_models." + std::to_string(i + 1) + ".";
+      const auto* w = find_w(e, p + "weight", (size_t)4 * planes[i] * D, &err); if (!w) return fail(err);
+      const auto* b = find_w(e, p + "bias", (size_t)4 * planes[i], &err); if (!b) return fail(err);
+      wf.insert(wf.end(), w->begin(), w->end());
+      bf.insert(bf.end(), b->begin(), b->end());
+    }
+    if (!upload_act(e, *wt, &e->w_text, &err) || !upload_f32(e, *bt, &e->b_text, &err) ||
+        !upload_act(e, wf, &e->w_film, &err) || !upload_f32(e, bf, &e->b_film, &err))
+      return fail(err);
+    bool ok = true;
+    ok &= (e->task_emb_act = e->dalloc<act_t>((size_t)c.max_batch * E)) != nullptr;
+    ok &= (e->task_tok_act = e->dalloc<act_t>((size_t)c.max_batch * D)) != nullptr;
+    ok &= (e->task_tok = e->dalloc<float>((size_t)c.max_batch * D)) != nullptr;
+    ok &= (e->film = e->dalloc<float>((size_t)c.max_batch * rmb_act_engine::kFilmLd)) != nullptr;
+    if (!ok) return fail("cudaMalloc failed (task embedding buffers)");
   }
 
   // ---- workspace
@@ -447,7 +487,7 @@ int rmb_act_finalize(rmb_act_engine_t* e) {
     const size_t BL = (size_t)c.max_batch * e->L, BC = (size_t)c.max_batch * C;
     bool ok = true;
     ok &= (e->x0 = e->dalloc<act_t>(NI * H * (W + 8) * 4)) != nullptr;
-    ok &= (e->c1 = e->dalloc<act_t>(NI * (H / 2) * (W / 2) * 64)) != nullptr;
+    if (!e->fuse_stem_pool) ok &= (e->c1 = e->dalloc<act_t>(NI * (H / 2) * (W / 2) * 64)) != nullptr;
     for (int li = 0; li < 4; ++li)
       for (int k = 0; k < 3; ++k)
         ok &= (e->stage[li][k] = e->dalloc<act_t>(NI * (H >> (2 + li)) * (W >> (2 + li)) * chans[li])) != nullptr;
@@ -485,7 +525,11 @@ static int build_plans(rmb_act_engine* e, int nb, rmb_act_engine::BatchPlans** o
   const rmb_act_config_t& c = e->cfg;
   const int NI = nb * c.num_cams, H = c.img_h, W = c.img_w, D = 512, FF = c.dim_feedforward, C = c.chunk_size, L = e->L;
   const int chans[4] = {64, 128, 256, 512};
-  if (!plan_conv1_halo(&bp->stem, e->x0, NI, H, W, e->stem.w, e->stem.b, e->c1, &err)) return fail(err);
+  if (e->fuse_stem_pool) {
+    if (!plan_stem_pool(&bp->stem_pool, e->x0, NI, H, W, e->stem.w, e->stem.b, e->stage[0][2], e->num_sms, &err)) return fail(err);
+  } else {
+    if (!plan_conv1_halo(&bp->stem, e->x0, NI, H, W, e->stem.w, e->stem.b, e->c1, &err)) return fail(err);
+  }
   // stage buffers: [0] = t (mid), [1] = y (block 0 out), [2] = d (downsample) then z (block 1 out)
   for (int li = 0; li < 4; ++li) {
     const int h = H >> (2 + li), w = W >> (2 + li);
@@ -509,10 +553,20 @@ static int build_plans(rmb_act_engine* e, int nb, rmb_act_engine::BatchPlans** o
     if (!plan_conv(&bp->conv[li][0][1], t, NI, h, w, chans[li], 3, 1, e->blk[li][0][1].w, chans[li], e->blk[li][0][1].b, identity, false, y, chans[li], false, true, &err)) return fail(err);
     if (!plan_conv(&bp->conv[li][1][0], y, NI, h, w, chans[li], 3, 1, e->blk[li][1][0].w, chans[li], e->blk[li][1][0].b, nullptr, false, t, chans[li], false, true, &err)) return fail(err);
     if (!plan_conv(&bp->conv[li][1][1], t, NI, h, w, chans[li], 3, 1, e->blk[li][1][1].w, chans[li], e->blk[li][1][1].b, y, false, z, chans[li], false, true, &err)) return fail(err);
+    if (c.multi_task) {
+      // per-episode layout of e->film: layer base, then [gamma | beta] x [block 0 | block 1] x planes
+      const int base = (li == 1) ? 0 : (li == 2) ? 4 * 128 : 4 * 128 + 4 * 256;
+      for (int bi = 0; bi < 2; ++bi) {
+        GemmParams& fp = bp->conv[li][bi][1].p;
+        fp.film = e->film; fp.film_ld = rmb_act_engine::kFilmLd; fp.film_div = c.num_cams;
+        fp.film_g_off = base + (0 * 2 + bi) * chans[li];
+        fp.film_b_off = base + (1 * 2 + bi) * chans[li];
+      }
+    }
   }
   // input_proj: 1x1 conv whose output rows are scattered straight into token order, fp32 residual stream
   if (!plan_conv(&bp->input_proj, e->stage[3][2], NI, e->Hf, e->Wf, 512, 1, 1, e->input_proj.w, D, e->input_proj.b, nullptr, false, e->tok_f32, D, true, false, &err)) return fail(err);
-  bp->input_proj.p.remap_ncam = c.num_cams; bp->input_proj.p.remap_L = L; bp->input_proj.p.remap_off = 2;
+  bp->input_proj.p.remap_ncam = c.num_cams; bp->input_proj.p.remap_L = L; bp->input_proj.p.remap_off = e->n_prefix;
 
   const long long BL = (long long)nb * L, BC = (long long)nb * C;
   bp->enc.resize(c.enc_layers);
@@ -542,7 +596,7 @@ int rmb_act_forward_num_launches(const rmb_act_engine_t* e) {
   if (!e) return -1;
   // preprocess, stem, maxpool, 16 convs + 3 downsamples, input_proj, extra tokens, cast(+pos), 8 per encoder layer,
   // decoder: K, V, attention, out, LN, FF1, FF2, head
-  return 3 + 19 + 3 + 8 * e->cfg.enc_layers + 8;
+  return (e->fuse_stem_pool ? 2 : 3) + 19 + 3 + 8 * e->cfg.enc_layers + 8;
 }
 
 double rmb_act_forward_flops(const rmb_act_engine_t* e, int batch) {
@@ -683,6 +737,8 @@ static int forward_impl(rmb_act_engine_t* e, const void* d_images, int image_for
   if (!e->finalized) return fail("rmb_act_forward: weights not finalized");
   if (batch < 1 || batch > e->cfg.max_batch) return fail("rmb_act_forward: batch out of range");
   if (image_format != 0 && image_format != 1) return fail("rmb_act_forward: image_format must be 0 (u8 HWC) or 1 (f32 CHW)");
+  if (e->cfg.multi_task && e->task_batch < batch)
+    return fail("rmb_act_forward: multi-task engine without a task embedding for every episode (call rmb_act_set_task_embedding)");
   PdlScope pdl;   // every launch below is a pdl_wait()-aware kernel (launch.h)
   rmb_act_engine::BatchPlans* bp = nullptr;
   if (int r = build_plans(e, batch, &bp)) return r;
@@ -750,8 +806,15 @@ static int forward_impl(rmb_act_engine_t* e, const void* d_images, int image_for
     end();
     scan(e->x0, (long long)NI * H * (W + 8) * 4);
   }
-  RMB_RUN(run_halo("stem conv7x7/2", bp->stem, (double)NI * H * (W + 8) * 8));
-  {
+  if (e->fuse_stem_pool) {
+    // algorithmic bytes: the padded 16-bit image in, the pooled map out (the conv output never reaches HBM)
+    begin("stem conv7x7/2 + maxpool3x3/2", "stem_pool_kernel", (double)bp->stem_pool.flops,
+          (double)NI * H * (W + 8) * 8 + 64 * 224 * 2 + (double)NI * (H / 4) * (W / 4) * 128);
+    RMB_CUDA(launch_stem_pool(bp->stem_pool, s));
+    end();
+    scan(e->stage[0][2], (long long)NI * (H / 4) * (W / 4) * 64);
+  } else {
+    RMB_RUN(run_halo("stem conv7x7/2", bp->stem, (double)NI * H * (W + 8) * 8));
     const long long items = (long long)NI * (H / 4) * (W / 4) * 8;
     begin("maxpool3x3/2", "maxpool3x3s2_kernel", 0, (double)NI * (H / 2) * (W / 2) * 128 + (double)NI * (H / 4) * (W / 4) * 128);
     RMB_CUDA(launch_pdl(maxpool3x3s2_kernel, dim3(grid_for(items, 256, sms)), dim3(256), 0, s, (const act_t*)e->c1, e->stage[0][2], NI, H / 2, W / 2, 64));
@@ -777,8 +840,8 @@ static int forward_impl(rmb_act_engine_t* e, const void* d_images, int image_for
     snprintf(nm, sizeof(nm), "layer%d.1.conv2 3x3", li + 1); RMB_RUN(run_gemm(nm, bp->conv[li][1][1], mid_b));
   }
   RMB_RUN(run_gemm("input_proj 1x1 -> tokens", bp->input_proj, (double)NI * e->Hf * e->Wf * 512 * 2));
-  begin("latent+proprio tokens", "act_extra_tokens_kernel", 0, (double)batch * 2 * 512 * 4);
-  RMB_CUDA(launch_pdl(act_extra_tokens_kernel, dim3(batch), dim3(256), 0, s, d_qpos, c.state_dim, (const float*)e->latent_bias, (const float*)e->w_state, (const float*)e->b_state, e->tok_f32, L));
+  begin("latent+proprio tokens", "act_extra_tokens_kernel", 0, (double)batch * e->n_prefix * 512 * 4);
+  RMB_CUDA(launch_pdl(act_extra_tokens_kernel, dim3(batch), dim3(256), 0, s, d_qpos, c.state_dim, (const float*)e->latent_bias, (const float*)e->w_state, (const float*)e->b_state, (const float*)(c.task_token ? e->task_tok : nullptr), e->tok_f32, L));
   end();
   const int ln_grid = grid_for(BL * 32, 256, sms);
   begin("tokens cast(+pos)", "layernorm512_kernel", 0, (double)BL * 512 * (4 + 2 + 2));
@@ -833,6 +896,26 @@ static int forward_impl(rmb_act_engine_t* e, const void* d_images, int image_for
   end();
 #undef RMB_RUN
   RMB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int rmb_act_set_task_embedding(rmb_act_engine_t* e, const float* d_task_emb, int batch, void* stream_) {
+  if (!e || !d_task_emb) return fail("rmb_act_set_task_embedding: null argument");
+  if (!e->finalized) return fail("rmb_act_set_task_embedding: weights not finalized");
+  if (!e->cfg.multi_task) return fail("rmb_act_set_task_embedding: engine was not created with multi_task");
+  if (batch < 1 || batch > e->cfg.max_batch) return fail("rmb_act_set_task_embedding: batch out of range");
+  cudaStream_t s = static_cast<cudaStream_t>(stream_);
+  const int E = e->cfg.task_emb_dim, D = 512, F = rmb_act_engine::kFilmLd;
+  std::string err;
+  GemmPlan proj, film;
+  if (!plan_linear(&proj, e->task_emb_act, batch, E, E, e->w_text, D, e->b_text, nullptr, 0, false, e->task_tok, D, true, false, &err)) return fail(err);
+  if (!plan_linear(&film, e->task_tok_act, batch, D, D, e->w_film, F, e->b_film, nullptr, 0, false, e->film, F, true, false, &err)) return fail(err);
+  cast_f32_to_act_kernel<<<grid_for((long long)batch * E, 256, e->num_sms), 256, 0, s>>>(d_task_emb, e->task_emb_act, (long long)batch * E);
+  RMB_CUDA(launch_gemm(proj, e->num_sms, s));
+  cast_f32_to_act_kernel<<<grid_for((long long)batch * D, 256, e->num_sms), 256, 0, s>>>(e->task_tok, e->task_tok_act, (long long)batch * D);
+  RMB_CUDA(launch_gemm(film, e->num_sms, s));
+  RMB_CUDA(cudaGetLastError());
+  e->task_batch = batch;
   return 0;
 }
 
@@ -972,6 +1055,16 @@ int rmb_conv1_stem(const void* d_in_padded, const void* d_Wt, const float* d_bia
   std::string err;
   if (!plan_conv1_halo(&g, d_in_padded, B, H, W, d_Wt, d_bias, d_out, &err)) return fail(err);
   RMB_CUDA(launch_halo(g, device_sms(), static_cast<cudaStream_t>(stream_)));
+  return 0;
+}
+
+int rmb_stem_pool(const void* d_in_padded, const void* d_Wt, const float* d_bias, void* d_out, int B, int H, int W,
+                  void* stream_) {
+  if (!d_in_padded || !d_Wt || !d_out) return fail("rmb_stem_pool: null argument");
+  StemPoolPlan g;
+  std::string err;
+  if (!plan_stem_pool(&g, d_in_padded, B, H, W, d_Wt, d_bias, d_out, device_sms(), &err)) return fail(err);
+  RMB_CUDA(launch_stem_pool(g, static_cast<cudaStream_t>(stream_)));
   return 0;
 }
 

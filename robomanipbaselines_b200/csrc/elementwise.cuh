@@ -199,9 +199,11 @@ __global__ void layernorm512_kernel(const float* __restrict__ x_in, const float*
 // ---------------------------------------------------------------------------------------------------------------------
 // Tokens 0 (latent) and 1 (proprio) of every episode (detr_vae.py:124-125,138; transformer.py:62-63), fp32 [B, L, 512].
 //   latent token = latent_out_proj.bias (latent sample is zeros); proprio = input_proj_robot_state(qpos).
+//   task_tok (MT-ACT with the task token switched on, else nullptr): third prefix token = proj_text_emb(task_emb).
 __global__ void act_extra_tokens_kernel(const float* __restrict__ qpos, int Ds, const float* __restrict__ latent_bias,
                                         const float* __restrict__ w_state,  // [512, Ds]
-                                        const float* __restrict__ b_state, float* __restrict__ x_f32, int L) {
+                                        const float* __restrict__ b_state, const float* __restrict__ task_tok,
+                                        float* __restrict__ x_f32, int L) {
   pdl_trigger();
   pdl_wait();
   const int b = blockIdx.x;
@@ -210,7 +212,15 @@ __global__ void act_extra_tokens_kernel(const float* __restrict__ qpos, int Ds, 
     for (int k = 0; k < Ds; ++k) acc += w_state[c * Ds + k] * qpos[b * Ds + k];
     x_f32[(static_cast<long long>(b) * L + 0) * kD + c] = latent_bias[c];
     x_f32[(static_cast<long long>(b) * L + 1) * kD + c] = acc;
+    if (task_tok != nullptr) x_f32[(static_cast<long long>(b) * L + 2) * kD + c] = task_tok[static_cast<long long>(b) * kD + c];
   }
+}
+
+// fp32 -> 16-bit operand cast (task embeddings of MT-ACT in front of their projection GEMMs)
+__global__ void cast_f32_to_act_kernel(const float* __restrict__ x, act_t* __restrict__ y, long long n) {
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<long long>(gridDim.x) * blockDim.x)
+    y[i] = to_act(x[i]);
 }
 
 // ---------------------------------------------------------------------------------------------------------------------

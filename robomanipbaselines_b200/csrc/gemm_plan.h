@@ -8,6 +8,7 @@
 #include <string>
 
 #include "conv_halo.cuh"
+#include "stem_pool.cuh"
 #include "gemm_tc.cuh"
 #include "launch.h"
 #include "tma_host.h"
@@ -71,6 +72,7 @@ inline void fill_common(GemmParams& p, const float* bias, const void* residual, 
   p.out = out; p.ld_out = ld_out; p.out_f32 = out_f32 ? 1 : 0; p.relu = relu ? 1 : 0;
   p.remap_ncam = 0; p.remap_L = 0; p.remap_off = 0;
   p.n_valid = 1 << 30;
+  p.film = nullptr; p.film_ld = 0; p.film_g_off = 0; p.film_b_off = 0; p.film_div = 1;
 }
 
 // out[M, N] = A[M, K] (row-major, leading dim lda) * Wt[N, K]^T
@@ -263,7 +265,12 @@ inline cudaError_t launch_gemm_variant(const GemmPlan& g, int num_sms, cudaStrea
       if (!has_res && g.tma_out) return launch_gemm_instance<BN, BK, ST, false, 0, PAIR, 3>(g, num_sms, stream);
     }
     if (!has_res) return launch_gemm_instance<BN, BK, ST, false, 0, PAIR>(g, num_sms, stream);
-    if (!g.p.res_f32) return launch_gemm_instance<BN, BK, ST, false, 1, PAIR>(g, num_sms, stream);
+    if (!g.p.res_f32) {
+      if constexpr (BK == 64) {
+        if (g.p.film != nullptr) return launch_gemm_instance<BN, BK, ST, false, 1, PAIR, 4>(g, num_sms, stream);
+      }
+      return launch_gemm_instance<BN, BK, ST, false, 1, PAIR>(g, num_sms, stream);
+    }
   } else {
     if (!has_res) return launch_gemm_instance<BN, BK, ST, true, 0, PAIR>(g, num_sms, stream);
     if (g.p.res_f32) return launch_gemm_instance<BN, BK, ST, true, 2, PAIR>(g, num_sms, stream);
@@ -427,6 +434,69 @@ inline bool plan_conv1_halo(HaloPlan* g, const void* in_padded, int B, int H, in
   g->tres = g->tout;
   g->flops = 2ll * B * OH * OW * 64 * 147;
   return true;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Fused stem + max-pool (stem_pool.cuh)
+struct StemPoolPlan {
+  CUtensorMap ta, tb;
+  StemPoolParams p;
+  int smem = 0, grid = 0;
+  long long flops = 0;
+};
+
+// in_padded: the NHWC4 image of preprocess_*_kernel [B, H, W + 8, 4]; out: pooled [B, H/4, W/4, 64]
+inline bool plan_stem_pool(StemPoolPlan* g, const void* in_padded, int B, int H, int W, const void* Wt, const float* bias,
+                           void* out, int num_sms, std::string* err) {
+  *g = StemPoolPlan();
+  if (H % 8 != 0 || W % 4 != 0 || B < 1) { if (err) *err = "plan_stem_pool: H must be a multiple of 8 and W of 4"; return false; }
+  const int OH = H / 2, OW = W / 2, Wp = W + 8;
+  StemPoolParams& p = g->p;
+  memset(&p, 0, sizeof(p));
+  p.n_img = B; p.OH = OH; p.OW = OW;
+  p.strips = (OW + kSpBoxW - 1) / kSpBoxW;
+  const int TR = OH / kSpBoxH;
+  // bands per image: a divisor of the tile rows; more bands = better balance over the 2 x SMs epilogue groups, fewer =
+  // less warm-up recomputation (one tile row per band that does not start at the image top)
+  double best = 1e30; int best_nbi = 0;
+  for (int nbi = 1; nbi <= TR; ++nbi) {
+    if (TR % nbi != 0 || TR / nbi > kSpMaxBandRows) continue;
+    const long long bands = 1ll * B * nbi;
+    const long long groups = 2 * std::min<long long>(num_sms, (bands + 1) / 2);
+    const long long rounds = (bands + groups - 1) / groups;
+    const double rows = TR / nbi + (nbi > 1 ? static_cast<double>(nbi - 1) / nbi : 0.0);
+    const double cost = static_cast<double>(rounds) * rows;
+    if (cost < best - 1e-9) { best = cost; best_nbi = nbi; }
+  }
+  if (best_nbi == 0) { if (err) *err = "plan_stem_pool: no band split fits"; return false; }
+  p.bands_per_img = best_nbi; p.rows_band = TR / best_nbi; p.n_bands = B * best_nbi;
+  p.bias = bias; p.out = static_cast<act_t*>(out);
+  const int fixed = kSpWBytes + 2 * kSpGroupBytes + 256 + 1024;
+  p.n_stages = std::min<int>(kSpMaxStages, (kMaxDynSmem - fixed) / kSpBoxBytes);
+  if (p.n_stages < 2) { if (err) *err = "plan_stem_pool: shared memory"; return false; }
+  g->smem = fixed + p.n_stages * kSpBoxBytes;
+  g->grid = static_cast<int>(std::min<long long>(num_sms, (1ll * p.n_bands + 1) / 2));
+  const uint64_t rowb = (uint64_t)Wp * 8;                    // bytes per padded image row
+  const uint64_t dims[5] = {32, (uint64_t)OW, 2, (uint64_t)H / 2, (uint64_t)B};
+  const uint64_t strides[4] = {16, rowb, 2 * rowb, (uint64_t)H * rowb};
+  const uint32_t box[5] = {32, (uint32_t)kSpBoxW, 1, (uint32_t)(kSpBoxH + 3), 1};
+  if (!make_tmap_act(&g->ta, in_padded, 5, dims, strides, box, 64, err)) return false;
+  const uint64_t wdims[2] = {224, 64};
+  const uint64_t wstr[1] = {224 * 2};
+  const uint32_t wbox[2] = {32, 64};
+  if (!make_tmap_act(&g->tb, Wt, 2, wdims, wstr, wbox, 64, err)) return false;
+  g->flops = 2ll * B * OH * OW * 64 * 147;
+  return true;
+}
+
+inline cudaError_t launch_stem_pool(const StemPoolPlan& g, cudaStream_t stream) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(stem_pool_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
+    if (e != cudaSuccess) return e;
+    attr_set = true;
+  }
+  return launch_pdl(stem_pool_kernel, dim3(g.grid), dim3(kGemmThreads), g.smem, stream, g.ta, g.tb, g.p);
 }
 
 template <int BK, int RES>

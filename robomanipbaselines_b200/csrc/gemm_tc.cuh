@@ -48,6 +48,10 @@ struct GemmParams {
   const void* gn_res;        // act_t [rows, gn_ld_res] or nullptr
   int gn_ld_res;
   int gn_cg;                 // channels per group = N / 8
+  // per-episode FiLM of the MT-ACT backbone (EPI == 4): out = relu((1 + gamma) * (acc + bias) + beta + residual), with
+  // gamma = film[ep * film_ld + film_g_off + c], beta = film[ep * film_ld + film_b_off + c], ep = image / film_div
+  const float* film;
+  int film_ld, film_g_off, film_b_off, film_div;
 };
 
 // PAIR: two CTAs of a cluster work on one 256-row tile (tcgen05 cta_group::2); each holds its 128 rows of A and half
@@ -83,7 +87,7 @@ struct TileSched {
 
 // ---------------------------------------------------------------------------------------------------------------------
 // Epilogue shared by the GEMM / conv kernels (warps 0..7 of the CTA).
-template <int BLOCK_N, bool OUT_F32, int RES, bool PAIR>
+template <int BLOCK_N, bool OUT_F32, int RES, bool PAIR, bool FILM = false>
 __device__ __forceinline__ void gemm_epilogue(const GemmParams& p, uint8_t* smem_stage, uint32_t tmem_base,
                                               uint64_t* tmem_full_bar, uint64_t* tmem_empty_bar,
                                               const TileSched<PAIR>& ts, int warp, int lane) {
@@ -126,7 +130,9 @@ __device__ __forceinline__ void gemm_epilogue(const GemmParams& p, uint8_t* smem
     const int w = wt * p.box_w + wl, h = ht * p.box_h + hl, b = bt * p.box_b + bl;
     const bool valid = (r < rows_per_tile) && (w < p.W) && (h < p.H) && (b < p.B);
     int my_grow = -1, my_orow = -1;               // source row (residual, natural pixel order) / destination row
+    int my_film = 0;                              // FiLM row offset of this row's episode
     if (valid) {
+      if (FILM) my_film = (b / p.film_div) * p.film_ld;
       my_grow = (b * p.H + h) * p.W + w;
       my_orow = my_grow;
       if (p.remap_ncam > 0)
@@ -144,8 +150,10 @@ __device__ __forceinline__ void gemm_epilogue(const GemmParams& p, uint8_t* smem
     }
     char* optr[8];
     const char* rptr[8];
+    const float* fptr[8];
   #pragma unroll
     for (int it = 0; it < 8; ++it) {
+      fptr[it] = FILM ? p.film + __shfl_sync(0xffffffffu, my_film, it * 4 + rsel) + col0 : nullptr;
       const int orow = __shfl_sync(0xffffffffu, my_orow, it * 4 + rsel);
       optr[it] = (orow >= 0) ? static_cast<char*>(p.out) + (static_cast<long long>(orow) * p.ld_out + col0) * kOutEsz : nullptr;
       if (RES != 0) {
@@ -176,6 +184,19 @@ __device__ __forceinline__ void gemm_epilogue(const GemmParams& p, uint8_t* smem
       float4 f[8];
   #pragma unroll
       for (int it = 0; it < 8; ++it) f[it] = ld_shared_v4f(((it & 1) ? ld_odd : ld_even) + (it >> 1) * 1024);
+      if (FILM) {
+        // bn2 output (acc + folded bias) modulated per episode BEFORE the identity branch is added; the bias is
+        // consumed here, so the common tail below adds zero
+  #pragma unroll
+        for (int it = 0; it < 8; ++it) {
+          if (optr[it] == nullptr) continue;
+          const float4 g4 = __ldg(reinterpret_cast<const float4*>(fptr[it] + p.film_g_off + j * 64));
+          const float4 b4 = __ldg(reinterpret_cast<const float4*>(fptr[it] + p.film_b_off + j * 64));
+          f[it].x = (1.0f + g4.x) * (f[it].x + bv.x) + b4.x; f[it].y = (1.0f + g4.y) * (f[it].y + bv.y) + b4.y;
+          f[it].z = (1.0f + g4.z) * (f[it].z + bv.z) + b4.z; f[it].w = (1.0f + g4.w) * (f[it].w + bv.w) + b4.w;
+        }
+        bv = make_float4(0.f, 0.f, 0.f, 0.f);
+      }
       if (RES == 2) {
         float4 rv[8];
   #pragma unroll
@@ -292,7 +313,7 @@ __device__ __forceinline__ void gemm_gn_epilogue(const GemmParams& p, uint8_t* s
 
 // OUT_F32: fp32 output (else act_t). RES: 0 no residual, 1 act_t residual, 2 fp32 residual.
 // EPI: 0 plain epilogue (bias / residual / ReLU); fused GroupNorm + Mish (gemm_gn.cuh) followed by 1: FiLM, 2: residual;
-// 3: plain 16-bit output through a TMA store (tmap_out; the other modes ignore it).
+// 3: plain 16-bit output through a TMA store (tmap_out; the other modes ignore it); 4: plain + per-episode FiLM (MT-ACT).
 // PAIR: launched as clusters of two CTAs (gemm_tc_pair_kernel); see GemmSmem / TileSched.
 template <int BLOCK_N, int BLOCK_K, int STAGES, bool OUT_F32, int RES, int EPI, bool PAIR>
 __device__ __forceinline__ void gemm_tc_body(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, const CUtensorMap& tmap_out,
@@ -435,6 +456,8 @@ __device__ __forceinline__ void gemm_tc_body(const CUtensorMap& tmap_a, const CU
   } else {
     if constexpr (EPI == 3)
       gemm_epilogue_tma<BLOCK_N, PAIR>(&tmap_out, p, smem_stage, tmem_base, tmem_full_bar, tmem_empty_bar, ts, warp, lane);
+    else if constexpr (EPI == 4)
+      gemm_epilogue<BLOCK_N, OUT_F32, RES, PAIR, true>(p, smem_stage, tmem_base, tmem_full_bar, tmem_empty_bar, ts, warp, lane);
     else if constexpr (EPI != 0)
       gemm_gn_epilogue<BLOCK_N, EPI == 1, PAIR>(p, smem_stage, tmem_base, tmem_full_bar, tmem_empty_bar, ts, warp, lane);
     else

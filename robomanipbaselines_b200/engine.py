@@ -12,12 +12,14 @@ class ActEngine:
     """One engine per GPU. Owns the bf16 weight arena and the activation workspace (sized for max_batch)."""
 
     def __init__(self, *, max_batch, num_cams, img_h, img_w, state_dim, action_dim, hidden_dim=512,
-                 dim_feedforward=3200, nheads=8, enc_layers=4, dec_layers=7, chunk_size=100, device=0):
+                 dim_feedforward=3200, nheads=8, enc_layers=4, dec_layers=7, chunk_size=100, device=0,
+                 multi_task=False, task_emb_dim=384, task_token=False):
         if not torch.cuda.is_available():
             raise _lib.RmbError("ActEngine needs a CUDA device (sm_100a); there is no CPU fallback")
         self.lib = _lib.load()
         self.cfg = ActConfig(max_batch, num_cams, img_h, img_w, state_dim, action_dim, hidden_dim, dim_feedforward,
-                             nheads, enc_layers, dec_layers, chunk_size, device)
+                             nheads, enc_layers, dec_layers, chunk_size, device, int(bool(multi_task)),
+                             int(task_emb_dim) if multi_task else 0, int(bool(task_token)))
         self.device = torch.device("cuda", device)
         self._h = ctypes.c_void_p()
         check(self.lib.rmb_act_engine_create(ctypes.byref(self.cfg), ctypes.byref(self._h)), "rmb_act_engine_create")
@@ -82,7 +84,18 @@ class ActEngine:
 
     @property
     def seq_len(self):
-        return 2 + (self.cfg.img_h // 32) * (self.cfg.img_w // 32) * self.cfg.num_cams
+        return 2 + self.cfg.task_token + (self.cfg.img_h // 32) * (self.cfg.img_w // 32) * self.cfg.num_cams
+
+    def set_task_embedding(self, task_emb):
+        """MT-ACT: float32 (B, task_emb_dim) sentence embeddings, one per episode; the projected token and the FiLM
+        gamma / beta stay resident in the engine until the next call (RolloutMtAct.get_task_emb caches likewise)."""
+        if task_emb.dtype != torch.float32 or task_emb.dim() != 2 or task_emb.shape[1] != self.cfg.task_emb_dim:
+            raise ValueError(f"task_emb must be float32 (B, {self.cfg.task_emb_dim})")
+        if not task_emb.is_cuda:
+            raise ValueError("task_emb must be a CUDA tensor")
+        task_emb = task_emb.contiguous()
+        check(self.lib.rmb_act_set_task_embedding(self._h, ptr(task_emb), task_emb.shape[0], cur_stream()),
+              "rmb_act_set_task_embedding")
 
     def attention_debug(self, on=True, episode=0):
         """Opt-in: keep the head-averaged encoder self-attention maps of one episode (RolloutAct.draw_plot)."""
@@ -104,7 +117,7 @@ class ActEngine:
         return check(self.lib.rmb_saturation_count(int(bool(clear))), "rmb_saturation_count")
 
     def debug_read(self, which, batch):
-        L = 2 + (self.cfg.img_h // 32) * (self.cfg.img_w // 32) * self.cfg.num_cams
+        L = self.seq_len
         out = torch.empty(batch, L, 512, device=self.device)
         check(self.lib.rmb_act_debug_read(self._h, which, ptr(out), batch, cur_stream()), "rmb_act_debug_read")
         return out

@@ -181,6 +181,10 @@ class ACTPolicy(nn.Module):
         self._invalidate()
         return out
 
+    def engine_kwargs(self):
+        """Extra ActEngine options of subclasses (MT-ACT)."""
+        return {}
+
     def engine_for(self, batch, img_h, img_w, device):
         """(Re)build the device engine for this image size; the workspace grows to the largest batch seen."""
         dev_index = device.index if device.index is not None else torch.cuda.current_device()
@@ -193,7 +197,7 @@ class ACTPolicy(nn.Module):
                                      state_dim=self.state_dim, action_dim=self.action_dim, hidden_dim=a["hidden_dim"],
                                      dim_feedforward=a["dim_feedforward"], nheads=a["nheads"],
                                      enc_layers=a["enc_layers"], dec_layers=a["dec_layers"],
-                                     chunk_size=a["num_queries"], device=dev_index)
+                                     chunk_size=a["num_queries"], device=dev_index, **self.engine_kwargs())
             self._engine.load_state_dict(self.state_dict())
             self._engine_key = key
             self.max_batch = max_batch

@@ -18,7 +18,7 @@ PT="python -m pytest -q -s -m gpu -p no:cacheprovider"
 run t_elem 300 $PT tests/test_kernels_gpu.py -k "maxpool or layernorm or ensemble or normalize"
 run t_gemm 300 $PT tests/test_kernels_gpu.py -k "test_gemm"
 run t_conv 300 $PT tests/test_kernels_gpu.py -k "test_conv"
-run t_stem 300 $PT tests/test_kernels_gpu.py -k "preprocess_and_stem"
+run t_stem 300 $PT tests/test_kernels_gpu.py -k "preprocess_and_stem or stem_pool"
 run t_attn 300 $PT tests/test_kernels_gpu.py -k "test_attention"
 run t_engine 600 $PT tests/test_act_engine_gpu.py
 ENGINE_RC=$?
@@ -26,6 +26,7 @@ run t_diffusion 900 $PT tests/test_diffusion_gpu.py
 run t_pointcloud 300 $PT tests/test_pointcloud_gpu.py
 run t_resize 300 $PT tests/test_resize_gpu.py
 run t_glue 300 $PT tests/test_rollout_glue_gpu.py
+run t_mtact 600 $PT tests/test_mt_act_gpu.py
 run t_classes 600 $PT tests/test_rollout_classes_gpu.py
 run t_dtype 900 $PT tests/test_dtype_builds_gpu.py
 if [ "$1" != "--no-bench" ] && [ $ENGINE_RC -eq 0 ]; then

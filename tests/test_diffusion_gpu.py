@@ -185,7 +185,7 @@ def test_batched_dp3_rollout_matches_reference_glue(cuda):
             assert br._host_pos[b] == Na - len(orcs[b].policy_action_buf)
         assert np.array_equal(br.fifo_pos.cpu().numpy(), br._host_pos)       # the host mirror is exact
     assert br.n_inferences == 7
-    assert br.n_inferred_episodes == 3 + 1 + 2 + 1 + 2 + 1 + 2      # only the episodes whose FIFO was empty were run
+    assert br.n_inferred_episodes == 3 + 1 + 2 + 1 + 1 + 1 + 1      # only the episodes whose FIFO was empty were run
 
 
 def _visual_core_state(seed):

@@ -125,6 +125,33 @@ def test_preprocess_and_stem(lib, cuda, B, H, W):
     assert err <= 2e-2 * max(scale, 1.0)
 
 
+@pytest.mark.parametrize("B,H,W", [(2, 64, 96), (1, 96, 160), (5, 256, 192), (3, 480, 640), (300, 64, 64)])
+def test_stem_pool_fused_is_bit_identical_to_stem_then_pool(lib, cuda, B, H, W):
+    """stem_pool_kernel (the launch the engine uses) == conv1 stem kernel followed by the max-pool kernel, bit for bit:
+    ragged last strip (W/2 = 80 = 2.5 strips), one band per image and several (warm-up tile rows, carries across
+    strips), more bands than epilogue groups (300 images), and vs the fp32 torch reference."""
+    g = torch.Generator(device="cpu").manual_seed(H + W)
+    img = torch.randint(0, 256, (B, H, W, 3), generator=g, dtype=torch.uint8).to(cuda)
+    x0 = torch.empty(B, H, W + 8, 4, device=cuda, dtype=_act_dtype())
+    check(lib.rmb_preprocess_images_u8(ptr(img), ptr(x0), B, H, W, cur_stream()), "preprocess_u8")
+    w = _bf16(torch.randn(64, 3, 7, 7, generator=g) / 147 ** 0.5).to(cuda)
+    bias = torch.randn(64, generator=g).to(cuda)
+    wt = _stem_weight(w)
+    c1 = torch.zeros(B, H // 2, W // 2, 64, device=cuda, dtype=_act_dtype())
+    check(lib.rmb_conv1_stem(ptr(x0), ptr(wt), ptr(bias), ptr(c1), B, H, W, cur_stream()), "stem")
+    pooled = torch.zeros(B, H // 4, W // 4, 64, device=cuda, dtype=_act_dtype())
+    check(lib.rmb_maxpool3x3s2_nhwc(ptr(c1), ptr(pooled), B, H // 2, W // 2, 64, cur_stream()), "maxpool")
+    fused = torch.full((B, H // 4, W // 4, 64), -7.0, device=cuda, dtype=_act_dtype())
+    check(lib.rmb_stem_pool(ptr(x0), ptr(wt), ptr(bias), ptr(fused), B, H, W, cur_stream()), "stem_pool")
+    torch.cuda.synchronize()
+    assert torch.equal(fused.view(torch.int16), pooled.view(torch.int16))
+    if B <= 5:
+        ref = F.conv2d(x0[:, :, 4:-4, :3].float().permute(0, 3, 1, 2), w.float(), bias, stride=2, padding=3).relu()
+        ref = F.max_pool2d(ref, 3, 2, 1).permute(0, 2, 3, 1)
+        err, scale = _report(f"stem+pool {B}x{H}x{W}", fused, ref)
+        assert err <= 4e-3 * max(scale, 1.0)
+
+
 def test_maxpool(lib, cuda):
     x = _bf16(torch.randn(3, 24, 32, 64)).to(cuda)
     out = torch.empty(3, 12, 16, 64, device=cuda, dtype=_act_dtype())

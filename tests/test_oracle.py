@@ -170,3 +170,37 @@ def test_dp3_rollout_oracle_matches_reference_golden(norm):
             a = o.step()
         assert np.array_equal(a, g[f"{p}_actions"][t]), t
     assert steps == list(g[f"{p}_infer_steps"])
+
+
+def test_mt_act_oracle_hypothesis_reduces_to_act():
+    """The MT-ACT branch of the oracle (architecture hypothesis, parity unpinned) with zero FiLM generators and no task
+    token must be the ACT network: it reproduces the reference's DETRVAE golden. And the policy mirror carries the
+    hypothesised extra keys next to all of ACT's."""
+    from robomanipbaselines_b200.policy.mt_act import ACTPolicy as MtPolicy
+
+    case = ACT_CASES["small"]
+    gold = np.load(os.path.join(GOLD, "act_golden_small.npz"))
+    pol = MtPolicy(policy_args(case), state_dim=case["state_dim"], action_dim=case["action_dim"])
+    shapes = {k: tuple(v.shape) for k, v in pol.state_dict().items()}
+    act_keys = set(ACTPolicy(policy_args(case), state_dim=case["state_dim"], action_dim=case["action_dim"]).state_dict())
+    extra = sorted(set(shapes) - act_keys)
+    assert extra == sorted(["model.proj_text_emb.weight", "model.proj_text_emb.bias"] +
+                           [f"model.backbones.0.0.film_models.{i}.{w}" for i in (1, 2, 3) for w in ("weight", "bias")])
+    assert shapes["model.backbones.0.0.film_models.2.weight"] == (2 * 2 * 256, 512)
+    sd = synthetic_state_dict(shapes, seed=case["weight_seed"])
+    for k in sd:
+        if "film_models" in k:
+            sd[k] = torch.zeros_like(sd[k])
+    qpos, img_u8 = act_inputs(case)
+    image = torch.from_numpy(np.concatenate([rollout_oracle.get_images(list(img_u8[b])) for b in range(case["batch"])]))
+    te = torch.randn(1, 384)
+    a = act_oracle.act_forward(sd, policy_args(case), torch.from_numpy(qpos), image, task_emb=te)
+    assert np.abs(a.numpy() - gold["a_hat"]).max() <= 2e-5
+    for k in sd:
+        if "film_models" in k:
+            sd[k] = torch.randn_like(sd[k]) * 0.1
+    b = act_oracle.act_forward(sd, policy_args(case), torch.from_numpy(qpos), image, task_emb=te)
+    assert (a - b).abs().max() > 1e-3                       # the FiLM term is live
+    tok = dict(policy_args(case), task_token=True)
+    pol3 = MtPolicy(tok, state_dim=case["state_dim"], action_dim=case["action_dim"])
+    assert tuple(pol3.state_dict()["model.additional_pos_embed.weight"].shape) == (3, 512)
