@@ -150,6 +150,12 @@ int rmb_preprocess_images_f32(const float* d_images_chw, void* d_out_act, int n_
 /* out[M,N] = A[M,K](act) * Wt[N,K]^T(act) + bias (+ residual) (ReLU); flags: bit0 relu, bit1 out fp32, bit2 residual fp32 */
 int rmb_gemm(const void* d_A, const void* d_Wt, const float* d_bias, const void* d_residual, void* d_out,
                   int64_t M, int N, int K, int flags, void* stream);
+/* LayerNorm(A[M,K] Wt[512,K]^T + bias + residual) in one launch (the encoder's out-projection / FFN down-projection
+ * with norm1 / norm2 fused, third_party/act/detr/models/transformer.py:172-178): residual, out fp32 [M,512]; optional
+ * 16-bit copies y_act = y and ypos_act = y + pos[row % L] (pos fp32 [L,512]); eps 1e-5 */
+int rmb_gemm_residual_layernorm(const void* d_A, const void* d_Wt, const float* d_bias, const float* d_residual,
+                                const float* d_gamma, const float* d_beta, const float* d_pos, int L, float* d_out,
+                                void* d_y_act, void* d_ypos_act, int64_t M, int K, void* stream);
 /* NHWC act conv k in {1,3}, stride in {1,2}, pad k/2; Wt [Cout, k*k*Cin] tap-major; residual/out [B,OH,OW,Cout] act */
 int rmb_conv2d_nhwc(const void* d_in, const void* d_Wt, const float* d_bias, const void* d_residual, void* d_out,
                          int B, int H, int W, int Cin, int Cout, int ksize, int stride, int relu, void* stream);

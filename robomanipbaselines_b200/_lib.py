@@ -116,6 +116,8 @@ SIGNATURES = {
     "rmb_preprocess_images_f32": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
     "rmb_gemm": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int,
                               c_void_p]),
+    "rmb_gemm_residual_layernorm": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int,
+                                            c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p]),
     "rmb_conv2d_nhwc": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int,
                                      c_int, c_int, c_int, c_int, c_void_p]),
     "rmb_stem_pool": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),

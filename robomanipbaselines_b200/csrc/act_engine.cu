@@ -139,6 +139,7 @@ struct rmb_act_engine {
   act_t *kd = nullptr, *vd = nullptr, *aod = nullptr, *t_b = nullptr, *hd = nullptr;
   float *yd = nullptr, *t_f32 = nullptr, *yd2 = nullptr;
 
+  bool fuse_ln = true;          // RMB_NO_LN_FUSE=1: residual GEMMs and LayerNorm as separate launches
   bool fuse_stem_pool = true;   // RMB_NO_STEM_POOL=1: stem and max-pool as two kernels through a [img, H/2, W/2, 64] buffer
   struct BatchPlans {
     HaloPlan stem;
@@ -147,7 +148,8 @@ struct rmb_act_engine {
     HaloPlan conv_l1[2][2];   // layer1 (Cin = Cout = 64): halo-reuse kernel
     GemmPlan down[4];
     GemmPlan input_proj;
-    struct Enc { GemmPlan qk, v, o, ff1, ff2; AttnPlan attn; };
+    struct Enc { GemmPlan qk, v, o, ff1, ff2, o_ln, ff2_ln; AttnPlan attn; };
+    bool ln_fused = false;    // enough rows for a 256 x 512 pair tile per SM pair: the two residual GEMMs carry their LayerNorm
     std::vector<Enc> enc;
     GemmPlan dk, dv, dout, dff1, dff2;
     AttnPlan dattn;
@@ -276,6 +278,7 @@ int rmb_act_engine_create(const rmb_act_config_t* cfg, rmb_act_engine_t** out) {
   cudaGetDeviceProperties(&prop, cfg->device);
   e->num_sms = prop.multiProcessorCount;
   { const char* ev = getenv("RMB_NO_STEM_POOL"); e->fuse_stem_pool = !(ev != nullptr && ev[0] == '1'); }
+  { const char* ev = getenv("RMB_NO_LN_FUSE"); e->fuse_ln = !(ev != nullptr && ev[0] == '1'); }
   e->Hf = cfg->img_h / 32; e->Wf = cfg->img_w / 32;
   e->n_prefix = 2 + (cfg->task_token ? 1 : 0);
   e->L = e->n_prefix + e->Hf * e->Wf * cfg->num_cams;
@@ -570,9 +573,14 @@ static int build_plans(rmb_act_engine* e, int nb, rmb_act_engine::BatchPlans** o
 
   const long long BL = (long long)nb * L, BC = (long long)nb * C;
   bp->enc.resize(c.enc_layers);
+  bp->ln_fused = e->fuse_ln && (BL + 255) / 256 >= e->num_sms / 2;
   for (int l = 0; l < c.enc_layers; ++l) {
     auto& w = e->enc[l];
     auto& pl = bp->enc[l];
+    if (bp->ln_fused) {
+      if (!plan_linear_ln(&pl.o_ln, e->ao, BL, D, D, w.w_o, w.b_o, e->tok_f32, e->x1_f32, w.g1, w.be1, nullptr, L, e->x1_b, nullptr, 1e-5f, &err)) return fail(err);
+      if (!plan_linear_ln(&pl.ff2_ln, e->hh, BL, FF, FF, w.w_2, w.b_2, e->x1_f32, e->tok_f32, w.g2, w.be2, e->pos, L, e->tok_b, e->tok_pb, 1e-5f, &err)) return fail(err);
+    }
     if (!plan_linear(&pl.qk, e->tok_pb, BL, D, D, w.w_qk, 2 * D, w.b_qk, nullptr, 0, false, e->qk, 2 * D, false, false, &err)) return fail(err);
     if (!plan_linear(&pl.v, e->tok_b, BL, D, D, w.w_v, D, w.b_v, nullptr, 0, false, e->v, D, false, false, &err)) return fail(err);
     if (!plan_attention(&pl.attn, e->qk, 2 * D, 0, false, e->qk, 2 * D, D, e->v, D, 0, e->ao, D, nb, c.nheads, L, L, &err)) return fail(err);
@@ -768,7 +776,8 @@ static int forward_impl(rmb_act_engine_t* e, const void* d_images, int image_for
   auto gemm_bytes = [&](const GemmPlan& g, double a_bytes) {
     const double rows = (double)g.p.W * g.p.H * g.p.B, N = (double)g.p.n_col_tiles * g.block_n;
     const double K = (double)g.p.num_taps * g.p.chunks_per_tap * g.block_k;
-    return a_bytes + N * K * 2 + rows * N * (g.p.out_f32 ? 4 : 2) + (g.p.residual ? rows * N * (g.p.res_f32 ? 4 : 2) : 0);
+    const double ln_extra = (g.p.ln_y_act ? rows * N * 2 : 0) + (g.p.ln_ypos_act ? rows * N * 2 : 0);
+    return a_bytes + N * K * 2 + rows * N * (g.p.out_f32 ? 4 : 2) + (g.p.residual ? rows * N * (g.p.res_f32 ? 4 : 2) : 0) + ln_extra;
   };
   // check mode: count clamped values in the 16-bit tensor the launch just stored
   auto scan = [&](const void* ptr, long long n_elems) {
@@ -785,7 +794,7 @@ static int forward_impl(rmb_act_engine_t* e, const void* d_images, int image_for
     return 0;
   };
   auto run_gemm = [&](const char* name, const GemmPlan& g, double a_bytes) -> int {
-    begin(name, g.pair ? "gemm_tc_pair_kernel" : "gemm_tc_kernel", (double)g.flops, gemm_bytes(g, a_bytes));
+    begin(name, g.ln ? "gemm_tc_pair_kernel<LN>" : g.pair ? "gemm_tc_pair_kernel" : "gemm_tc_kernel", (double)g.flops, gemm_bytes(g, a_bytes));
     RMB_CUDA(launch_gemm(g, sms, s));
     end();
     if (!g.p.out_f32 && g.p.remap_ncam == 0) scan(g.p.out, (long long)g.p.W * g.p.H * g.p.B * g.p.ld_out);
@@ -867,6 +876,12 @@ static int forward_impl(rmb_act_engine_t* e, const void* d_images, int image_for
     begin(nm, "attention_tc_kernel", attn_flops, attn_bytes);
     RMB_CUDA(launch_attention(pl.attn, s));
     end();
+    if (bp->ln_fused) {
+      snprintf(nm, sizeof(nm), "enc%d out proj +res +norm1", l); RMB_RUN(run_gemm(nm, pl.o_ln, tokb));
+      snprintf(nm, sizeof(nm), "enc%d linear1+relu", l); RMB_RUN(run_gemm(nm, pl.ff1, tokb));
+      snprintf(nm, sizeof(nm), "enc%d linear2 +res +norm2", l); RMB_RUN(run_gemm(nm, pl.ff2_ln, (double)BL * FF * 2));
+      continue;
+    }
     snprintf(nm, sizeof(nm), "enc%d out proj +res", l); RMB_RUN(run_gemm(nm, pl.o, tokb));   // y = ao Wo^T + bo + x
     snprintf(nm, sizeof(nm), "enc%d norm1", l);
     begin(nm, "layernorm512_kernel", 0, (double)BL * 512 * (4 + 4 + 2));
@@ -1028,6 +1043,17 @@ int rmb_gemm(const void* d_A, const void* d_Wt, const float* d_bias, const void*
   GemmPlan g;
   std::string err;
   if (!plan_linear(&g, d_A, M, K, K, d_Wt, N, d_bias, d_residual, N, (flags & 4) != 0, d_out, N, (flags & 2) != 0, (flags & 1) != 0, &err)) return fail(err);
+  RMB_CUDA(launch_gemm(g, device_sms(), static_cast<cudaStream_t>(stream_)));
+  return 0;
+}
+
+int rmb_gemm_residual_layernorm(const void* d_A, const void* d_Wt, const float* d_bias, const float* d_residual,
+                                const float* d_gamma, const float* d_beta, const float* d_pos, int L, float* d_out,
+                                void* d_y_act, void* d_ypos_act, int64_t M, int K, void* stream_) {
+  if (!d_A || !d_Wt) return fail("rmb_gemm_residual_layernorm: null argument");
+  GemmPlan g;
+  std::string err;
+  if (!plan_linear_ln(&g, d_A, M, K, K, d_Wt, d_bias, d_residual, d_out, d_gamma, d_beta, d_pos, L, d_y_act, d_ypos_act, 1e-5f, &err)) return fail(err);
   RMB_CUDA(launch_gemm(g, device_sms(), static_cast<cudaStream_t>(stream_)));
   return 0;
 }

@@ -1,0 +1,151 @@
+// Fused epilogue of the transformer's two residual GEMMs (attention out-projection, FFN down-projection):
+//   v = A Wt^T + bias + residual      (fp32, residual stream)          transformer.py:172-173,176-177 (src + src2)
+//   y = LayerNorm(v) * gamma + beta   (eps inside the sqrt, as torch)  transformer.py:173,178 (norm1 / norm2)
+// written as fp32 (next residual), as the 16-bit A operand of the next GEMM, and as 16-bit (y + pos) for the next
+// layer's Q/K projection -- everything layernorm512_kernel produced, without v ever being a separate HBM round trip
+// (unfused: out-proj + residual writes v, LayerNorm reads it back: 632 MB per launch at 256 episodes, HBM-bound).
+//
+// The tile is 128 rows x 512 columns = all of TMEM (gemm_tc_body's EPI == 5 mode), so rows are complete in the tile.
+// Warp e of the eight epilogue warps owns TMEM lanes 32 (e % 4).. and the 32-column chunks with (chunk % 2) == e / 4,
+// exactly as gemm_epilogue: pass 1 thread = row (tcgen05.ld -> swizzled staging), pass 2 eight lanes = one row, so
+// every residual load and output store is a full 128-byte row segment.
+//   phase A  per chunk: v = acc + bias + residual; row sums of v and v^2; v is PARKED in the fp32 output (it is
+//            rewritten below by the same lane, so it only ever lives in L2). The accumulator is released at the end of
+//            phase A: the next tile's MMAs run under phase B.
+//   exchange the two warps that share a row quarter swap their half-row sums through shared memory (64-thread barrier)
+//   phase B  per chunk: re-read v (L2 hit, same lane that wrote it), normalise, store fp32 + 16-bit (+ pos) outputs.
+#pragma once
+#include "gemm_tc.cuh"
+
+namespace rmb {
+
+template <bool PAIR>
+__device__ __forceinline__ void gemm_ln_epilogue(const GemmParams& p, uint8_t* smem_stage, uint32_t tmem_base,
+                                                 uint64_t* tmem_full_bar, uint64_t* tmem_empty_bar,
+                                                 const TileSched<PAIR>& ts, int warp, int lane) {
+  constexpr int BLOCK_N = 512;
+  constexpr int kChunks = BLOCK_N / 64;            // 32-column chunks per warp
+  const int q = warp & 3, half = warp >> 2;
+  const int sub = lane & 7, rsel = lane >> 3;
+  const uint32_t stg = smem_u32(smem_stage + warp * 4096);
+  uint32_t st_addr[8];
+#pragma unroll
+  for (int g = 0; g < 8; ++g) st_addr[g] = stg + lane * 128 + ((g ^ (lane & 7)) << 4);
+  const uint32_t ld_even = stg + rsel * 128 + ((sub ^ rsel) << 4);
+  const uint32_t ld_odd = stg + (rsel + 4) * 128 + ((sub ^ (rsel + 4)) << 4);
+  // half-row sums of this warp's 32 rows live at the start of its own staging tile between phase A and phase B
+  float2* my_stats = reinterpret_cast<float2*>(smem_stage + warp * 4096);
+  const float2* peer_stats = reinterpret_cast<const float2*>(smem_stage + (warp ^ 4) * 4096);
+  const int col0 = half * 32 + sub * 4;            // first of this lane's 4 columns inside chunk 0 of this warp
+  const long long M = p.W;
+  uint32_t acc_phase = 0;
+  for (int ti = ts.first; ti < ts.count; ti += ts.step) {
+    const int tile = ts.tile(ti);                  // n_col_tiles == 1: tile == row tile
+    const long long row_q = static_cast<long long>(tile) * 128 + q * 32;
+    // rows of this lane in pass 2: row_q + rsel + 4 it; residual / out are dense [M, 512] (plan_linear_ln), so row `it`
+    // is a compile-time offset from one base pointer; rows at or past M are never dereferenced
+    const int rows_left = static_cast<int>(min(M - row_q - rsel, static_cast<long long>(128)));   // row `it` is valid iff 4 it < rows_left
+    const float* rbase = static_cast<const float*>(p.residual) + (row_q + rsel) * BLOCK_N + col0;
+    float* obase = static_cast<float*>(p.out) + (row_q + rsel) * BLOCK_N + col0;
+#define RMB_LN_OK(it) (4 * (it) < rows_left)
+#define RMB_LN_R(it) (rbase + (it) * 4 * BLOCK_N)
+#define RMB_LN_O(it) (obase + (it) * 4 * BLOCK_N)
+    {
+      // residual rows of this quarter go to L2 while the accumulator is still being built
+      const long long grow = row_q + lane;
+      if (grow < M) {
+        const char* rrow = reinterpret_cast<const char*>(static_cast<const float*>(p.residual) + grow * BLOCK_N + half * 32);
+#pragma unroll
+        for (int j = 0; j < kChunks; ++j) prefetch_l2(rrow + j * 256);
+      }
+    }
+    mbar_wait(&tmem_full_bar[0], acc_phase);
+    tc_fence_after();
+    const uint32_t t_row = tmem_base + half * 32 + (static_cast<uint32_t>(q * 32) << 16);
+    float sum[8], sq[8];
+#pragma unroll
+    for (int it = 0; it < 8; ++it) { sum[it] = 0.f; sq[it] = 0.f; }
+    uint32_t v[32];
+    tmem_ld_32x32b_x32(t_row, v);
+    // ---------------------------------------------------------------- phase A
+#pragma unroll
+    for (int j = 0; j < kChunks; ++j) {
+      tmem_ld_wait();
+#pragma unroll
+      for (int g = 0; g < 8; ++g) st_shared_v4(st_addr[g], v[4 * g], v[4 * g + 1], v[4 * g + 2], v[4 * g + 3]);
+      if (j + 1 < kChunks) tmem_ld_32x32b_x32(t_row + (j + 1) * 64, v);
+      else tc_fence_before();
+      __syncwarp();
+      if (j + 1 == kChunks && lane == 0) ts.release_acc(tmem_empty_bar, 0);
+      const float4 bv = (p.bias != nullptr) ? __ldg(reinterpret_cast<const float4*>(p.bias + col0 + j * 64)) : make_float4(0.f, 0.f, 0.f, 0.f);
+      float4 f[8], rv[8];
+#pragma unroll
+      for (int it = 0; it < 8; ++it) f[it] = ld_shared_v4f(((it & 1) ? ld_odd : ld_even) + (it >> 1) * 1024);
+#pragma unroll
+      for (int it = 0; it < 8; ++it)
+        rv[it] = RMB_LN_OK(it) ? __ldg(reinterpret_cast<const float4*>(RMB_LN_R(it) + j * 64)) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int it = 0; it < 8; ++it) {
+        const float x = f[it].x + bv.x + rv[it].x, y = f[it].y + bv.y + rv[it].y;
+        const float z = f[it].z + bv.z + rv[it].z, w = f[it].w + bv.w + rv[it].w;
+        sum[it] += (x + y) + (z + w);
+        sq[it] += (x * x + y * y) + (z * z + w * w);
+        if (RMB_LN_OK(it)) *reinterpret_cast<float4*>(RMB_LN_O(it) + j * 64) = make_float4(x, y, z, w);
+      }
+      __syncwarp();                                // staging tile is rewritten by the next chunk's pass 1
+    }
+    // ---------------------------------------------------------------- half-row sums -> whole-row statistics
+#pragma unroll
+    for (int it = 0; it < 8; ++it) {
+#pragma unroll
+      for (int o = 1; o < 8; o <<= 1) {
+        sum[it] += __shfl_xor_sync(0xffffffffu, sum[it], o);
+        sq[it] += __shfl_xor_sync(0xffffffffu, sq[it], o);
+      }
+      if (sub == 0) my_stats[it * 4 + rsel] = make_float2(sum[it], sq[it]);
+    }
+    named_bar_sync(1 + q, 64);                     // the two warps of this row quarter
+    float mean[8], rstd[8];
+#pragma unroll
+    for (int it = 0; it < 8; ++it) {
+      const float2 o = peer_stats[it * 4 + rsel];
+      const float s = sum[it] + o.x, ss = sq[it] + o.y;
+      mean[it] = s * (1.0f / BLOCK_N);
+      const float var = fmaxf(ss * (1.0f / BLOCK_N) - mean[it] * mean[it], 0.f);
+      rstd[it] = rsqrtf(var + p.ln_eps);
+    }
+    // ---------------------------------------------------------------- phase B
+    act_t* yact = static_cast<act_t*>(p.ln_y_act);
+    act_t* ypos = static_cast<act_t*>(p.ln_ypos_act);
+#pragma unroll
+    for (int j = 0; j < kChunks; ++j) {
+      const float4 g4 = __ldg(reinterpret_cast<const float4*>(p.ln_gamma + col0 + j * 64));
+      const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.ln_beta + col0 + j * 64));
+#pragma unroll
+      for (int it = 0; it < 8; ++it) {
+        if (!RMB_LN_OK(it)) continue;
+        float4* op = reinterpret_cast<float4*>(RMB_LN_O(it) + j * 64);
+        const float4 x = *op;                      // parked by this lane in phase A
+        float4 y;
+        y.x = (x.x - mean[it]) * rstd[it] * g4.x + b4.x; y.y = (x.y - mean[it]) * rstd[it] * g4.y + b4.y;
+        y.z = (x.z - mean[it]) * rstd[it] * g4.z + b4.z; y.w = (x.w - mean[it]) * rstd[it] * g4.w + b4.w;
+        *op = y;
+        const long long grow = row_q + it * 4 + rsel;
+        const long long eoff = grow * BLOCK_N + col0 + j * 64;
+        if (yact != nullptr)
+          *reinterpret_cast<uint2*>(yact + eoff) = make_uint2(pack_act2(y.x, y.y), pack_act2(y.z, y.w));
+        if (ypos != nullptr) {
+          const float4 pv = __ldg(reinterpret_cast<const float4*>(p.ln_pos + (grow % p.ln_L) * BLOCK_N + col0 + j * 64));
+          *reinterpret_cast<uint2*>(ypos + eoff) = make_uint2(pack_act2(y.x + pv.x, y.y + pv.y), pack_act2(y.z + pv.z, y.w + pv.w));
+        }
+      }
+    }
+    named_bar_sync(1 + q, 64);                     // peer has read my_stats before the next tile's pass 1 overwrites it
+    acc_phase ^= 1;
+  }
+#undef RMB_LN_OK
+#undef RMB_LN_R
+#undef RMB_LN_O
+}
+
+}  // namespace rmb

@@ -10,6 +10,7 @@
 #include "conv_halo.cuh"
 #include "stem_pool.cuh"
 #include "gemm_tc.cuh"
+#include "gemm_ln.cuh"
 #include "launch.h"
 #include "tma_host.h"
 
@@ -21,6 +22,7 @@ struct GemmPlan {
   int block_n = 0, block_k = 0;
   bool tma_out = false;  // epilogue stores through tout (plain matrices, 16-bit output, no residual, no row remap)
   bool pair = false;     // launch gemm_tc_pair_kernel (tb's box then holds block_n / 2 weight rows)
+  bool ln = false;       // 512-wide tiles with the fused residual + LayerNorm epilogue (gemm_ln.cuh); always a pair launch
   long long flops = 0;   // 2*rows*N*K of useful work (for reporting)
 };
 
@@ -73,6 +75,8 @@ inline void fill_common(GemmParams& p, const float* bias, const void* residual, 
   p.remap_ncam = 0; p.remap_L = 0; p.remap_off = 0;
   p.n_valid = 1 << 30;
   p.film = nullptr; p.film_ld = 0; p.film_g_off = 0; p.film_b_off = 0; p.film_div = 1;
+  p.ln_gamma = nullptr; p.ln_beta = nullptr; p.ln_pos = nullptr; p.ln_L = 1; p.ln_y_act = nullptr; p.ln_ypos_act = nullptr;
+  p.ln_eps = 1e-5f;
 }
 
 // out[M, N] = A[M, K] (row-major, leading dim lda) * Wt[N, K]^T
@@ -115,6 +119,38 @@ inline bool plan_linear(GemmPlan* g, const void* A, long long M, int K, int lda,
     g->tma_out = true;
   }
   g->flops = 2ll * M * N * K;
+  return true;
+}
+
+// y = LayerNorm(A[M, K] * Wt[512, K]^T + bias + residual) with the outputs of layernorm512_kernel, in one launch
+// (gemm_ln.cuh). residual / out are fp32 [M, 512]; y_act / ypos_act (optional) 16-bit [M, 512].
+inline bool plan_linear_ln(GemmPlan* g, const void* A, long long M, int K, int lda, const void* Wt, const float* bias,
+                           const float* residual, float* out, const float* gamma, const float* beta, const float* pos,
+                           int L, void* y_act, void* ypos_act, float eps, std::string* err) {
+  *g = GemmPlan();
+  g->block_k = 64; g->block_n = 512; g->pair = true; g->ln = true;
+  if (K % 64 != 0 || M < 1) { if (err) *err = "plan_linear_ln: K must be a multiple of 64"; return false; }
+  if (!residual || !out || !gamma || !beta || (ypos_act && (!pos || L < 1))) { if (err) *err = "plan_linear_ln: null argument"; return false; }
+  GemmParams& p = g->p;
+  p.box_w = 128; p.box_h = 1; p.box_b = 1;
+  p.W = static_cast<int>(M); p.H = 1; p.B = 1;
+  p.tiles_w = static_cast<int>((M + 127) / 128); p.tiles_h = 1; p.tiles_b = 1;
+  p.n_col_tiles = 1;
+  p.num_taps = 1; p.chunks_per_tap = K / 64;
+  for (int t = 0; t < kMaxTaps; ++t) { p.tap_c0[t] = p.tap_d1[t] = p.tap_d2[t] = p.tap_d3[t] = 0; }
+  fill_common(p, bias, residual, 512, true, out, 512, true, false);
+  p.ln_gamma = gamma; p.ln_beta = beta; p.ln_pos = pos; p.ln_L = L < 1 ? 1 : L;
+  p.ln_y_act = y_act; p.ln_ypos_act = ypos_act; p.ln_eps = eps;
+  const uint64_t dims[5] = {static_cast<uint64_t>(K), static_cast<uint64_t>(M), 1, 1, 1};
+  const uint64_t row = static_cast<uint64_t>(lda) * 2;
+  const uint64_t strides[4] = {row, row * M, row * M, row * M};
+  const uint32_t box[5] = {64, 128, 1, 1, 1};
+  if (!make_tmap_act(&g->ta, A, 5, dims, strides, box, 128, err)) return false;
+  const uint64_t wdims[2] = {static_cast<uint64_t>(K), 512};
+  const uint64_t wstr[1] = {static_cast<uint64_t>(K) * 2};
+  const uint32_t wbox[2] = {64, 128};       // a CTA holds two 128-row boxes per k-block (one per N = 256 half)
+  if (!make_tmap_act(&g->tb, Wt, 2, wdims, wstr, wbox, 128, err)) return false;
+  g->flops = 2ll * M * 512 * K;
   return true;
 }
 
@@ -279,7 +315,24 @@ inline cudaError_t launch_gemm_variant(const GemmPlan& g, int num_sms, cudaStrea
   return cudaErrorInvalidValue;   // act out + fp32 residual: not needed on this path
 }
 
+// the LayerNorm-fused mode exists as a pair kernel only (launch_gemm_instance would also name the single-CTA kernel)
+inline cudaError_t launch_gemm_ln(const GemmPlan& g, int num_sms, cudaStream_t stream) {
+  using S = GemmSmem<512, 64, 4, true, 5>;
+  static_assert(S::kTotal <= 232448, "shared memory");
+  auto kern = gemm_tc_pair_kernel<512, 64, 4, true, 2, 5>;
+  static bool attr_set = false;
+  static int max_pairs = 0;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal);
+    if (e != cudaSuccess) return e;
+    max_pairs = max_active_pairs(kern, S::kTotal, num_sms);
+    attr_set = true;
+  }
+  return launch_pdl(kern, dim3(gemm_grid(g, num_sms, max_pairs)), dim3(kGemmThreads), S::kTotal, stream, g.ta, g.tb, g.ta, g.p);
+}
+
 inline cudaError_t launch_gemm(const GemmPlan& g, int num_sms, cudaStream_t stream) {
+  if (g.ln) return launch_gemm_ln(g, num_sms, stream);
   if (g.pair) {
     if (g.block_k == 64 && g.block_n == 64) return launch_gemm_variant<64, 64, 8, true>(g, num_sms, stream);
     if (g.block_k == 64 && g.block_n == 128) return launch_gemm_variant<128, 64, 8, true>(g, num_sms, stream);

@@ -52,6 +52,15 @@ struct GemmParams {
   // gamma = film[ep * film_ld + film_g_off + c], beta = film[ep * film_ld + film_b_off + c], ep = image / film_div
   const float* film;
   int film_ld, film_g_off, film_b_off, film_div;
+  // fused residual + LayerNorm(512) epilogue (EPI == 5, gemm_ln.cuh): v = acc + bias + residual (fp32); y = LN(v);
+  // `out` gets y in fp32 (the residual stream), ln_y_act y in 16 bits, ln_ypos_act (y + ln_pos[row % ln_L]) in 16 bits
+  const float* ln_gamma;
+  const float* ln_beta;
+  const float* ln_pos;       // [ln_L, 512] or nullptr
+  int ln_L;
+  void* ln_y_act;            // act_t [rows, 512] or nullptr
+  void* ln_ypos_act;         // act_t [rows, 512] or nullptr (needs ln_pos)
+  float ln_eps;
 };
 
 // PAIR: two CTAs of a cluster work on one 256-row tile (tcgen05 cta_group::2); each holds its 128 rows of A and half
@@ -310,22 +319,34 @@ template <int BLOCK_N, bool FILM, bool PAIR>
 __device__ __forceinline__ void gemm_gn_epilogue(const GemmParams& p, uint8_t* smem_stage, uint32_t tmem_base,
                                                  uint64_t* tmem_full_bar, uint64_t* tmem_empty_bar,
                                                  const TileSched<PAIR>& ts, int warp, int lane);
+template <bool PAIR>
+__device__ __forceinline__ void gemm_ln_epilogue(const GemmParams& p, uint8_t* smem_stage, uint32_t tmem_base,
+                                                 uint64_t* tmem_full_bar, uint64_t* tmem_empty_bar,
+                                                 const TileSched<PAIR>& ts, int warp, int lane);
 
 // OUT_F32: fp32 output (else act_t). RES: 0 no residual, 1 act_t residual, 2 fp32 residual.
 // EPI: 0 plain epilogue (bias / residual / ReLU); fused GroupNorm + Mish (gemm_gn.cuh) followed by 1: FiLM, 2: residual;
-// 3: plain 16-bit output through a TMA store (tmap_out; the other modes ignore it); 4: plain + per-episode FiLM (MT-ACT).
+// 3: plain 16-bit output through a TMA store (tmap_out; the other modes ignore it); 4: plain + per-episode FiLM (MT-ACT);
+// 5: BLOCK_N = 512 = the whole row, fp32 residual + LayerNorm fused (gemm_ln.cuh). A 128 x 512 fp32 tile is all of TMEM,
+//    so this mode has ONE accumulator and issues every k-step as two N = 256 MMAs; PAIR only (each CTA then holds two
+//    128-row boxes of the weight tile, rows 128 r.. and 256 + 128 r..).
 // PAIR: launched as clusters of two CTAs (gemm_tc_pair_kernel); see GemmSmem / TileSched.
 template <int BLOCK_N, int BLOCK_K, int STAGES, bool OUT_F32, int RES, int EPI, bool PAIR>
 __device__ __forceinline__ void gemm_tc_body(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, const CUtensorMap& tmap_out,
                                              const GemmParams& p) {
   static_assert(BLOCK_K == 64 || BLOCK_K == 32, "BLOCK_K selects the 128B / 64B swizzle");
-  static_assert(BLOCK_N == 64 || BLOCK_N == 128 || BLOCK_N == 256, "BLOCK_N");
+  static_assert(BLOCK_N == 64 || BLOCK_N == 128 || BLOCK_N == 256 || BLOCK_N == 512, "BLOCK_N");
+  constexpr bool kWide = (BLOCK_N == 512);
+  static_assert(!kWide || (PAIR && EPI == 5), "512-wide tiles: CTA pairs with the LayerNorm epilogue only");
+  static_assert(kWide || EPI != 5, "the LayerNorm epilogue needs the whole 512-wide row in the tile");
+  constexpr int kMmaN = kWide ? 256 : BLOCK_N;                      // N of one tcgen05.mma
+  constexpr int kAccs = kWide ? 1 : 2;                              // accumulators in TMEM
   pdl_trigger();
   using S = GemmSmem<BLOCK_N, BLOCK_K, STAGES, PAIR, EPI>;
   constexpr uint32_t kSwizzleLayout = (BLOCK_K == 64) ? 2u : 4u;   // SWIZZLE_128B : SWIZZLE_64B
   constexpr uint32_t kSBO = 8u * BLOCK_K * 2u;                      // 8-row core-matrix group stride
-  constexpr uint32_t kTmemCols = 2 * BLOCK_N;                       // double-buffered accumulator
-  constexpr uint32_t kIdesc = make_idesc_f16(PAIR ? 256 : 128, BLOCK_N, false, false);
+  constexpr uint32_t kTmemCols = kAccs * BLOCK_N;                   // double-buffered accumulator (one when 512 wide)
+  constexpr uint32_t kIdesc = make_idesc_f16(PAIR ? 256 : 128, kMmaN, false, false);
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -401,7 +422,12 @@ __device__ __forceinline__ void gemm_tc_body(const CUtensorMap& tmap_a, const CU
             if (PAIR) {
               if (rank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * cta_tx_bytes);   // the peer's boxes land here too
               tma_load_5d_pair(a_base + stage * S::kABytes, &tmap_a, fb, c0 + ch * BLOCK_K, d1, d2, d3, b0);
-              tma_load_2d_pair(b_base + stage * S::kBBytes, &tmap_b, fb, kcol, n0);
+              if (kWide) {   // this CTA's share of both N = 256 halves: weight rows 128 r.. and 256 + 128 r..
+                tma_load_2d_pair(b_base + stage * S::kBBytes, &tmap_b, fb, kcol, ct * BLOCK_N + rank * 128);
+                tma_load_2d_pair(b_base + stage * S::kBBytes + S::kBBytes / 2, &tmap_b, fb, kcol, ct * BLOCK_N + 256 + rank * 128);
+              } else {
+                tma_load_2d_pair(b_base + stage * S::kBBytes, &tmap_b, fb, kcol, n0);
+              }
             } else {
               mbar_arrive_expect_tx_u32(fb, cta_tx_bytes);
               tma_load_5d_u32(a_base + stage * S::kABytes, &tmap_a, fb, c0 + ch * BLOCK_K, d1, d2, d3, b0);
@@ -435,8 +461,14 @@ __device__ __forceinline__ void gemm_tc_body(const CUtensorMap& tmap_a, const CU
             const uint64_t db = b_desc0 + static_cast<uint64_t>(stage * (S::kBBytes >> 4));
 #pragma unroll
             for (int k = 0; k < BLOCK_K / 16; ++k) {
-              if (PAIR) umma_f16_ss_pair(d_tmem, da + 2 * k, db + 2 * k, kIdesc, (kb | k) != 0 ? 1u : 0u);
-              else umma_f16_ss(d_tmem, da + 2 * k, db + 2 * k, kIdesc, (kb | k) != 0 ? 1u : 0u);
+              if (kWide) {
+                umma_f16_ss_pair(d_tmem, da + 2 * k, db + 2 * k, kIdesc, (kb | k) != 0 ? 1u : 0u);
+                umma_f16_ss_pair(d_tmem + 256, da + 2 * k, db + 2 * k + (S::kBBytes >> 5), kIdesc, (kb | k) != 0 ? 1u : 0u);
+              } else if (PAIR) {
+                umma_f16_ss_pair(d_tmem, da + 2 * k, db + 2 * k, kIdesc, (kb | k) != 0 ? 1u : 0u);
+              } else {
+                umma_f16_ss(d_tmem, da + 2 * k, db + 2 * k, kIdesc, (kb | k) != 0 ? 1u : 0u);
+              }
             }
             // frees this smem stage (in both CTAs) when the MMAs above retire
             if (PAIR) umma_commit_pair_u32(empty_base + stage * 8, 3u);
@@ -450,11 +482,13 @@ __device__ __forceinline__ void gemm_tc_body(const CUtensorMap& tmap_a, const CU
           else umma_commit(&tmem_full_bar[acc]);
         }
         __syncwarp();
-        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        if (++acc == kAccs) { acc = 0; acc_phase ^= 1; }
       }
     }
   } else {
-    if constexpr (EPI == 3)
+    if constexpr (EPI == 5)
+      gemm_ln_epilogue<PAIR>(p, smem_stage, tmem_base, tmem_full_bar, tmem_empty_bar, ts, warp, lane);
+    else if constexpr (EPI == 3)
       gemm_epilogue_tma<BLOCK_N, PAIR>(&tmap_out, p, smem_stage, tmem_base, tmem_full_bar, tmem_empty_bar, ts, warp, lane);
     else if constexpr (EPI == 4)
       gemm_epilogue<BLOCK_N, OUT_F32, RES, PAIR, true>(p, smem_stage, tmem_base, tmem_full_bar, tmem_empty_bar, ts, warp, lane);

@@ -57,6 +57,38 @@ def test_gemm(lib, cuda, M, N, K, flags):
     assert err <= 2e-2 * max(scale, 1.0)
 
 
+@pytest.mark.parametrize("M,K,with_pos", [(602 * 40, 512, False), (602 * 33 + 77, 3200, True), (300, 512, True), (128, 64, False)])
+def test_gemm_residual_layernorm(lib, cuda, M, K, with_pos):
+    """The fused out-projection / FFN-down + residual + LayerNorm launch vs fp32 torch on the same 16-bit operands:
+    fp32 residual stream within 1e-4 (the accuracy of the stand-alone LayerNorm kernel), 16-bit copies within one
+    rounding step; ragged last row tile, odd number of row tiles (one CTA of the last pair idle), tiny M."""
+    g = torch.Generator(device="cpu").manual_seed(M + K)
+    L = 602
+    A = _bf16(torch.randn(M, K, generator=g)).to(cuda)
+    W = _bf16(torch.randn(512, K, generator=g) / K ** 0.5).to(cuda)
+    bias = torch.randn(512, generator=g).to(cuda)
+    res = torch.randn(M, 512, generator=g).to(cuda)
+    gamma = (1 + 0.1 * torch.randn(512, generator=g)).to(cuda)
+    beta = (0.1 * torch.randn(512, generator=g)).to(cuda)
+    pos = torch.randn(L, 512, generator=g).to(cuda)
+    out = torch.full((M, 512), -77.0, device=cuda)
+    y_act = torch.full((M, 512), -7.0, device=cuda, dtype=_act_dtype())
+    ypos = torch.full((M, 512), -7.0, device=cuda, dtype=_act_dtype()) if with_pos else None
+    check(lib.rmb_gemm_residual_layernorm(ptr(A), ptr(W), ptr(bias), ptr(res), ptr(gamma), ptr(beta), ptr(pos) if with_pos else None,
+                                          L, ptr(out), ptr(y_act), ptr(ypos), M, K, cur_stream()), "gemm_ln")
+    torch.cuda.synchronize()
+    v = A.double() @ W.double().t() + bias.double() + res.double()
+    ref = F.layer_norm(v, (512,), gamma.double(), beta.double(), 1e-5)
+    err = (out.double() - ref).abs().max().item()
+    print(f"[gemm+res+LN {M}x512x{K}] fp32 stream max-abs err {err:.3e}")
+    assert err <= 1e-4
+    step = 2.0 ** -8 if _act_dtype() == torch.bfloat16 else 2.0 ** -11
+    assert (y_act.double() - ref).abs().max().item() <= step * ref.abs().max().item() + 1e-4
+    if with_pos:
+        refp = ref + pos.double()[torch.arange(M, device=cuda) % L]
+        assert (ypos.double() - refp).abs().max().item() <= step * refp.abs().max().item() + 1e-4
+
+
 def _conv_ref(x_nhwc, w_oihw, bias, res_nhwc, stride, relu):
     y = F.conv2d(x_nhwc.float().permute(0, 3, 1, 2), w_oihw.float(), bias, stride=stride, padding=w_oihw.shape[-1] // 2)
     y = y.permute(0, 2, 3, 1)
