@@ -48,3 +48,73 @@ def gather_results(success, reward, duration, total_episodes, group=None):
     packed = torch.stack([success.to(torch.float32), reward.to(torch.float32), duration.to(torch.float32)], dim=1)
     allp = gather_episodes(packed, total_episodes, group)
     return allp[:, 0].to(torch.uint8), allp[:, 1], allp[:, 2]
+
+
+class AsyncEpisodeGather:
+    """The per-step action all-gather OFF the compute stream ("issue it on a side stream").
+
+    submit(local) snapshots the rank-local (B_local, ...) tensor into a staging slot on the compute stream and enqueues
+    the all-gather on a side stream behind an event; the compute stream goes on with the next policy step. Ranks may
+    therefore drift apart by up to `depth` steps instead of meeting at a collective every step (every step otherwise
+    costs the slowest rank's time). result() returns the gathered (total, ...) tensor of the OLDEST outstanding submit
+    and makes the current stream wait for just that gather. On CPU tensors (gloo tests) it degrades to the synchronous
+    gather_episodes with the same submit / result order."""
+
+    def __init__(self, total_episodes, local_shape, dtype, device, depth=2, group=None):
+        self.total, self.group, self.depth = int(total_episodes), group, int(depth)
+        self.device = torch.device(device)
+        self.cuda = self.device.type == "cuda"
+        self.active = dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1
+        if self.active and self.total % dist.get_world_size(group) != 0:
+            raise ValueError("AsyncEpisodeGather needs equal episode blocks (use gather_episodes for ragged ones)")
+        self.stage = [torch.empty(tuple(local_shape), dtype=dtype, device=self.device) for _ in range(self.depth)]
+        self.out = [torch.empty((self.total,) + tuple(local_shape[1:]), dtype=dtype, device=self.device)
+                    for _ in range(self.depth)] if self.active else None
+        self.side = torch.cuda.Stream(device=self.device) if (self.cuda and self.active) else None
+        self.ready = [None] * self.depth          # event: staging slot filled (compute stream)
+        self.done = [None] * self.depth           # event: gather finished (side stream)
+        self.n_submit = 0
+        self.n_result = 0
+
+    def submit(self, local):
+        if self.n_submit - self.n_result >= self.depth:
+            raise RuntimeError("AsyncEpisodeGather: more than `depth` gathers outstanding; call result() first")
+        slot = self.n_submit % self.depth
+        self.n_submit += 1
+        if not self.active:
+            self.stage[slot].copy_(local)
+            return
+        if not self.cuda:
+            self.stage[slot].copy_(local)
+            dist.all_gather_into_tensor(self.out[slot], self.stage[slot], group=self.group)
+            return
+        cur = torch.cuda.current_stream(self.device)
+        if self.done[slot] is not None:
+            cur.wait_event(self.done[slot])       # the gather that last read this staging slot
+        self.stage[slot].copy_(local)
+        ev = torch.cuda.Event()
+        ev.record(cur)
+        self.ready[slot] = ev
+        with torch.cuda.stream(self.side):
+            self.side.wait_event(ev)
+            dist.all_gather_into_tensor(self.out[slot], self.stage[slot], group=self.group)
+            dn = torch.cuda.Event()
+            dn.record(self.side)
+            self.done[slot] = dn
+
+    def result(self):
+        if self.n_result >= self.n_submit:
+            raise RuntimeError("AsyncEpisodeGather: nothing outstanding")
+        slot = self.n_result % self.depth
+        self.n_result += 1
+        if not self.active:
+            return self.stage[slot]
+        if self.cuda:
+            torch.cuda.current_stream(self.device).wait_event(self.done[slot])
+        return self.out[slot]
+
+    def drain(self):
+        last = None
+        while self.n_result < self.n_submit:
+            last = self.result()
+        return last

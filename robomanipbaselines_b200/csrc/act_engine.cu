@@ -19,6 +19,7 @@
 
 #include "../../include/rmb_b200.h"
 #include "attention_tc.cuh"
+#include "attention_v2.cuh"
 #include "elementwise.cuh"
 #include "gemm_plan.h"
 
@@ -68,7 +69,26 @@ bool plan_attention(AttnPlan* a, const void* Q, int ldq, int q_col0, bool q_shar
   return true;
 }
 
+// attention_v2_kernel (persistent, two streams per CTA, one sweep) unless RMB_ATTN_V1=1 asks for the first version
+cudaError_t launch_attention_v1(const AttnPlan& a, cudaStream_t stream);
 cudaError_t launch_attention(const AttnPlan& a, cudaStream_t stream) {
+  static const bool v1 = [] { const char* e = getenv("RMB_ATTN_V1"); return e != nullptr && e[0] == '1'; }();
+  if (v1) return launch_attention_v1(a, stream);
+  static bool attr_set = false;
+  static int sms = 148;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(attention_v2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttn2SmemBytes);
+    if (e != cudaSuccess) return e;
+    int dev = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    attr_set = true;
+  }
+  const int n_items = a.grid;                       // (episode, head, query tile) work items
+  const int grid = std::min(sms, (n_items + 1) / 2);
+  return launch_pdl(attention_v2_kernel, dim3(grid), dim3(kAttn2Threads), kAttn2SmemBytes, stream, a.tq, a.tk, a.tv, a.p, n_items);
+}
+
+cudaError_t launch_attention_v1(const AttnPlan& a, cudaStream_t stream) {
   static bool attr_set = false;
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttnSmemBytes);
@@ -873,7 +893,7 @@ static int forward_impl(rmb_act_engine_t* e, const void* d_images, int image_for
     }
     snprintf(nm, sizeof(nm), "enc%d V proj", l); RMB_RUN(run_gemm(nm, pl.v, tokb));
     snprintf(nm, sizeof(nm), "enc%d self-attention", l);
-    begin(nm, "attention_tc_kernel", attn_flops, attn_bytes);
+    begin(nm, "attention_v2_kernel", attn_flops, attn_bytes);
     RMB_CUDA(launch_attention(pl.attn, s));
     end();
     if (bp->ln_fused) {
@@ -896,7 +916,7 @@ static int forward_impl(rmb_act_engine_t* e, const void* d_images, int image_for
   }
   RMB_RUN(run_gemm("dec0 K proj", bp->dk, tokb));
   RMB_RUN(run_gemm("dec0 V proj", bp->dv, tokb));
-  begin("dec0 cross-attention", "attention_tc_kernel", 4.0 * batch * (double)C * L * 512, (double)BL * 512 * 2 * 2 + (double)BC * 512 * 2);
+  begin("dec0 cross-attention", "attention_v2_kernel", 4.0 * batch * (double)C * L * 512, (double)BL * 512 * 2 * 2 + (double)BC * 512 * 2);
   RMB_CUDA(launch_attention(bp->dattn, s));
   end();
   RMB_RUN(run_gemm("dec0 out proj +tgt", bp->dout, (double)BC * 512 * 2));

@@ -7,7 +7,8 @@ import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp
 
-from robomanipbaselines_b200.common.sharding import episode_block, episode_seed, gather_episodes, gather_results
+from robomanipbaselines_b200.common.sharding import (AsyncEpisodeGather, episode_block, episode_seed, gather_episodes,
+                                                     gather_results)
 
 
 def test_episode_blocks_partition():
@@ -37,6 +38,19 @@ def _worker(rank, world, port, total, q):
           and torch.equal(full[:, 6], torch.arange(total, dtype=torch.float64) * 10 + 6)
           and torch.equal(s, (torch.arange(total) % 2 == 0).to(torch.uint8))
           and torch.equal(r, torch.arange(total).float() * 0.5) and torch.equal(t, torch.arange(total).float() + 1))
+    if total % world == 0:      # the pipelined gather: two submits outstanding, results come back in submit order
+        ag = AsyncEpisodeGather(total, local.shape, local.dtype, "cpu", depth=2)
+        ag.submit(local)
+        ag.submit(local + 1000)
+        r0 = ag.result().clone()
+        ag.submit(local + 2000)
+        r1, r2 = ag.result().clone(), ag.drain().clone()
+        ok = ok and torch.equal(r0, full) and torch.equal(r1, full + 1000) and torch.equal(r2, full + 2000)
+        try:
+            ag.result()
+            ok = False
+        except RuntimeError:
+            pass
     q.put((rank, bool(ok)))
     dist.barrier()
     dist.destroy_process_group()
