@@ -159,7 +159,10 @@ struct rmb_act_engine {
   act_t *kd = nullptr, *vd = nullptr, *aod = nullptr, *t_b = nullptr, *hd = nullptr;
   float *yd = nullptr, *t_f32 = nullptr, *yd2 = nullptr;
 
-  bool fuse_ln = true;          // RMB_NO_LN_FUSE=1: residual GEMMs and LayerNorm as separate launches
+  // RMB_LN_FUSE = auto (default): the encoder's residual GEMMs carry their LayerNorm when there is a 256-row pair tile
+  // for every SM pair, else GEMM + layernorm512_kernel (narrow tiles spread a small batch over more SMs); always /
+  // never force one path (tests: each path is bit-invariant to the batch size; the two agree to fp32 round-off)
+  int fuse_ln = 1;              // 0 never, 1 auto, 2 always
   bool fuse_stem_pool = true;   // RMB_NO_STEM_POOL=1: stem and max-pool as two kernels through a [img, H/2, W/2, 64] buffer
   struct BatchPlans {
     HaloPlan stem;
@@ -298,7 +301,7 @@ int rmb_act_engine_create(const rmb_act_config_t* cfg, rmb_act_engine_t** out) {
   cudaGetDeviceProperties(&prop, cfg->device);
   e->num_sms = prop.multiProcessorCount;
   { const char* ev = getenv("RMB_NO_STEM_POOL"); e->fuse_stem_pool = !(ev != nullptr && ev[0] == '1'); }
-  { const char* ev = getenv("RMB_NO_LN_FUSE"); e->fuse_ln = !(ev != nullptr && ev[0] == '1'); }
+  { const char* ev = getenv("RMB_LN_FUSE"); e->fuse_ln = (ev == nullptr) ? 1 : (ev[0] == 'n' ? 0 : (ev[0] == 'a' && ev[1] == 'l') ? 2 : 1); }
   e->Hf = cfg->img_h / 32; e->Wf = cfg->img_w / 32;
   e->n_prefix = 2 + (cfg->task_token ? 1 : 0);
   e->L = e->n_prefix + e->Hf * e->Wf * cfg->num_cams;
@@ -593,7 +596,7 @@ static int build_plans(rmb_act_engine* e, int nb, rmb_act_engine::BatchPlans** o
 
   const long long BL = (long long)nb * L, BC = (long long)nb * C;
   bp->enc.resize(c.enc_layers);
-  bp->ln_fused = e->fuse_ln && (BL + 255) / 256 >= e->num_sms / 2;
+  bp->ln_fused = e->fuse_ln == 2 || (e->fuse_ln == 1 && (BL + 255) / 256 >= e->num_sms / 2);
   for (int l = 0; l < c.enc_layers; ++l) {
     auto& w = e->enc[l];
     auto& pl = bp->enc[l];

@@ -43,8 +43,11 @@ class ACTPolicy(_ActPolicy):
     def set_task_embedding(self, task_emb, batch, img_h, img_w, device):
         """(B or 1, 384) float32 -> engine-resident token + FiLM parameters (skipped when unchanged)."""
         eng = self.engine_for(batch, img_h, img_w, device)
-        key = (task_emb.data_ptr(), task_emb._version, tuple(task_emb.shape), batch, id(eng))
-        if key != self._task_key:
+        # "unchanged" = the very same tensor object at the same version (a reference is kept, so its storage cannot be
+        # recycled for another embedding behind our back), for the same batch on the same engine
+        key = (task_emb, task_emb._version, batch, eng)
+        old = self._task_key
+        if old is None or old[0] is not key[0] or old[1:3] != key[1:3] or old[3] is not eng:
             te = task_emb.to(device=device, dtype=torch.float32)
             if te.dim() != 2 or te.shape[1] != TASK_EMB_DIM or te.shape[0] not in (1, batch):
                 raise ValueError(f"task_emb must be (B or 1, {TASK_EMB_DIM}), got {tuple(task_emb.shape)}")

@@ -220,6 +220,32 @@ def test_attention(lib, cuda, B, Lq, Lk, shared):
     assert err <= 2e-2 * max(scale, 1.0)
 
 
+@pytest.mark.parametrize("B,Lq,Lk", [(2, 602, 602), (40, 602, 602), (3, 100, 602), (2, 130, 257), (300, 20, 602)])
+def test_attention_online_softmax_reference_point_moves(lib, cuda, B, Lq, Lk):
+    """One-sweep attention keeps a reference maximum per row and only moves it (rescaling O and the row sum in TMEM)
+    when a key block exceeds it by more than 2^8. Here the logits GROW along the keys (later blocks are up to 6x larger),
+    so every block forces the move; plus a flat case mix: more work items than streams (40 x 8 x 5 = 1600 items on 296
+    streams), a single query tile with dead warps (Lq = 20, 100), ragged key blocks (Lk = 257: one valid key in the last
+    block). P is 16-bit, so errors are relative to the softmax's own scale."""
+    g = torch.Generator(device="cpu").manual_seed(B + Lq + Lk)
+    H, D = 8, 512
+    Q = _bf16(torch.randn(B * Lq, D, generator=g) * 1.5).to(cuda)
+    grow = (1.0 + 5.0 * torch.arange(Lk).float() / Lk).repeat(B).unsqueeze(1)
+    K = _bf16(torch.randn(B * Lk, D, generator=g) * grow).to(cuda)
+    V = _bf16(torch.randn(B * Lk, D, generator=g)).to(cuda)
+    out = torch.full((B * Lq, D), 7.0, device=cuda, dtype=_act_dtype())
+    check(lib.rmb_attention(ptr(Q), D, 0, 0, ptr(K), D, 0, ptr(V), D, 0, ptr(out), D, B, H, Lq, Lk, cur_stream()), "attention")
+    torch.cuda.synchronize()
+    q = Q.float().view(B, Lq, H, 64)
+    k = K.float().view(B, Lk, H, 64)
+    v = V.float().view(B, Lk, H, 64)
+    s = torch.einsum("bqhd,bkhd->bhqk", q, k) / 8.0
+    assert (s.amax(-1) - s[..., :128].amax(-1)).max().item() * 1.4427 > 8.0      # the move really is exercised
+    ref = torch.einsum("bhqk,bkhd->bqhd", s.softmax(-1), v).reshape(B * Lq, D)
+    err, scale = _report(f"attention (growing logits) B{B} Lq{Lq} Lk{Lk}", out, ref)
+    assert torch.isfinite(out.float()).all() and err <= 1e-2 * max(scale, 1.0)
+
+
 def test_layernorm(lib, cuda):
     rows, L = 1204, 602
     x = (torch.randn(rows, 512) * 3 + 1).to(cuda)
