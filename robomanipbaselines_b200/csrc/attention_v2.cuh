@@ -196,34 +196,68 @@ attention_v2_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
         const int nchunks = (nvalid + 31) >> 5;
         mbar_wait(s_bar, s_cnt & 1); ++s_cnt;
         tc_fence_after();
-        bool o_waited = false;
         if (warp_live) {
-          // ---- pass 1: block maximum of this row
+          // ONE pass over S(g), 32 keys at a time, the next chunk's tcgen05.ld in flight under this chunk's arithmetic.
+          // Each chunk is max-scanned first; P is formed against the current reference m. When the last chunk has been
+          // seen and the block maximum turns out to exceed m by more than 2^8 (rare: see the header), the block is
+          // redone against a new reference in the slow path below, before S(g) is released.
+          const float row_sum_prev = row_sum;
           float bm = -INFINITY;
-          for (int c = 0; c < nchunks; ++c) {
-            uint32_t v[32];
-            tmem_ld_32x32b_x32(tmem_S + lane_off + c * 32, v);
-            tmem_ld_wait();
-            if ((c + 1) * 32 > nvalid) {
+          bool redo = false;
+          uint32_t va[32], vb[32];
+          tmem_ld_32x32b_x32(tmem_S + lane_off, va);
 #pragma unroll
-              for (int i = 0; i < 32; ++i)
-                if (c * 32 + i >= nvalid) v[i] = 0xff800000u;
+          for (int c = 0; c < 4; ++c) {
+            uint32_t (&cur)[32] = (c & 1) ? vb : va;
+            uint32_t (&nxt)[32] = (c & 1) ? va : vb;
+            uint32_t pk[16];
+            if (c < nchunks) {
+              tmem_ld_wait();
+              if (c + 1 < nchunks) tmem_ld_32x32b_x32(tmem_S + lane_off + (c + 1) * 32, nxt);
+              if ((c + 1) * 32 > nvalid) {            // keys past Lk: -inf drops out of the maximum and gives P = 0
+#pragma unroll
+                for (int i = 0; i < 32; ++i)
+                  if (c * 32 + i >= nvalid) cur[i] = 0xff800000u;
+              }
+#pragma unroll
+              for (int i = 0; i < 32; i += 2) bm = max3(bm, __uint_as_float(cur[i]), __uint_as_float(cur[i + 1]));
+              if (g == 0 && c == 0) { m = bm; msc = m * p.scale_log2e; }   // first reference point: the first 32 keys
+              if (c + 1 == nchunks) {
+                redo = __any_sync(0xffffffffu, (bm - m) * p.scale_log2e > kAttn2RescaleLog2);
+                if (!redo) {                          // last read of S(g): the issuer may overwrite it
+                  tc_fence_before();
+                  __syncwarp();
+                  if (lane == 0) mbar_arrive(sc_bar);
+                }
+              }
+#pragma unroll
+              for (int i = 0; i < 32; i += 2) {
+                const float p0 = fast_exp2(fmaf(__uint_as_float(cur[i]), p.scale_log2e, -msc));
+                const float p1 = fast_exp2(fmaf(__uint_as_float(cur[i + 1]), p.scale_log2e, -msc));
+                row_sum += p0 + p1;
+                pk[i >> 1] = pack_act2(p0, p1);
+              }
+            } else {
+#pragma unroll
+              for (int i = 0; i < 16; ++i) pk[i] = 0u;
             }
-#pragma unroll
-            for (int i = 0; i < 32; i += 2) bm = max3(bm, __uint_as_float(v[i]), __uint_as_float(v[i + 1]));
-          }
-          if (g == 0) {
-            m = bm;
-            msc = m * p.scale_log2e;
-          } else {
-            const bool need = (bm - m) * p.scale_log2e > kAttn2RescaleLog2;
-            if (__any_sync(0xffffffffu, need)) {      // rare: move the reference point, rescale what has been accumulated
-              mbar_wait(o_bar, o_cnt & 1); ++o_cnt;   // P V (g - 1) complete
-              o_waited = true;
+            if (c == 0 && g > 0) {                    // P V (g - 1) has finished reading the P tile (and writing O)
+              mbar_wait(o_bar, o_cnt & 1); ++o_cnt;
               tc_fence_after();
-              const float alpha = need ? fast_exp2((m - bm) * p.scale_log2e) : 1.0f;
-              if (need) { m = bm; msc = m * p.scale_log2e; }
-              row_sum *= alpha;
+            }
+            const uint32_t pa = p_row + (c >> 1) * 16384;
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              st_shared_v4(pa + (((((c & 1) << 2) + j) ^ swz) << 4), pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+          }
+          if (redo) {
+            // ---- slow path (warp-uniform): move the reference point of the rows that need it, rescale what they have
+            // accumulated, and form this block's P again
+            const bool need = (bm - m) * p.scale_log2e > kAttn2RescaleLog2;
+            const float alpha = (need && g > 0) ? fast_exp2((m - bm) * p.scale_log2e) : 1.0f;
+            if (need) { m = bm; msc = m * p.scale_log2e; }
+            row_sum = row_sum_prev * alpha;
+            if (g > 0) {
 #pragma unroll
               for (int hcol = 0; hcol < 2; ++hcol) {
                 uint32_t o[32];
@@ -234,45 +268,28 @@ attention_v2_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
                 tmem_st_32x32b_x32(tmem_O + lane_off + hcol * 32, o);
               }
               tmem_st_wait();
-              tc_fence_before();
             }
-          }
-          // ---- pass 2: P = exp2(S * scale - m * scale), 16-bit, into the swizzled P tile (this row's 256 bytes)
-          for (int c = 0; c < 4; ++c) {
-            uint32_t pk[16];
-            if (c < nchunks) {
-              uint32_t v[32];
+            for (int c = 0; c < nchunks; ++c) {
+              uint32_t v[32], pk[16];
               tmem_ld_32x32b_x32(tmem_S + lane_off + c * 32, v);
               tmem_ld_wait();
-              if (c + 1 == nchunks) {                 // last read of S(g): the issuer may overwrite it
-                tc_fence_before();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(sc_bar);
-              }
-              const bool ragged = (c + 1) * 32 > nvalid;
 #pragma unroll
               for (int i = 0; i < 32; i += 2) {
                 float p0 = fast_exp2(fmaf(__uint_as_float(v[i]), p.scale_log2e, -msc));
                 float p1 = fast_exp2(fmaf(__uint_as_float(v[i + 1]), p.scale_log2e, -msc));
-                if (ragged) {
-                  if (c * 32 + i >= nvalid) p0 = 0.f;
-                  if (c * 32 + i + 1 >= nvalid) p1 = 0.f;
-                }
+                if (c * 32 + i >= nvalid) p0 = 0.f;
+                if (c * 32 + i + 1 >= nvalid) p1 = 0.f;
                 row_sum += p0 + p1;
                 pk[i >> 1] = pack_act2(p0, p1);
               }
-            } else {
+              const uint32_t pa = p_row + (c >> 1) * 16384;
 #pragma unroll
-              for (int i = 0; i < 16; ++i) pk[i] = 0u;
+              for (int j = 0; j < 4; ++j)
+                st_shared_v4(pa + (((((c & 1) << 2) + j) ^ swz) << 4), pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
             }
-            if (c == 0 && g > 0 && !o_waited) {       // P V (g - 1) has finished reading the P tile
-              mbar_wait(o_bar, o_cnt & 1); ++o_cnt;
-              tc_fence_after();
-            }
-            const uint32_t pa = p_row + (c >> 1) * 16384;
-#pragma unroll
-            for (int j = 0; j < 4; ++j)
-              st_shared_v4(pa + (((((c & 1) << 2) + j) ^ swz) << 4), pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(sc_bar);
           }
         } else {
           // all 32 query rows of this warp are past Lq: no arithmetic, only the protocol

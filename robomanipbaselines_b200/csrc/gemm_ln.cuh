@@ -117,28 +117,45 @@ __device__ __forceinline__ void gemm_ln_epilogue(const GemmParams& p, uint8_t* s
     // ---------------------------------------------------------------- phase B
     act_t* yact = static_cast<act_t*>(p.ln_y_act);
     act_t* ypos = static_cast<act_t*>(p.ln_ypos_act);
+    // The parked rows come back from L2: all eight loads of a chunk are issued before anything is stored (a store in
+    // between would order the loads behind it), and the next chunk's loads are in flight under this chunk's arithmetic.
+    float4 x[8], xn[8];
+#pragma unroll
+    for (int it = 0; it < 8; ++it)
+      x[it] = RMB_LN_OK(it) ? *reinterpret_cast<const float4*>(RMB_LN_O(it)) : make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
     for (int j = 0; j < kChunks; ++j) {
+      if (j + 1 < kChunks) {
+#pragma unroll
+        for (int it = 0; it < 8; ++it)
+          xn[it] = RMB_LN_OK(it) ? *reinterpret_cast<const float4*>(RMB_LN_O(it) + (j + 1) * 64) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
       const float4 g4 = __ldg(reinterpret_cast<const float4*>(p.ln_gamma + col0 + j * 64));
       const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.ln_beta + col0 + j * 64));
+      float4 pv[8];
+      if (ypos != nullptr) {
+#pragma unroll
+        for (int it = 0; it < 8; ++it) {
+          const long long grow = row_q + it * 4 + rsel;
+          pv[it] = RMB_LN_OK(it) ? __ldg(reinterpret_cast<const float4*>(p.ln_pos + (grow % p.ln_L) * BLOCK_N + col0 + j * 64))
+                                 : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+      }
 #pragma unroll
       for (int it = 0; it < 8; ++it) {
         if (!RMB_LN_OK(it)) continue;
-        float4* op = reinterpret_cast<float4*>(RMB_LN_O(it) + j * 64);
-        const float4 x = *op;                      // parked by this lane in phase A
         float4 y;
-        y.x = (x.x - mean[it]) * rstd[it] * g4.x + b4.x; y.y = (x.y - mean[it]) * rstd[it] * g4.y + b4.y;
-        y.z = (x.z - mean[it]) * rstd[it] * g4.z + b4.z; y.w = (x.w - mean[it]) * rstd[it] * g4.w + b4.w;
-        *op = y;
-        const long long grow = row_q + it * 4 + rsel;
-        const long long eoff = grow * BLOCK_N + col0 + j * 64;
+        y.x = (x[it].x - mean[it]) * rstd[it] * g4.x + b4.x; y.y = (x[it].y - mean[it]) * rstd[it] * g4.y + b4.y;
+        y.z = (x[it].z - mean[it]) * rstd[it] * g4.z + b4.z; y.w = (x[it].w - mean[it]) * rstd[it] * g4.w + b4.w;
+        *reinterpret_cast<float4*>(RMB_LN_O(it) + j * 64) = y;
+        const long long eoff = (row_q + it * 4 + rsel) * BLOCK_N + col0 + j * 64;
         if (yact != nullptr)
           *reinterpret_cast<uint2*>(yact + eoff) = make_uint2(pack_act2(y.x, y.y), pack_act2(y.z, y.w));
-        if (ypos != nullptr) {
-          const float4 pv = __ldg(reinterpret_cast<const float4*>(p.ln_pos + (grow % p.ln_L) * BLOCK_N + col0 + j * 64));
-          *reinterpret_cast<uint2*>(ypos + eoff) = make_uint2(pack_act2(y.x + pv.x, y.y + pv.y), pack_act2(y.z + pv.z, y.w + pv.w));
-        }
+        if (ypos != nullptr)
+          *reinterpret_cast<uint2*>(ypos + eoff) = make_uint2(pack_act2(y.x + pv[it].x, y.y + pv[it].y), pack_act2(y.z + pv[it].z, y.w + pv[it].w));
       }
+#pragma unroll
+      for (int it = 0; it < 8; ++it) x[it] = xn[it];
     }
     named_bar_sync(1 + q, 64);                     // peer has read my_stats before the next tile's pass 1 overwrites it
     acc_phase ^= 1;
