@@ -342,6 +342,43 @@ int rmb_action_fifo_step(double* d_fifo, int32_t* d_pos, const float* d_act_new,
                          const int32_t* d_sub_row, int norm_type, const double* d_p0, const double* d_p1, double out_min,
                          double* d_action, double* d_action_norm, int batch, int n_action_steps, int Da, void* stream);
 
+/* ---- Batched action consumer for arm bodies (the step right after infer_policy): ArmManager.set_command_data /
+ * get_command_data / inverse_kinematics (robo_manip_baselines/common/body/ArmManager.py:88-254), one damped least-squares
+ * IK step per end-effector command, fp64, one thread per episode. The kinematic model is a serial chain of revolute
+ * joints (what pin.buildModelFromUrdf yields for the reference's arm URDFs; Pinocchio is restated, not linked). */
+#define RMB_ARM_MAX_JOINTS 8
+#define RMB_ARM_MAX_GRIPPER 4
+typedef struct rmb_arm_model {
+  int32_t n_joints;                                  /* revolute joints of the chain (<= RMB_ARM_MAX_JOINTS) */
+  int32_t ik_joint_id;                               /* ArmConfig.ik_eef_joint_id: 1-based joint whose frame is the end effector */
+  double placement_R[RMB_ARM_MAX_JOINTS][9];         /* joint placement in its parent joint's frame, rotation row-major */
+  double placement_p[RMB_ARM_MAX_JOINTS][3];
+  double axis[RMB_ARM_MAX_JOINTS][3];                /* rotation axis in the joint's own frame (unit) */
+} rmb_arm_model_t;
+typedef struct rmb_arm_layout {
+  int32_t n_gripper;                                 /* gripper joints of this body (<= RMB_ARM_MAX_GRIPPER) */
+  int32_t eef_idx;                                   /* ArmConfig.eef_idx */
+  int32_t arm_idx[RMB_ARM_MAX_JOINTS];               /* ArmConfig.arm_joint_idxes: columns of a joint-position command */
+  int32_t gripper_idx[RMB_ARM_MAX_GRIPPER];          /* ArmConfig.gripper_joint_idxes */
+  int32_t gripper_idx_in_gripper[RMB_ARM_MAX_GRIPPER]; /* ArmConfig.gripper_joint_idxes_in_gripper_joint_pos */
+  double init_arm[RMB_ARM_MAX_JOINTS];               /* ArmConfig.init_arm_joint_pos */
+  double init_gripper[RMB_ARM_MAX_GRIPPER];
+  double gripper_low[RMB_ARM_MAX_GRIPPER];           /* env.action_space.low / high at gripper_joint_idxes_for_limit */
+  double gripper_high[RMB_ARM_MAX_GRIPPER];
+} rmb_arm_layout_t;
+/* key: 0 command_joint_pos, 1 command_joint_pos_rel, 2 command_gripper_joint_pos, 3 command_eef_pose (tx ty tz qw qx qy qz),
+ * 4 command_eef_pose_rel (tx ty tz roll pitch yaw), 5 reset. d_command float64 [batch, >= columns the key reads] with row
+ * stride cmd_stride (elements); d_mask uint8 [batch] or NULL (0 = leave the episode alone). State, all float64 on the
+ * device: d_arm_q [batch, n_joints], d_gripper_q [batch, max(n_gripper, 1)], d_target_se3 [batch, 12] (R row-major, p). */
+int rmb_arm_command(const rmb_arm_model_t* model, const rmb_arm_layout_t* layout, int key, const double* d_command,
+                    int cmd_stride, int is_skip, const uint8_t* d_mask, double* d_arm_q, double* d_gripper_q,
+                    double* d_target_se3, int batch, void* stream);
+/* get_command_data: d_joint_pos [batch, joint_pos_stride] (arm and gripper joints scattered to their command columns) and /
+ * or d_eef_pose [batch, 7] = pose of the target SE3; either may be NULL. */
+int rmb_arm_get_command(const rmb_arm_model_t* model, const rmb_arm_layout_t* layout, const double* d_arm_q,
+                        const double* d_gripper_q, const double* d_target_se3, double* d_joint_pos, int joint_pos_stride,
+                        double* d_eef_pose, int batch, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -86,6 +86,25 @@ class PointcloudParams(ctypes.Structure):
     ]
 
 
+ARM_MAX_JOINTS, ARM_MAX_GRIPPER = 8, 4
+
+
+class ArmModel(ctypes.Structure):
+    """Mirror of rmb_arm_model_t."""
+
+    _fields_ = [("n_joints", c_int32), ("ik_joint_id", c_int32), ("placement_R", (c_double * 9) * ARM_MAX_JOINTS),
+                ("placement_p", (c_double * 3) * ARM_MAX_JOINTS), ("axis", (c_double * 3) * ARM_MAX_JOINTS)]
+
+
+class ArmLayout(ctypes.Structure):
+    """Mirror of rmb_arm_layout_t."""
+
+    _fields_ = [("n_gripper", c_int32), ("eef_idx", c_int32), ("arm_idx", c_int32 * ARM_MAX_JOINTS),
+                ("gripper_idx", c_int32 * ARM_MAX_GRIPPER), ("gripper_idx_in_gripper", c_int32 * ARM_MAX_GRIPPER),
+                ("init_arm", c_double * ARM_MAX_JOINTS), ("init_gripper", c_double * ARM_MAX_GRIPPER),
+                ("gripper_low", c_double * ARM_MAX_GRIPPER), ("gripper_high", c_double * ARM_MAX_GRIPPER)]
+
+
 # name -> (restype, argtypes); must list every symbol include/rmb_b200.h declares (tests check this)
 SIGNATURES = {
     "rmb_last_error": (c_char_p, []),
@@ -157,6 +176,10 @@ SIGNATURES = {
     "rmb_pointcloud_scratch_bytes": (c_int64, [c_int, c_int, c_int, c_int]),
     "rmb_pointcloud_from_depth": (c_int, [c_void_p, c_void_p, POINTER(PointcloudParams), c_void_p, c_void_p, c_void_p,
                                           c_void_p, c_int, c_void_p]),
+    "rmb_arm_command": (c_int, [POINTER(ArmModel), POINTER(ArmLayout), c_int, c_void_p, c_int, c_int, c_void_p, c_void_p,
+                                c_void_p, c_void_p, c_int, c_void_p]),
+    "rmb_arm_get_command": (c_int, [POINTER(ArmModel), POINTER(ArmLayout), c_void_p, c_void_p, c_void_p, c_void_p, c_int,
+                                    c_void_p, c_int, c_void_p]),
     "rmb_obs_ring_push": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int64, c_void_p]),
     "rmb_gather_rows": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int64, c_void_p]),
     "rmb_action_fifo_step": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int, c_void_p, c_void_p,

@@ -69,11 +69,16 @@ bool plan_attention(AttnPlan* a, const void* Q, int ldq, int q_col0, bool q_shar
   return true;
 }
 
-// attention_v2_kernel (persistent, two streams per CTA, one sweep) unless RMB_ATTN_V1=1 asks for the first version
+// attention_tc_kernel (two sweeps, two CTAs per SM) is the default: 0.47 ms per encoder launch at 256 episodes.
+// RMB_ATTN_V2=1 selects attention_v2_kernel (persistent, two streams per CTA, one sweep), correct but at 0.63 ms not yet
+// faster: its softmax warps still wait on the S / P hand-offs (ncu: profiles/r02_attention_v2_ncu_full_summary.txt).
 cudaError_t launch_attention_v1(const AttnPlan& a, cudaStream_t stream);
+bool attention_use_v2() {
+  static const bool v2 = [] { const char* e = getenv("RMB_ATTN_V2"); return e != nullptr && e[0] == '1'; }();
+  return v2;
+}
 cudaError_t launch_attention(const AttnPlan& a, cudaStream_t stream) {
-  static const bool v1 = [] { const char* e = getenv("RMB_ATTN_V1"); return e != nullptr && e[0] == '1'; }();
-  if (v1) return launch_attention_v1(a, stream);
+  if (!attention_use_v2()) return launch_attention_v1(a, stream);
   static bool attr_set = false;
   static int sms = 148;
   if (!attr_set) {
@@ -896,7 +901,7 @@ static int forward_impl(rmb_act_engine_t* e, const void* d_images, int image_for
     }
     snprintf(nm, sizeof(nm), "enc%d V proj", l); RMB_RUN(run_gemm(nm, pl.v, tokb));
     snprintf(nm, sizeof(nm), "enc%d self-attention", l);
-    begin(nm, "attention_v2_kernel", attn_flops, attn_bytes);
+    begin(nm, attention_use_v2() ? "attention_v2_kernel" : "attention_tc_kernel", attn_flops, attn_bytes);
     RMB_CUDA(launch_attention(pl.attn, s));
     end();
     if (bp->ln_fused) {
@@ -919,7 +924,7 @@ static int forward_impl(rmb_act_engine_t* e, const void* d_images, int image_for
   }
   RMB_RUN(run_gemm("dec0 K proj", bp->dk, tokb));
   RMB_RUN(run_gemm("dec0 V proj", bp->dv, tokb));
-  begin("dec0 cross-attention", "attention_v2_kernel", 4.0 * batch * (double)C * L * 512, (double)BL * 512 * 2 * 2 + (double)BC * 512 * 2);
+  begin("dec0 cross-attention", attention_use_v2() ? "attention_v2_kernel" : "attention_tc_kernel", 4.0 * batch * (double)C * L * 512, (double)BL * 512 * 2 * 2 + (double)BC * 512 * 2);
   RMB_CUDA(launch_attention(bp->dattn, s));
   end();
   RMB_RUN(run_gemm("dec0 out proj +tgt", bp->dout, (double)BC * 512 * 2));
@@ -1157,3 +1162,4 @@ int rmb_layernorm512(const float* d_x, const float* d_gamma, const float* d_beta
 #include "pointcloud.cuh"
 #include "resize.cuh"
 #include "rollout_glue.cuh"
+#include "ik.cuh"

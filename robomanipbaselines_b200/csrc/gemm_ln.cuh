@@ -39,6 +39,17 @@ __device__ __forceinline__ void gemm_ln_epilogue(const GemmParams& p, uint8_t* s
   const int col0 = half * 32 + sub * 4;            // first of this lane's 4 columns inside chunk 0 of this warp
   const long long M = p.W;
   uint32_t acc_phase = 0;
+  // The residual rows of a tile (256 KB per CTA, straight from HBM: the previous LayerNorm wrote them a whole launch ago)
+  // are requested into L2 long before phase A reads them: with eight float4 loads per lane in flight a warp covers only
+  // 4 KB per HBM round trip, which alone would bound the epilogue at ~20 GB/s per SM.
+  auto prefetch_residual = [&](int t) {
+    const long long grow = static_cast<long long>(t) * 128 + q * 32 + lane;
+    if (grow < M) {
+      const char* rrow = reinterpret_cast<const char*>(static_cast<const float*>(p.residual) + grow * BLOCK_N + half * 32);
+#pragma unroll
+      for (int j = 0; j < kChunks; ++j) prefetch_l2(rrow + j * 256);
+    }
+  };
   for (int ti = ts.first; ti < ts.count; ti += ts.step) {
     const int tile = ts.tile(ti);                  // n_col_tiles == 1: tile == row tile
     const long long row_q = static_cast<long long>(tile) * 128 + q * 32;
@@ -50,15 +61,7 @@ __device__ __forceinline__ void gemm_ln_epilogue(const GemmParams& p, uint8_t* s
 #define RMB_LN_OK(it) (4 * (it) < rows_left)
 #define RMB_LN_R(it) (rbase + (it) * 4 * BLOCK_N)
 #define RMB_LN_O(it) (obase + (it) * 4 * BLOCK_N)
-    {
-      // residual rows of this quarter go to L2 while the accumulator is still being built
-      const long long grow = row_q + lane;
-      if (grow < M) {
-        const char* rrow = reinterpret_cast<const char*>(static_cast<const float*>(p.residual) + grow * BLOCK_N + half * 32);
-#pragma unroll
-        for (int j = 0; j < kChunks; ++j) prefetch_l2(rrow + j * 256);
-      }
-    }
+    if (ti == ts.first) prefetch_residual(tile);   // later tiles are prefetched one tile ahead, under phase B (below)
     mbar_wait(&tmem_full_bar[0], acc_phase);
     tc_fence_after();
     const uint32_t t_row = tmem_base + half * 32 + (static_cast<uint32_t>(q * 32) << 16);
@@ -115,6 +118,7 @@ __device__ __forceinline__ void gemm_ln_epilogue(const GemmParams& p, uint8_t* s
       rstd[it] = rsqrtf(var + p.ln_eps);
     }
     // ---------------------------------------------------------------- phase B
+    if (ti + ts.step < ts.count) prefetch_residual(ts.tile(ti + ts.step));
     act_t* yact = static_cast<act_t*>(p.ln_y_act);
     act_t* ypos = static_cast<act_t*>(p.ln_ypos_act);
     // The parked rows come back from L2: all eight loads of a chunk are issued before anything is stored (a store in

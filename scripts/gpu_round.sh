@@ -20,7 +20,7 @@ run t_gemm 300 $PT tests/test_kernels_gpu.py -k "test_gemm"
 run t_conv 300 $PT tests/test_kernels_gpu.py -k "test_conv"
 run t_stem 300 $PT tests/test_kernels_gpu.py -k "preprocess_and_stem or stem_pool"
 run t_attn 300 $PT tests/test_kernels_gpu.py -k "test_attention"
-RMB_ATTN_V1=1 run t_attn_v1 300 $PT tests/test_kernels_gpu.py -k "test_attention and not online"
+RMB_ATTN_V2=1 run t_attn_v2 300 $PT tests/test_kernels_gpu.py -k "test_attention"
 run t_engine 600 $PT tests/test_act_engine_gpu.py
 ENGINE_RC=$?
 run t_diffusion 900 $PT tests/test_diffusion_gpu.py
