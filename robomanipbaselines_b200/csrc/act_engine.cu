@@ -164,10 +164,12 @@ struct rmb_act_engine {
   act_t *kd = nullptr, *vd = nullptr, *aod = nullptr, *t_b = nullptr, *hd = nullptr;
   float *yd = nullptr, *t_f32 = nullptr, *yd2 = nullptr;
 
-  // RMB_LN_FUSE = auto (default): the encoder's residual GEMMs carry their LayerNorm when there is a 256-row pair tile
-  // for every SM pair, else GEMM + layernorm512_kernel (narrow tiles spread a small batch over more SMs); always /
-  // never force one path (tests: each path is bit-invariant to the batch size; the two agree to fp32 round-off)
-  int fuse_ln = 1;              // 0 never, 1 auto, 2 always
+  // RMB_LN_FUSE: never (default) = residual GEMM + layernorm512_kernel; always = the encoder's residual GEMMs carry
+  // their LayerNorm (gemm_ln.cuh); auto = fused when there is a 256-row pair tile for every SM pair. The fused launch
+  // is correct (tests) but measured SLOWER on B200 (out-proj 0.40 vs 0.20 + 0.13 ms, FFN-down 0.64 vs 0.39 + 0.16 ms at
+  // 256 episodes, same box): one TMEM accumulator serialises the MMAs with the first epilogue phase and the epilogue is
+  // memory-latency bound (ncu: profiles/r02_gemm_ln_out_proj_ncu_full_summary.txt), so it is opt-in.
+  int fuse_ln = 0;              // 0 never, 1 auto, 2 always
   bool fuse_stem_pool = true;   // RMB_NO_STEM_POOL=1: stem and max-pool as two kernels through a [img, H/2, W/2, 64] buffer
   struct BatchPlans {
     HaloPlan stem;
@@ -306,7 +308,7 @@ int rmb_act_engine_create(const rmb_act_config_t* cfg, rmb_act_engine_t** out) {
   cudaGetDeviceProperties(&prop, cfg->device);
   e->num_sms = prop.multiProcessorCount;
   { const char* ev = getenv("RMB_NO_STEM_POOL"); e->fuse_stem_pool = !(ev != nullptr && ev[0] == '1'); }
-  { const char* ev = getenv("RMB_LN_FUSE"); e->fuse_ln = (ev == nullptr) ? 1 : (ev[0] == 'n' ? 0 : (ev[0] == 'a' && ev[1] == 'l') ? 2 : 1); }
+  { const char* ev = getenv("RMB_LN_FUSE"); e->fuse_ln = (ev == nullptr) ? 0 : (ev[0] == 'n' ? 0 : (ev[0] == 'a' && ev[1] == 'l') ? 2 : 1); }
   e->Hf = cfg->img_h / 32; e->Wf = cfg->img_w / 32;
   e->n_prefix = 2 + (cfg->task_token ? 1 : 0);
   e->L = e->n_prefix + e->Hf * e->Wf * cfg->num_cams;

@@ -43,12 +43,8 @@ __device__ __forceinline__ void gemm_ln_epilogue(const GemmParams& p, uint8_t* s
   // are requested into L2 long before phase A reads them: with eight float4 loads per lane in flight a warp covers only
   // 4 KB per HBM round trip, which alone would bound the epilogue at ~20 GB/s per SM.
   auto prefetch_residual = [&](int t) {
-    const long long grow = static_cast<long long>(t) * 128 + q * 32 + lane;
-    if (grow < M) {
-      const char* rrow = reinterpret_cast<const char*>(static_cast<const float*>(p.residual) + grow * BLOCK_N + half * 32);
-#pragma unroll
-      for (int j = 0; j < kChunks; ++j) prefetch_l2(rrow + j * 256);
-    }
+    const long long grow = static_cast<long long>(t) * 128 + q * 32 + lane;      // one 2 KB row per thread of warps 0..3
+    if (half == 0 && grow < M) prefetch_l2_bulk(static_cast<const float*>(p.residual) + grow * BLOCK_N, BLOCK_N * 4);
   };
   for (int ti = ts.first; ti < ts.count; ti += ts.step) {
     const int tile = ts.tile(ti);                  // n_col_tiles == 1: tile == row tile

@@ -133,6 +133,11 @@ __device__ __forceinline__ void prefetch_l2(const void* p) {
   asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
 }
 
+// bulk L2 prefetch of `bytes` (multiple of 16) contiguous bytes starting at a 16-byte aligned address
+__device__ __forceinline__ void prefetch_l2_bulk(const void* p, uint32_t bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
+}
+
 // ---------------------------------------------------------------- programmatic dependent launch
 // Kernels launched with cudaLaunchAttributeProgrammaticStreamSerialization may start while their predecessor in the
 // stream is still running. pdl_trigger(): this CTA no longer holds the next kernel back (it is scheduled onto free SMs

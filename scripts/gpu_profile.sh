@@ -13,14 +13,15 @@ timeout 300 python scripts/profile_step.py --batch 256 --once > gpurun_out/plain
 timeout 900 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none --csv \
     --log-file "gpurun_out/${TAG}_ncu_launches.csv" python scripts/profile_step.py --batch 256 --once > gpurun_out/ncu_list.log 2>&1
 echo "ncu list rc=$?"
-for REGEX in "$@"; do
+for SPEC in "$@"; do
+  REGEX=${SPEC%%:*}; SKIP=${SPEC##*:}
   NAME="${TAG}_$(echo "$REGEX" | tr -c 'a-zA-Z0-9' '_')"
-  timeout 900 ncu --set full --clock-control none --import-source on -k "regex:$REGEX" -s 2 -c 1 -f -o "gpurun_out/$NAME" \
+  timeout 900 ncu --set full --clock-control none --import-source on --kernel-name-base demangled -k "regex:$REGEX" -s "$SKIP" -c 1 -f -o "gpurun_out/$NAME" \
       python scripts/profile_step.py --batch 64 --once > "gpurun_out/$NAME.log" 2>&1
   echo "ncu full $REGEX rc=$?"
   ncu -i "gpurun_out/$NAME.ncu-rep" --page raw --csv > "gpurun_out/$NAME.raw.csv" 2>/dev/null
   ncu -i "gpurun_out/$NAME.ncu-rep" --page details > "gpurun_out/$NAME.details.txt" 2>/dev/null
-  SZ=$(stat -c %s "gpurun_out/$NAME.ncu-rep" 2>/dev/null || echo 0)
-  if [ "$SZ" -gt 20000000 ]; then rm -f "gpurun_out/$NAME.ncu-rep"; fi
+  ncu -i "gpurun_out/$NAME.ncu-rep" --page source --csv > "gpurun_out/$NAME.source.csv" 2>/dev/null
+  rm -f "gpurun_out/$NAME.ncu-rep"
 done
 ls -la gpurun_out | head -40

@@ -28,10 +28,14 @@ run t_pointcloud 300 $PT tests/test_pointcloud_gpu.py
 run t_resize 300 $PT tests/test_resize_gpu.py
 run t_glue 300 $PT tests/test_rollout_glue_gpu.py
 run t_mtact 600 $PT tests/test_mt_act_gpu.py
+run t_consumer 300 $PT tests/test_action_consumer_gpu.py
 run t_classes 600 $PT tests/test_rollout_classes_gpu.py
 run t_dtype 900 $PT tests/test_dtype_builds_gpu.py
 if [ "$1" != "--no-bench" ] && [ $ENGINE_RC -eq 0 ]; then
   run smoke 300 python -c "import __graft_entry__ as g; g.smoke()"
-  run bench 900 python bench.py --steps 5 --warmup 3
+  run bench 900 python bench.py --steps 10 --warmup 3
+  timeout 300 python scripts/profile_step.py --batch 256 > gpurun_out/table.txt 2>&1
+  RMB_LN_FUSE=never timeout 300 python scripts/profile_step.py --batch 256 > gpurun_out/table_ln_never.txt 2>&1
+  tail -n 1 gpurun_out/table.txt gpurun_out/table_ln_never.txt
 fi
 exit 0
