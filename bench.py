@@ -403,10 +403,13 @@ def cpu_arm(sample, iters, warmup):
     sd = act_weights(shell)
     meta = act_meta()
     images, state = synthetic_act_observations(sample, NCAM, IMG_H, IMG_W, DS, seed=1)
+    import contextlib
+
     from oracle import reference_runner
 
     if reference_runner.reference_root() is not None:
-        runner = reference_runner.ReferenceActRollout(POLICY_ARGS, DS, DA, sd, meta, POLICY_ARGS["camera_names"], sample)
+        with contextlib.redirect_stdout(sys.stderr):      # the reference prints its parameter count while it is built
+            runner = reference_runner.ReferenceActRollout(POLICY_ARGS, DS, DA, sd, meta, POLICY_ARGS["camera_names"], sample)
         kind = "reference"
         what = ("the reference's own ACTPolicy/DETRVAE (third_party/act) + RolloutAct.infer_policy, unmodified sources from "
                 f"{os.path.relpath(runner.root, ROOT) if runner.root.startswith(ROOT) else runner.root}, fp32 eager PyTorch")

@@ -48,7 +48,7 @@ def main():
             continue
         unit = r.get("Metric Unit", "")
         scale = {"Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "byte": 1.0, "usecond": 1e-3, "msecond": 1.0, "nsecond": 1e-6,
-                 "second": 1e3}.get(unit, 1.0)
+                 "second": 1e3, "ns": 1e-6, "us": 1e-3, "ms": 1.0, "s": 1e3}.get(unit, 1.0)
         e[r["Metric Name"]] = val * scale
     ids = sorted(rows)
     if args.last_step:
