@@ -126,6 +126,7 @@ struct rmb_unet_engine {
   float* b_film = nullptr;
 
   // workspace
+  int xcol_w = 64;          // im2col width of the network input: kernel_size * input_dim rounded up to 64 or 128
   act_t *xcol = nullptr, *gcm = nullptr, *h1 = nullptr, *resb = nullptr, *xa = nullptr, *xb = nullptr;
   act_t* cat[4] = {};
   float *film_gc = nullptr, *conv_out = nullptr, *x_state = nullptr;
@@ -192,7 +193,7 @@ int rmb_unet_engine_create(const rmb_unet_config_t* cfg, rmb_unet_engine_t** out
   if (cfg->n_levels < 2 || cfg->n_levels > 4) return fail("rmb_unet: n_levels must be 2..4");
   if (cfg->n_groups != 8) return fail("rmb_unet: n_groups must be 8");
   if (cfg->kernel_size < 1 || cfg->kernel_size % 2 == 0 || cfg->kernel_size > kMaxTaps) return fail("rmb_unet: kernel_size must be odd and <= 9");
-  if (cfg->input_dim < 1 || cfg->kernel_size * cfg->input_dim > kXcolWidth) return fail("rmb_unet: kernel_size * input_dim must be <= 64");
+  if (cfg->input_dim < 1 || cfg->kernel_size * cfg->input_dim > kXcolMaxWidth) return fail("rmb_unet: kernel_size * input_dim must be <= 128 (action dim <= 25 at kernel size 5)");
   if (cfg->horizon < 1 || (cfg->horizon & (cfg->horizon - 1)) != 0 || (cfg->horizon >> (cfg->n_levels - 1)) < 1) return fail("rmb_unet: horizon must be a power of two >= 2^(n_levels-1)");
   if (cfg->max_batch < 1 || cfg->global_cond_dim < 1 || cfg->dsed < 2 || cfg->dsed % 2 != 0 || cfg->num_train_timesteps < 1) return fail("rmb_unet: bad config");
   for (int i = 0; i < cfg->n_levels; ++i) {
@@ -203,6 +204,7 @@ int rmb_unet_engine_create(const rmb_unet_config_t* cfg, rmb_unet_engine_t** out
   if (int r = rmb_check_device(cfg->device)) return r;
   auto* e = new rmb_unet_engine();
   e->cfg = *cfg;
+  e->xcol_w = (cfg->kernel_size * cfg->input_dim <= 64) ? 64 : 128;
   cudaDeviceProp prop;
   cudaGetDeviceProperties(&prop, cfg->device);
   e->num_sms = prop.multiProcessorCount;
@@ -296,16 +298,16 @@ int rmb_unet_finalize(rmb_unet_engine_t* e) {
       // Conv1d(Da -> cout, K) and the 1x1 residual conv both read the im2col row [tap*Da + a] (64 columns)
       const auto* W = e->find(p + "blocks.0.block.0.weight", (size_t)b.cout * Da * K, &err); if (!W) return fail(err);
       const auto* B0 = e->find(p + "blocks.0.block.0.bias", b.cout, &err); if (!B0) return fail(err);
-      std::vector<float> r((size_t)b.cout * kXcolWidth, 0.f);
+      std::vector<float> r((size_t)b.cout * e->xcol_w, 0.f);
       for (int co = 0; co < b.cout; ++co)
         for (int a = 0; a < Da; ++a)
-          for (int kk = 0; kk < K; ++kk) r[(size_t)co * kXcolWidth + kk * Da + a] = (*W)[((size_t)co * Da + a) * K + kk];
+          for (int kk = 0; kk < K; ++kk) r[(size_t)co * e->xcol_w + kk * Da + a] = (*W)[((size_t)co * Da + a) * K + kk];
       if (!e->up_act(r, &b.w0, &err) || !e->up_f32(*B0, &b.b0, &err)) return fail(err);
       const auto* WR = e->find(p + "residual_conv.weight", (size_t)b.cout * Da, &err); if (!WR) return fail(err);
       const auto* BR = e->find(p + "residual_conv.bias", b.cout, &err); if (!BR) return fail(err);
-      std::vector<float> rr((size_t)b.cout * kXcolWidth, 0.f);
+      std::vector<float> rr((size_t)b.cout * e->xcol_w, 0.f);
       for (int co = 0; co < b.cout; ++co)
-        for (int a = 0; a < Da; ++a) rr[(size_t)co * kXcolWidth + pad * Da + a] = (*WR)[(size_t)co * Da + a];
+        for (int a = 0; a < Da; ++a) rr[(size_t)co * e->xcol_w + pad * Da + a] = (*WR)[(size_t)co * Da + a];
       if (!e->up_act(rr, &b.wres, &err) || !e->up_f32(*BR, &b.bres, &err)) return fail(err);
     } else {
       if (!e->up_conv1d(p + "blocks.0.block.0", b.cout, b.cin, K, &b.w0, &b.b0, &err)) return fail(err);
@@ -372,7 +374,7 @@ int rmb_unet_finalize(rmb_unet_engine_t* e) {
     }
     const size_t B = c.max_batch;
     bool ok = true;
-    ok &= (e->xcol = e->dalloc<act_t>(B * c.horizon * kXcolWidth)) != nullptr;
+    ok &= (e->xcol = e->dalloc<act_t>(B * c.horizon * e->xcol_w)) != nullptr;
     ok &= (e->gcm = e->dalloc<act_t>(B * e->Gp)) != nullptr;
     ok &= (e->film_gc = e->dalloc<float>(B * e->film_total)) != nullptr;
     ok &= (e->conv_out = e->dalloc<float>(B * maxTC)) != nullptr;
@@ -454,7 +456,7 @@ static int unet_build_plans(rmb_unet_engine* e, int nb, rmb_unet_engine::Plans**
   auto crb = [&](const rmb_unet_engine::Crb& b, const act_t* x_in, int ld_x, act_t* x_out, int ld_o) -> bool {
     const act_t* res = x_in; int ld_res = ld_x;
     const act_t* in0 = b.first ? e->xcol : x_in;
-    const int ld0 = b.first ? kXcolWidth : ld_x, cin0 = b.first ? kXcolWidth : b.cin, taps0 = b.first ? 1 : K;
+    const int ld0 = b.first ? e->xcol_w : ld_x, cin0 = b.first ? e->xcol_w : b.cin, taps0 = b.first ? 1 : K;
     if (!conv_gn(b.name + " conv0", in0, ld0, cin0, b.T, taps0, b.w0, b.cout, b.b0, b.g0, b.be0, b.film_off, nullptr, 0, e->h1, b.cout)) return false;
     if (b.has_res) {
       if (!conv_s1(b.name + " res1x1", in0, ld0, cin0, b.T, 1, b.wres, b.cout, b.bres, e->resb, b.cout, false)) return false;
@@ -522,8 +524,8 @@ static int unet_build_plans(rmb_unet_engine* e, int nb, rmb_unet_engine::Plans**
     FinalParams& f = pl->fin;
     memset(&f, 0, sizeof(f));
     f.gn.in = e->conv_out; f.gn.in_f32 = 1; f.gn.ld_in = C; f.gn.gamma = e->g_fin; f.gn.beta = e->be_fin; f.gn.C = C; f.gn.T = T0;
-    f.w_head = e->w_head; f.b_head = e->b_head; f.Da = c.input_dim; f.ksize = K; f.xcol = e->xcol;
-    pl->fin_bytes = (double)nb * T0 * C * 4 + (double)nb * T0 * (c.input_dim * 12 + kXcolWidth * 2);
+    f.w_head = e->w_head; f.b_head = e->b_head; f.Da = c.input_dim; f.ksize = K; f.xcol = e->xcol; f.xcol_w = e->xcol_w;
+    pl->fin_bytes = (double)nb * T0 * C * 4 + (double)nb * T0 * (c.input_dim * 12 + e->xcol_w * 2);
   }
   *out = pl.get();
   e->plans[nb] = std::move(pl);
@@ -649,7 +651,7 @@ int rmb_unet1d_denoise(rmb_unet_engine_t* e, const float* d_global_cond, const f
   rmb_unet_engine::Plans* pl = nullptr;
   if (int r = unet_build_plans(e, batch, &pl)) return r;
   if (int r = unet_prepare_cond(e, pl, d_global_cond, batch, s)) return r;
-  unet_init_kernel<<<batch, 256, 0, s>>>(d_x_init, d_x_out, e->xcol, c.horizon, c.input_dim, c.kernel_size);
+  unet_init_kernel<<<batch, 256, 0, s>>>(d_x_init, d_x_out, e->xcol, c.horizon, c.input_dim, c.kernel_size, e->xcol_w);
   const size_t per_step = (size_t)batch * c.horizon * c.input_dim;
   for (int i = 0; i < n_steps; ++i) {
     FinalParams fin = pl->fin;
@@ -672,7 +674,7 @@ static int unet_forward_impl(rmb_unet_engine_t* e, const float* d_sample, int ti
   rmb_unet_engine::Plans* pl = nullptr;
   if (int r = unet_build_plans(e, batch, &pl)) return r;
   if (int r = unet_prepare_cond(e, pl, d_global_cond, batch, s)) return r;
-  unet_init_kernel<<<batch, 256, 0, s>>>(d_sample, e->x_state, e->xcol, c.horizon, c.input_dim, c.kernel_size);
+  unet_init_kernel<<<batch, 256, 0, s>>>(d_sample, e->x_state, e->xcol, c.horizon, c.input_dim, c.kernel_size, e->xcol_w);
   FinalParams fin = pl->fin;
   fin.x = e->x_state; fin.noise = nullptr; fin.model_out = d_out;
   fin.st.kind = 2;

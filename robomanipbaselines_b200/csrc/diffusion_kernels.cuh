@@ -17,7 +17,7 @@
 namespace rmb {
 
 constexpr int kGnMaxVec = 16;      // float4 vectors a lane may hold: T * (C / 8) / 128 <= 16
-constexpr int kXcolWidth = 64;     // im2col row of the UNet input: kernel_size * input_dim <= 64 columns (rest zero)
+constexpr int kXcolMaxWidth = 128;  // im2col row of the UNet input: kernel_size * input_dim padded to 64 or 128 columns (rest zero)
 
 __device__ __forceinline__ float mish_f(float x) {
   // x * tanh(softplus(x)) with tanh(log(1 + e)) = n / (n + 2), n = e * (e + 2), e = exp(x). Branch-free: the exponent is
@@ -142,7 +142,8 @@ struct FinalParams {
   float* x;                 // [B, T, Da] fp32 trajectory, updated in place
   const float* noise;       // [B, T, Da] or nullptr
   float* model_out;         // kind 2: [B, T, Da]
-  act_t* xcol;              // [B*T, 64] im2col of the new x for the first conv of the next step
+  act_t* xcol;              // [B*T, xcol_w] im2col of the new x for the first conv of the next step
+  int xcol_w;               // 64 or 128 (kernel_size * Da rounded up)
   SchedStep st;
 };
 
@@ -239,33 +240,34 @@ __global__ void __launch_bounds__(256) unet_final_step_kernel(const FinalParams 
   }
   __syncthreads();
   const int pad = p.ksize >> 1, kd = p.ksize * Da;
-  for (int i = threadIdx.x; i < T * kXcolWidth; i += 256) {
-    const int t = i / kXcolWidth, j = i - t * kXcolWidth;
+  const int xw = p.xcol_w;
+  for (int i = threadIdx.x; i < T * xw; i += 256) {
+    const int t = i / xw, j = i - t * xw;
     float val = 0.f;
     if (j < kd) {
       const int tap = j / Da, a = j - tap * Da, tt = t + tap - pad;
       if (tt >= 0 && tt < T) val = xs[tt * Da + a];
     }
-    p.xcol[(static_cast<long long>(b) * T + t) * kXcolWidth + j] = to_act(val);
+    p.xcol[(static_cast<long long>(b) * T + t) * xw + j] = to_act(val);
   }
 }
 
 // x_T (initial noise trajectory) -> fp32 state + im2col. One CTA per sample.
 __global__ void unet_init_kernel(const float* __restrict__ x_init, float* __restrict__ x, act_t* __restrict__ xcol,
-                                 int T, int Da, int ksize) {
+                                 int T, int Da, int ksize, int xw) {
   const int b = blockIdx.x;
   const float* src = x_init + static_cast<long long>(b) * T * Da;
   if (x != x_init)
     for (int i = threadIdx.x; i < T * Da; i += blockDim.x) x[static_cast<long long>(b) * T * Da + i] = src[i];
   const int pad = ksize >> 1, kd = ksize * Da;
-  for (int i = threadIdx.x; i < T * kXcolWidth; i += blockDim.x) {
-    const int t = i / kXcolWidth, j = i - t * kXcolWidth;
+  for (int i = threadIdx.x; i < T * xw; i += blockDim.x) {
+    const int t = i / xw, j = i - t * xw;
     float val = 0.f;
     if (j < kd) {
       const int tap = j / Da, a = j - tap * Da, tt = t + tap - pad;
       if (tt >= 0 && tt < T) val = src[tt * Da + a];
     }
-    xcol[(static_cast<long long>(b) * T + t) * kXcolWidth + j] = to_act(val);
+    xcol[(static_cast<long long>(b) * T + t) * xw + j] = to_act(val);
   }
 }
 

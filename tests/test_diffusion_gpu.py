@@ -18,6 +18,8 @@ UNET_CASES = {
     "mid3": dict(B=5, T=16, Da=7, G=142, dsed=128, down_dims=(64, 128, 256), k=5),
     "full_dp": dict(B=2, T=16, Da=7, G=142, dsed=128, down_dims=(512, 1024, 2048), k=5),
     "full_dp3": dict(B=9, T=16, Da=7, G=256, dsed=128, down_dims=(512, 1024, 2048), k=5),
+    # bimanual action space (14-d, e.g. ALOHA): kernel_size * Da = 70 > 64, the network input's im2col is 128 wide
+    "bimanual14": dict(B=4, T=16, Da=14, G=284, dsed=128, down_dims=(64, 128, 256), k=5),
 }
 
 
@@ -51,7 +53,7 @@ def test_unet_forward(cuda, case):
     assert eng.launches_per_step > 0 and eng.step_flops(1) > 0
 
 
-@pytest.mark.parametrize("case,kind,n_steps", [("small", "ddpm", 100), ("mid3", "ddim", 10), ("full_dp", "ddpm", 100),
+@pytest.mark.parametrize("case,kind,n_steps", [("small", "ddpm", 100), ("mid3", "ddim", 10), ("bimanual14", "ddim", 16), ("full_dp", "ddpm", 100),
                                                ("full_dp3", "ddim", 10), ("full_dp3", "ddim", 16)])
 def test_denoise_loop(cuda, case, kind, n_steps):
     c, ref, eng, x, gc, g = _unet_pair(case, cuda)
