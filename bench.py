@@ -365,9 +365,7 @@ def bench_micro(device):
                              "what": "DDPM step t=59 (x, model output, noise in; x' out), 4 x 256 MB arrays >> L2"}
     del x, o, z, y
     B, C, Da = 65536, CHUNK, DA
-    from robomanipbaselines_b200.common.ensemble import ring_row_width
-
-    ring = torch.zeros(B, C, C, ring_row_width(Da), device=device)
+    ring = torch.zeros(B, C, C, Da, device=device)
     chunks = torch.randn(B, C, Da, device=device)
     step = torch.zeros(B, device=device, dtype=torch.int32)
     wtab = torch.from_numpy(make_weight_table(C)).to(device)
@@ -385,8 +383,7 @@ def bench_micro(device):
     gbs = per_ep * B / ms / 1e6
     out["ensemble_step"] = {"kernel": "ensemble_step_kernel", "episodes": B, "algorithmic_bytes": per_ep * B, "ms": ms,
                             "achieved_gbs": gbs, "peak_gbs": peak, "frac": gbs / peak,
-                            "what": "temporal ensembling with a full 100-chunk history per episode, 21 GB time-major ring buffer "
-                                    "(contiguous row read, one 32-byte sector per scattered entry)"}
+                            "what": "temporal ensembling with a full 100-chunk history per episode, 18 GB ring buffer"}
     del ring, chunks
     torch.cuda.empty_cache()
     return out

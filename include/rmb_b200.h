@@ -119,10 +119,7 @@ int64_t rmb_act_read_attention_maps(rmb_act_engine_t* e, float* d_out, void* str
 
 /* ---- RolloutAct.infer_policy temporal ensembling + denormalize_data
  *      (robo_manip_baselines/policy/act/RolloutAct.py:68-101; common/utils/DataUtils.py:26-40)
- * d_ring  float32 [batch, C, C, Dp]   Dp = Da rounded up to a multiple of 8. TIME-major: row (t mod C) collects the
- *                                     predictions for time step t, column i ("age") the one made i calls earlier
- *                                     (= element i of the chunk of call t - i), so that a step reads one contiguous run
- *                                     and writes whole 32-byte sectors; must start zero-filled or be reset
+ * d_ring  float32 [batch, C, C, Da]   slot (n mod C) holds the chunk of policy call n
  * d_chunks float32 [batch, C, Da]     chunk predicted at this call (output of rmb_act_forward)
  * d_step  int32 [batch]               per-episode 0-based policy-call counter, advanced by one
  * d_reset uint8 [batch] or NULL       1 = episode restarts at this call (RolloutAct.reset_variables :62-66)

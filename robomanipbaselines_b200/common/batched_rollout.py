@@ -12,7 +12,7 @@ import torch
 
 from .. import _lib
 from .._lib import check, cur_stream, ptr
-from .ensemble import make_weight_table, ring_row_width, ring_to_slots
+from .ensemble import make_weight_table
 
 
 def _check_device_tensor(t, dtype, shape, device, name):
@@ -71,7 +71,7 @@ class BatchedRollout:
         self.Ds = len(model_meta_info["state"]["example"])
         self.no_temp_ensem = no_temp_ensem
         dev = self.device
-        self.ring = torch.zeros(batch, self.C, self.C, ring_row_width(self.Da), device=dev, dtype=torch.float32)   # time-major, see csrc/elementwise.cuh
+        self.ring = torch.zeros(batch, self.C, self.C, self.Da, device=dev, dtype=torch.float32)
         self.step = torch.zeros(batch, device=dev, dtype=torch.int32)
         self.reset_mask = torch.zeros(batch, device=dev, dtype=torch.uint8)
         self.wtab = torch.from_numpy(make_weight_table(self.C)).to(dev)
@@ -222,10 +222,6 @@ class BatchedRollout:
               "rmb_action_fifo_step")
         self._host_pos += 1
         return self.action
-
-    def history(self):
-        """The chunk history as the reference keeps it: (B, C, C, Da), slot (n mod C) = chunk of policy call n."""
-        return ring_to_slots(self.ring, self.Da)
 
     def check_fault(self):
         """Raise RmbError if a kernel of this process recorded a fault since the last check (synchronises)."""

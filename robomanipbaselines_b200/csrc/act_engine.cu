@@ -1012,7 +1012,7 @@ int rmb_ensemble_step(float* d_ring, const float* d_chunks, int32_t* d_step, con
   if (norm_type != 0 && norm_type != 1) return fail("rmb_ensemble_step: norm_type must be 0 (gaussian) or 1 (limits)");
   DenormParams dn{d_p0, d_p1, out_min, norm_type};
   PdlScope pdl;
-  const size_t diag_bytes = static_cast<size_t>(C) * ensemble_row_width(Da) * sizeof(float);
+  const size_t diag_bytes = static_cast<size_t>(C) * Da * sizeof(float);
   const int use_smem = diag_bytes <= 48 * 1024 ? 1 : 0;
   RMB_CUDA(launch_pdl(ensemble_step_kernel, dim3(batch), dim3(128), use_smem ? diag_bytes : 0, static_cast<cudaStream_t>(stream_), d_ring, d_chunks, d_step, d_reset, d_wtab, dn, d_action, d_action_f32, d_action_norm, C, Da, use_smem));
   return 0;

@@ -284,29 +284,22 @@ __global__ void act_head_kernel(const float* __restrict__ x_in, const float* __r
 
 // ---------------------------------------------------------------------------------------------------------------------
 // Temporal ensembling ring buffer (policy/act/RolloutAct.py:68-101).
-//   ring   [B, C, C, Dp] fp32 : TIME-major. Row (t mod C) collects the predictions made for time step t; column `age` i
-//                               holds the one made i calls earlier, i.e. element i of the chunk of call t - i.
-//                               Dp = Da rounded up to 8 floats, so every (row, age) entry is whole 32-byte sectors.
-//                               At call n the kernel scatters its chunk (element i -> row (n + i) mod C, age i: one
-//                               full-sector store each) and reads row n mod C, ages 0..m-1: ONE contiguous run.
-//                               (Round 1 kept it call-major [slot n mod C][i]: the read was a diagonal gather of one
-//                               28-byte row per 2.8 KB slot, 0.21 of the HBM peak on the micro-benchmark.)
+//   ring   [B, C, C, Da] fp32 : slot (n mod C) holds the chunk predicted at policy call n of that episode
 //   chunks [B, C, Da]   fp32 : chunk predicted at this call
 //   step   [B] int32          : n = 0-based count of policy calls in the episode (advanced by this kernel)
 //   reset  [B] uint8 or null  : 1 -> episode restarts: n := 0 before this call (RolloutAct.reset_variables :62-66)
 //   wtab   [C, C] fp64        : wtab[(m-1)*C + r] = exp(-k r) / sum_{s<m} exp(-k s), made on the host with numpy so
 //                               that it is bit-identical to the reference's np.exp / np.sum
-// action = sum_{i<m} w[m-1-i] * A[n-i][i] accumulated in fp64 in the reference's order (i = 0 is the newest chunk),
+//   action_n = sum_{i=0}^{m-1} wtab[m-1][m-1-i] * A[n-i][i],  m = min(n+1, C), accumulated in fp64 in the order
 //   i = 0,1,... with separately rounded multiply and add (numpy semantics; no FMA contraction), then denormalised:
 //   gaussian: std*a + mean ; limits: scale*(a - out_min) + min       (common/utils/DataUtils.py:26-40)
-// One CTA per episode; the scatter and the row read are cooperative, the m-term sum runs on Da threads.
+// One thread per (episode, action dim); the chunk store is cooperative over the block.
 struct DenormParams {
   const double* a;   // gaussian: std   | limits: scale = range / (out_max - out_min)
   const double* b;   // gaussian: mean  | limits: min
   double out_min;    // limits only
   int type;          // 0 gaussian, 1 limits
 };
-__host__ __device__ __forceinline__ int ensemble_row_width(int Da) { return (Da + 7) & ~7; }
 __global__ void ensemble_step_kernel(float* __restrict__ ring, const float* __restrict__ chunks,
                                      int32_t* __restrict__ step, const uint8_t* __restrict__ reset,
                                      const double* __restrict__ wtab, DenormParams dn, double* __restrict__ action_out,
@@ -315,31 +308,41 @@ __global__ void ensemble_step_kernel(float* __restrict__ ring, const float* __re
   pdl_trigger();
   pdl_wait();
   const int b = blockIdx.x;
-  const int Dp = ensemble_row_width(Da);
   int n = step[b];
   if (reset != nullptr && reset[b]) n = 0;
-  float* ring_b = ring + static_cast<long long>(b) * C * C * Dp;
+  const int slot = n % C;
+  float* ring_b = ring + static_cast<long long>(b) * C * C * Da;
   const float* chunk_b = chunks + static_cast<long long>(b) * C * Da;
-  // scatter: element i of this call's chunk is the age-i prediction for time n + i
-  for (int idx = threadIdx.x; idx < C * Dp; idx += blockDim.x) {
-    const int i = idx / Dp, d = idx - i * Dp;
-    const int row = (n + i) % C;
-    ring_b[(static_cast<long long>(row) * C + i) * Dp + d] = (d < Da) ? chunk_b[i * Da + d] : 0.f;
-  }
+  for (int i = threadIdx.x; i < C * Da; i += blockDim.x) ring_b[static_cast<long long>(slot) * C * Da + i] = chunk_b[i];
   __syncthreads();
   const int m = n + 1 < C ? n + 1 : C;
-  const float* row_n = ring_b + static_cast<long long>(n % C) * C * Dp;     // ages 0..m-1, contiguous
-  extern __shared__ float ens_row[];
+  // stage the diagonal A[n-i][i] (i < m) in shared memory with all threads (m independent 28-byte gathers in flight at
+  // once instead of m dependent ones); the fp64 sum below keeps the reference's order
+  extern __shared__ float ens_diag[];
   if (use_smem) {
-    for (int idx = threadIdx.x; idx < m * Dp; idx += blockDim.x) ens_row[idx] = row_n[idx];
+    for (int idx = threadIdx.x; idx < m * Da; idx += blockDim.x) {
+      const int i = idx / Da, d = idx - i * Da;
+      int s = (n - i) % C;
+      if (s < 0) s += C;
+      ens_diag[idx] = ring_b[(static_cast<long long>(s) * C + i) * Da + d];
+    }
     __syncthreads();
   }
   if (threadIdx.x < Da) {
     const int d = threadIdx.x;
     const double* w = wtab + static_cast<long long>(m - 1) * C;
-    const float* src = use_smem ? ens_row : row_n;
     double acc = 0.0;
-    for (int i = 0; i < m; ++i) acc = __dadd_rn(acc, __dmul_rn(w[m - 1 - i], static_cast<double>(src[i * Dp + d])));
+    for (int i = 0; i < m; ++i) {
+      float av;
+      if (use_smem) {
+        av = ens_diag[i * Da + d];
+      } else {
+        int s = (n - i) % C;
+        if (s < 0) s += C;
+        av = ring_b[(static_cast<long long>(s) * C + i) * Da + d];
+      }
+      acc = __dadd_rn(acc, __dmul_rn(w[m - 1 - i], static_cast<double>(av)));
+    }
     double o;
     if (dn.type == 0) o = __dadd_rn(__dmul_rn(dn.a[d], acc), dn.b[d]);
     else o = __dadd_rn(__dmul_rn(dn.a[d], __dsub_rn(acc, dn.out_min)), dn.b[d]);

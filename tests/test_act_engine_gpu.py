@@ -136,7 +136,7 @@ def test_batched_rollout_matches_oracle(cuda):
             n_calls[b] += 1
             assert np.array_equal(act[b].cpu().numpy(), ref), (t, b)
             oring, filled = oracles[b].ring_view(n_calls[b])
-            assert np.array_equal(br.history()[b].cpu().numpy()[filled], oring[filled]), (t, b)
+            assert np.array_equal(br.ring[b].cpu().numpy()[filled], oring[filled]), (t, b)
         assert br.step.cpu().tolist() == n_calls
 
 

@@ -271,7 +271,7 @@ def test_layernorm(lib, cuda):
 def test_ensemble_bit_exact(lib, cuda, norm):
     """Ring positions, step counters and float64 actions must equal the numpy oracle exactly (C=7, wraps 3 times)."""
     from oracle.rollout_oracle import ActRolloutOracle
-    from robomanipbaselines_b200.common.ensemble import make_weight_table, ring_row_width, ring_to_slots
+    from robomanipbaselines_b200.common.ensemble import make_weight_table
 
     B, C, Da, steps = 5, 7, 3, 25
     rng = np.random.default_rng(3)
@@ -284,7 +284,7 @@ def test_ensemble_bit_exact(lib, cuda, norm):
     else:
         p0, p1, out_min, ntype = stats["std"], stats["mean"], 0.0, 0
     oracles = [ActRolloutOracle(C, Da, stats) for _ in range(B)]
-    ring = torch.zeros(B, C, C, ring_row_width(Da), device=cuda)      # time-major device layout
+    ring = torch.zeros(B, C, C, Da, device=cuda)
     step = torch.zeros(B, dtype=torch.int32, device=cuda)
     wtab = torch.tensor(make_weight_table(C), device=cuda)
     d_p0, d_p1 = torch.tensor(p0, device=cuda), torch.tensor(p1, device=cuda)
@@ -309,7 +309,7 @@ def test_ensemble_bit_exact(lib, cuda, norm):
             assert np.array_equal(act[b].cpu().numpy(), ref), (t, b)
             assert np.array_equal(actn[b].cpu().numpy(), oracles[b].normalized_action), (t, b)
             oring, filled = oracles[b].ring_view(n_calls[b])
-            assert np.array_equal(ring_to_slots(ring, Da)[b].cpu().numpy()[filled], oring[filled]), (t, b)
+            assert np.array_equal(ring[b].cpu().numpy()[filled], oring[filled]), (t, b)
         assert step.cpu().tolist() == n_calls
 
 
