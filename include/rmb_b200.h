@@ -172,6 +172,10 @@ int rmb_maxpool3x3s2_nhwc(const void* d_in, void* d_out, int B, int H, int W, in
 int rmb_attention(const void* d_Q, int ldq, int q_col0, int q_shared, const void* d_K, int ldk, int k_col0,
                        const void* d_V, int ldv, int v_col0, void* d_out, int ld_out, int B, int n_heads, int Lq, int Lk,
                        void* stream);
+/* Which attention kernel rmb_attention and the ACT engine launch (csrc/act_engine.cu: 1 two-sweep, 2 one-sweep with P in
+ * shared memory, 3 one-sweep with P in TMEM). variant 0 = query. Returns the variant now in force, or -1.
+ * Captured CUDA graphs keep the kernel they were captured with. */
+int rmb_set_attention_variant(int variant);
 /* LayerNorm over 512 columns: x fp32 [rows,512]; outputs optional (NULL): y fp32, y act, act(y + pos[row % L]) */
 int rmb_layernorm512(const float* d_x, const float* d_gamma, const float* d_beta, const float* d_pos, int L,
                      float* d_y_f32, void* d_y_act, void* d_ypos_act, int64_t rows, int do_norm, void* stream);

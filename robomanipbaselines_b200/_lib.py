@@ -144,6 +144,7 @@ SIGNATURES = {
     "rmb_maxpool3x3s2_nhwc": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
     "rmb_attention": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_int, c_int, c_void_p, c_int, c_int,
                                    c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p]),
+    "rmb_set_attention_variant": (c_int, [c_int]),
     "rmb_layernorm512": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p,
                                  c_int64, c_int, c_void_p]),
     "rmb_scheduler_step": (c_int, [c_void_p, c_void_p, c_void_p, POINTER(SchedStep), c_void_p, c_int64, c_void_p]),

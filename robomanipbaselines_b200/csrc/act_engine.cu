@@ -20,6 +20,7 @@
 #include "../../include/rmb_b200.h"
 #include "attention_tc.cuh"
 #include "attention_v2.cuh"
+#include "attention_v3.cuh"
 #include "elementwise.cuh"
 #include "gemm_plan.h"
 
@@ -69,20 +70,35 @@ bool plan_attention(AttnPlan* a, const void* Q, int ldq, int q_col0, bool q_shar
   return true;
 }
 
-// attention_tc_kernel (two sweeps, two CTAs per SM) is the default: 0.47 ms per encoder launch at 256 episodes.
-// RMB_ATTN_V2=1 selects attention_v2_kernel (persistent, two streams per CTA, one sweep), correct but at 0.63 ms not yet
-// faster: its softmax warps still wait on the S / P hand-offs (ncu: profiles/r02_attention_v2_ncu_full_summary.txt).
+// Attention kernel variants (same results within the 16-bit P rounding; tests run all three):
+//   1 attention_tc_kernel  two sweeps, one tile per CTA, two CTAs per SM (round 1)
+//   2 attention_v2_kernel  persistent, two streams per CTA, one sweep, P through shared memory (round 2, not faster)
+//   3 attention_v3_kernel  v2's structure with P in TMEM as the A operand of P V, S released before the arithmetic,
+//                          packed fp32x2 softmax arithmetic
+// RMB_ATTN=1|2|3 (or RMB_ATTN_V2=1) picks one at start-up; rmb_set_attention_variant() switches at run time.
+#ifndef RMB_ATTN_DEFAULT
+#define RMB_ATTN_DEFAULT 1
+#endif
 cudaError_t launch_attention_v1(const AttnPlan& a, cudaStream_t stream);
-bool attention_use_v2() {
-  static const bool v2 = [] { const char* e = getenv("RMB_ATTN_V2"); return e != nullptr && e[0] == '1'; }();
-  return v2;
+static int g_attn_variant = [] {
+  const char* e = getenv("RMB_ATTN");
+  if (e != nullptr && e[0] >= '1' && e[0] <= '3') return e[0] - '0';
+  const char* e2 = getenv("RMB_ATTN_V2");
+  if (e2 != nullptr && e2[0] == '1') return 2;
+  return RMB_ATTN_DEFAULT;
+}();
+int attention_variant() { return g_attn_variant; }
+const char* attention_kernel_name() {
+  return g_attn_variant == 3 ? "attention_v3_kernel" : g_attn_variant == 2 ? "attention_v2_kernel" : "attention_tc_kernel";
 }
 cudaError_t launch_attention(const AttnPlan& a, cudaStream_t stream) {
-  if (!attention_use_v2()) return launch_attention_v1(a, stream);
+  if (g_attn_variant == 1) return launch_attention_v1(a, stream);
   static bool attr_set = false;
   static int sms = 148;
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(attention_v2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttn2SmemBytes);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(attention_v3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttn3SmemBytes);
     if (e != cudaSuccess) return e;
     int dev = 0;
     if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
@@ -90,7 +106,9 @@ cudaError_t launch_attention(const AttnPlan& a, cudaStream_t stream) {
   }
   const int n_items = a.grid;                       // (episode, head, query tile) work items
   const int grid = std::min(sms, (n_items + 1) / 2);
-  return launch_pdl(attention_v2_kernel, dim3(grid), dim3(kAttn2Threads), kAttn2SmemBytes, stream, a.tq, a.tk, a.tv, a.p, n_items);
+  if (g_attn_variant == 2)
+    return launch_pdl(attention_v2_kernel, dim3(grid), dim3(kAttn2Threads), kAttn2SmemBytes, stream, a.tq, a.tk, a.tv, a.p, n_items);
+  return launch_pdl(attention_v3_kernel, dim3(grid), dim3(kAttn3Threads), kAttn3SmemBytes, stream, a.tq, a.tk, a.tv, a.p, n_items);
 }
 
 cudaError_t launch_attention_v1(const AttnPlan& a, cudaStream_t stream) {
@@ -903,7 +921,7 @@ static int forward_impl(rmb_act_engine_t* e, const void* d_images, int image_for
     }
     snprintf(nm, sizeof(nm), "enc%d V proj", l); RMB_RUN(run_gemm(nm, pl.v, tokb));
     snprintf(nm, sizeof(nm), "enc%d self-attention", l);
-    begin(nm, attention_use_v2() ? "attention_v2_kernel" : "attention_tc_kernel", attn_flops, attn_bytes);
+    begin(nm, attention_kernel_name(), attn_flops, attn_bytes);
     RMB_CUDA(launch_attention(pl.attn, s));
     end();
     if (bp->ln_fused) {
@@ -926,7 +944,7 @@ static int forward_impl(rmb_act_engine_t* e, const void* d_images, int image_for
   }
   RMB_RUN(run_gemm("dec0 K proj", bp->dk, tokb));
   RMB_RUN(run_gemm("dec0 V proj", bp->dv, tokb));
-  begin("dec0 cross-attention", attention_use_v2() ? "attention_v2_kernel" : "attention_tc_kernel", 4.0 * batch * (double)C * L * 512, (double)BL * 512 * 2 * 2 + (double)BC * 512 * 2);
+  begin("dec0 cross-attention", attention_kernel_name(), 4.0 * batch * (double)C * L * 512, (double)BL * 512 * 2 * 2 + (double)BC * 512 * 2);
   RMB_CUDA(launch_attention(bp->dattn, s));
   end();
   RMB_RUN(run_gemm("dec0 out proj +tgt", bp->dout, (double)BC * 512 * 2));
@@ -1143,6 +1161,13 @@ int rmb_attention(const void* d_Q, int ldq, int q_col0, int q_shared, const void
   if (!plan_attention(&a, d_Q, ldq, q_col0, q_shared != 0, d_K, ldk, k_col0, d_V, ldv, v_col0, d_out, ld_out, B, n_heads, Lq, Lk, &err)) return fail(err);
   RMB_CUDA(launch_attention(a, static_cast<cudaStream_t>(stream_)));
   return 0;
+}
+
+int rmb_set_attention_variant(int variant) {
+  if (variant == 0) return g_attn_variant;
+  if (variant < 1 || variant > 3) return fail("rmb_set_attention_variant: variant must be 1, 2 or 3 (0 = query)");
+  g_attn_variant = variant;
+  return variant;
 }
 
 int rmb_layernorm512(const float* d_x, const float* d_gamma, const float* d_beta, const float* d_pos, int L,

@@ -193,9 +193,18 @@ def test_maxpool(lib, cuda):
     assert torch.equal(out.float(), ref)
 
 
+@pytest.fixture(params=[1, 2, 3], ids=["v1", "v2", "v3"])
+def attn_variant(lib, request):
+    """Every attention kernel variant (csrc/act_engine.cu::launch_attention); restores the library default afterwards."""
+    default = lib.rmb_set_attention_variant(0)
+    assert lib.rmb_set_attention_variant(request.param) == request.param
+    yield request.param
+    lib.rmb_set_attention_variant(default)
+
+
 @pytest.mark.parametrize("B,Lq,Lk,shared", [(2, 128, 128, 0), (2, 302, 302, 0), (3, 602, 602, 0), (3, 100, 602, 1),
-                                             (1, 902, 902, 0)])
-def test_attention(lib, cuda, B, Lq, Lk, shared):
+                                             (1, 902, 902, 0), (2, 77, 45, 0), (40, 602, 602, 0)])
+def test_attention(lib, cuda, attn_variant, B, Lq, Lk, shared):
     g = torch.Generator(device="cpu").manual_seed(Lq + Lk)
     H, D = 8, 512
     qrows = Lq if shared else B * Lq
@@ -221,7 +230,7 @@ def test_attention(lib, cuda, B, Lq, Lk, shared):
 
 
 @pytest.mark.parametrize("B,Lq,Lk", [(2, 602, 602), (40, 602, 602), (3, 100, 602), (2, 130, 257), (300, 20, 602)])
-def test_attention_online_softmax_reference_point_moves(lib, cuda, B, Lq, Lk):
+def test_attention_online_softmax_reference_point_moves(lib, cuda, attn_variant, B, Lq, Lk):
     """One-sweep attention keeps a reference maximum per row and only moves it (rescaling O and the row sum in TMEM)
     when a key block exceeds it by more than 2^8. Here the logits GROW along the keys (later blocks are up to 6x larger),
     so every block forces the move; plus a flat case mix: more work items than streams (40 x 8 x 5 = 1600 items on 296
