@@ -77,7 +77,7 @@ bool plan_attention(AttnPlan* a, const void* Q, int ldq, int q_col0, bool q_shar
 //                          packed fp32x2 softmax arithmetic
 // RMB_ATTN=1|2|3 (or RMB_ATTN_V2=1) picks one at start-up; rmb_set_attention_variant() switches at run time.
 #ifndef RMB_ATTN_DEFAULT
-#define RMB_ATTN_DEFAULT 1
+#define RMB_ATTN_DEFAULT 3
 #endif
 cudaError_t launch_attention_v1(const AttnPlan& a, cudaStream_t stream);
 static int g_attn_variant = [] {
