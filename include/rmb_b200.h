@@ -318,6 +318,19 @@ int64_t rmb_pointcloud_scratch_bytes(int batch, int H, int W, int num_points);
 int rmb_pointcloud_from_depth(const float* d_depth, const uint8_t* d_rgb, const rmb_pointcloud_params_t* p, void* d_scratch,
                               float* d_out, int32_t* d_count, int32_t* d_indices, int batch, void* stream);
 
+/* rmb_pointcloud_from_depth without caller-provided scratch and WITHOUT ANY ALLOCATION (no cudaMalloc / cudaFree inside):
+ * for callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid it). This entry point
+ * has no counterpart in the reference. The scratch is a file-scope
+ * static __device__ array of RMB_POINTCLOUD_STATIC_SCRATCH_BYTES (32 MiB) that every GPU loading the library holds until
+ * exit; batch * H * W * 56 + batch * num_points * 4 bytes must fit (e.g. 84 clouds of 84 x 84, one of 480 x 640), larger
+ * requests return -1 with a message in rmb_last_error(). Same arguments, kernel and bit-exact results as
+ * rmb_pointcloud_from_depth. All calls share the one array, which keeps the last call's contents (the kernel
+ * re-initialises everything it reads, nothing needs clearing): calls that OVERLAP on the GPU (two streams, parallel
+ * graph branches) race -- serialise them on one stream. */
+#define RMB_POINTCLOUD_STATIC_SCRATCH_BYTES (32ll << 20)
+int rmb_pointcloud_from_depth_static(const float* d_depth, const uint8_t* d_rgb, const rmb_pointcloud_params_t* p,
+                                     float* d_out, int32_t* d_count, int32_t* d_indices, int batch, void* stream);
+
 /* ---- cv2.resize(img, (W2, H2)) with INTER_LINEAR on the device (RolloutDiffusionPolicy.py:117,
  * RolloutDiffusionPolicy3d.py:134-137). uint8: OpenCV's fixed-point path, bit-exact for the reference's down-scaling;
  * out_mode 0 = uint8 HWC [n, H2, W2, 3]; out_mode 1 = float32 CHW [n, 3, H2, W2] = (v * (1/255)) * scale + offset

@@ -177,6 +177,8 @@ SIGNATURES = {
     "rmb_pointcloud_scratch_bytes": (c_int64, [c_int, c_int, c_int, c_int]),
     "rmb_pointcloud_from_depth": (c_int, [c_void_p, c_void_p, POINTER(PointcloudParams), c_void_p, c_void_p, c_void_p,
                                           c_void_p, c_int, c_void_p]),
+    "rmb_pointcloud_from_depth_static": (c_int, [c_void_p, c_void_p, POINTER(PointcloudParams), c_void_p, c_void_p, c_void_p,
+                                                 c_int, c_void_p]),
     "rmb_arm_command": (c_int, [POINTER(ArmModel), POINTER(ArmLayout), c_int, c_void_p, c_int, c_int, c_void_p, c_void_p,
                                 c_void_p, c_void_p, c_int, c_void_p]),
     "rmb_arm_get_command": (c_int, [POINTER(ArmModel), POINTER(ArmLayout), c_void_p, c_void_p, c_void_p, c_void_p, c_int,

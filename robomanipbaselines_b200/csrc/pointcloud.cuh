@@ -9,6 +9,8 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <mutex>
+#include <string>
 
 namespace rmb {
 
@@ -161,6 +163,65 @@ int rmb_pointcloud_from_depth(const float* d_depth, const uint8_t* d_rgb, const 
   p.norm_type = prm->norm_type; p.out_min = prm->norm_out_min;
   for (int i = 0; i < 6; ++i) { p.p0[i] = prm->norm_p0[i]; p.p1[i] = prm->norm_p1[i]; }
   double* scratch = static_cast<double*>(d_scratch);
+  int* idx = d_indices ? d_indices : reinterpret_cast<int*>(scratch + static_cast<long long>(batch) * p.H * p.W * 7);
+  rmb::pointcloud_from_depth_kernel<<<batch, rmb::kPcThreads, 0, static_cast<cudaStream_t>(stream_)>>>(d_depth, d_rgb, p, scratch, d_out, d_count, idx);
+  RMB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+
+// ---- rmb_pointcloud_from_depth_static: the same kernel with its scratch in a file-scope device array, for callers that
+// cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it). No counterpart in the
+// reference. The entry point allocates nothing (no cudaMalloc / cudaFree /
+// allocating library routine). Every GPU that loads the library holds the array (32 MiB) until exit.
+// Every call shares the array and it keeps the last call's contents: the kernel itself (re)initialises whatever it reads
+// (compacted points are written before they are read, the FPS distances are set to +inf, the index list is rewritten), so
+// nothing has to start at zero -- but two calls that overlap on the GPU (different streams, or graph branches) RACE.
+#define RMB_PC_STATIC_SCRATCH_BYTES (32ll << 20)
+static __device__ __align__(256) unsigned char g_pc_static_scratch[RMB_PC_STATIC_SCRATCH_BYTES];
+
+// In host code `g_pc_static_scratch` is a host-side stand-in, not a device address: the device address comes from
+// cudaGetSymbolAddress, once per device, with that device current.
+static int pc_static_scratch_ptr(void** out) {
+  constexpr int kMaxDevices = 64;
+  static void* ptrs[kMaxDevices] = {};
+  static std::mutex mu;
+  int dev = 0;
+  RMB_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) return fail("rmb_pointcloud_from_depth_static: device ordinal out of range");
+  std::lock_guard<std::mutex> lock(mu);
+  if (ptrs[dev] == nullptr) {
+    void* ptr = nullptr;
+    RMB_CUDA(cudaGetSymbolAddress(&ptr, g_pc_static_scratch));
+    if (ptr == nullptr) return fail("rmb_pointcloud_from_depth_static: cudaGetSymbolAddress returned a null address");
+    ptrs[dev] = ptr;
+  }
+  *out = ptrs[dev];
+  return 0;
+}
+
+int rmb_pointcloud_from_depth_static(const float* d_depth, const uint8_t* d_rgb, const rmb_pointcloud_params_t* prm,
+                                     float* d_out, int32_t* d_count, int32_t* d_indices, int batch, void* stream_) {
+  if (!d_depth || !d_rgb || !prm || !d_out) return fail("rmb_pointcloud_from_depth_static: null argument");
+  if (batch < 1 || prm->H < 1 || prm->W < 1 || prm->num_points < 1) return fail("rmb_pointcloud_from_depth_static: bad sizes");
+  if (prm->norm_type < -1 || prm->norm_type > 1) return fail("rmb_pointcloud_from_depth_static: norm_type must be -1, 0 or 1");
+  if (!(prm->focal_scaling > 0.0)) return fail("rmb_pointcloud_from_depth_static: focal_scaling must be positive");
+  const long long need = static_cast<long long>(batch) * prm->H * prm->W * 7 * static_cast<long long>(sizeof(double)) +
+                         static_cast<long long>(batch) * prm->num_points * static_cast<long long>(sizeof(int));
+  if (need > RMB_PC_STATIC_SCRATCH_BYTES)
+    return fail("rmb_pointcloud_from_depth_static: batch * H * W * 56 + batch * num_points * 4 = " + std::to_string(need) +
+                " bytes of scratch exceed the static maximum of " + std::to_string(RMB_PC_STATIC_SCRATCH_BYTES) +
+                " bytes (use rmb_pointcloud_from_depth with caller-provided scratch)");
+  void* scratch_v = nullptr;
+  if (int r = pc_static_scratch_ptr(&scratch_v)) return r;
+  rmb::PcParams p;
+  p.H = prm->H; p.W = prm->W; p.K = prm->num_points;
+  p.focal = prm->focal_scaling; p.near_clip = prm->near_clip; p.far_clip = prm->far_clip;
+  p.has_min = prm->has_min_bound; p.has_max = prm->has_max_bound;
+  for (int i = 0; i < 3; ++i) { p.mn[i] = prm->min_bound[i]; p.mx[i] = prm->max_bound[i]; }
+  p.norm_type = prm->norm_type; p.out_min = prm->norm_out_min;
+  for (int i = 0; i < 6; ++i) { p.p0[i] = prm->norm_p0[i]; p.p1[i] = prm->norm_p1[i]; }
+  double* scratch = static_cast<double*>(scratch_v);
   int* idx = d_indices ? d_indices : reinterpret_cast<int*>(scratch + static_cast<long long>(batch) * p.H * p.W * 7);
   rmb::pointcloud_from_depth_kernel<<<batch, rmb::kPcThreads, 0, static_cast<cudaStream_t>(stream_)>>>(d_depth, d_rgb, p, scratch, d_out, d_count, idx);
   RMB_CUDA(cudaGetLastError());
