@@ -498,9 +498,11 @@ def roofline_block(recs_runs, ms_per_step, peaks, batch):
             "profile_sum_ms": prof_ms, "step_stretch": stretch,
             "kernels": {k: entry(k, v) for k, v in by_kernel.items()}}
     # DRAM bytes per launch: from the committed ncu capture of this same command at this commit's kernels (bench.py
-    # never runs a profiler itself): profiles/r02_dram_traffic.json, written by scripts/ncu_traffic.py
-    tpath = os.path.join(ROOT, "profiles", "r02_dram_traffic.json")
-    if batch == 256 and os.path.exists(tpath):
+    # never runs a profiler itself): the newest profiles/r02*_dram_traffic.json, written by scripts/ncu_traffic.py
+    import glob
+    tpaths = sorted(glob.glob(os.path.join(ROOT, "profiles", "r02*_dram_traffic.json")))
+    tpath = tpaths[-1] if tpaths else ""
+    if batch == 256 and tpath:
         with open(tpath) as f:
             tj = json.load(f)
         for k, v in tj.get("kernels", {}).items():
@@ -509,7 +511,7 @@ def roofline_block(recs_runs, ms_per_step, peaks, batch):
         if dom in tj.get("kernels", {}) and "traffic" in roof["kernels"][dom]:
             roof["traffic"] = roof["kernels"][dom]["traffic"]
             roof["traffic_unit"] = "bytes/launch (dram__bytes_read.sum + dram__bytes_write.sum)"
-            roof["traffic_source"] = "profiles/r02_dram_traffic.json (" + tj.get("commit", "?") + ")"
+            roof["traffic_source"] = "profiles/" + os.path.basename(tpath) + " (" + tj.get("commit", "?") + ")"
     return roof
 
 
