@@ -15,6 +15,19 @@
 namespace rmb {
 
 constexpr int kPcThreads = 512;
+constexpr int kPcPpt = 14;                            // points per thread whose FPS state lives in registers
+constexpr int kPcGroup = 2;                           // points of a thread swept together (instruction-level parallelism)
+constexpr int kPcCap = kPcThreads * kPcPpt;           // clouds of up to 7168 kept points run the resident FPS loop
+// dynamic shared memory of the resident path: (x, y) double2 [cap] | z float [cap] | rgb packed u32 [cap] | u8/255 table
+constexpr int kPcSmemBytes = kPcCap * 24 + 256 * 4;
+
+// float -> double inside the sweep: volatile so that ptxas does not hoist the conversions of the register-resident
+// colours out of the loop (it then keeps them as doubles and spills)
+__device__ __forceinline__ double pc_widen(float f) {
+  double d;
+  asm volatile("cvt.f64.f32 %0, %1;" : "=d"(d) : "f"(f));
+  return d;
+}
 
 struct PcParams {
   int H, W, K;
@@ -26,33 +39,46 @@ struct PcParams {
 };
 
 // scratch per cloud: pts [HW][6] double, mind [HW] double
-__global__ void __launch_bounds__(kPcThreads) pointcloud_from_depth_kernel(const float* __restrict__ depth,
-                                                                           const uint8_t* __restrict__ rgb,
-                                                                           const PcParams p, double* __restrict__ scratch,
-                                                                           float* __restrict__ out, int* __restrict__ count,
-                                                                           int* __restrict__ indices) {
-  __shared__ int warp_cnt[kPcThreads / 32];
-  __shared__ int s_base, s_sel;
-  __shared__ double red_v[kPcThreads / 32];
-  __shared__ int red_i[kPcThreads / 32];
+// Farthest point sampling is 1023 dependent sweeps over the kept points. Round 2: a cloud of up to kPcCap points (the
+// DP3 input is 84 x 84 = 7056 pixels) is swept from ON-CHIP state -- coordinates in shared memory (x, y as doubles; z and
+// the colours are float32-valued, so they are kept as floats and widened, which is exact), the running minimum distance
+// and the point's colour in registers (thread t owns points t, t + 512, ...: the same assignment and so the same
+// first-maximum tie-break as the sweep over global memory), one __syncthreads per sweep (double-buffered partial
+// maxima, every warp finishes the reduction itself). Same fp64 operations in the same order => same indices bit for
+// bit; larger clouds take the sweep over the scratch buffer.
+__global__ void __launch_bounds__(kPcThreads, 1) pointcloud_from_depth_kernel(const float* __restrict__ depth,
+                                                                              const uint8_t* __restrict__ rgb,
+                                                                              const PcParams p, double* __restrict__ scratch,
+                                                                              float* __restrict__ out, int* __restrict__ count,
+                                                                              int* __restrict__ indices) {
+  extern __shared__ __align__(16) uint8_t pc_smem[];
+  double2* s_xy = reinterpret_cast<double2*>(pc_smem);
+  float* s_z = reinterpret_cast<float*>(pc_smem + kPcCap * 16);
+  uint32_t* s_rgb = reinterpret_cast<uint32_t*>(pc_smem + kPcCap * 20);
+  float* s_lut = reinterpret_cast<float*>(pc_smem + kPcCap * 24);
+  __shared__ int warp_cnt[2][kPcThreads / 32];
+  __shared__ double red_v[2][kPcThreads / 32];
+  __shared__ int red_i[2][kPcThreads / 32];
+  __shared__ int s_sel;
   __shared__ double sel_pt[6];
   const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int HW = p.H * p.W;
   double* pts = scratch + static_cast<long long>(b) * HW * 7;
-  double* mind = pts + static_cast<long long>(HW) * 6;
+  double* mind_g = pts + static_cast<long long>(HW) * 6;
   const float* dep = depth + static_cast<long long>(b) * HW;
   const uint8_t* col = rgb + static_cast<long long>(b) * HW * 3;
-  if (tid == 0) s_base = 0;
-  __syncthreads();
-  // ---- back-projection + clip + bounding box, stable compaction in pixel order
+  if (tid < 256) s_lut[tid] = __fdiv_rn(static_cast<float>(tid), 255.0f);
+  // ---- back-projection + clip + bounding box, stable compaction in pixel order (one barrier per 512 pixels)
   const float half_h = 0.5f * static_cast<float>(p.H), half_w = 0.5f * static_cast<float>(p.W);
-  for (int start = 0; start < HW; start += kPcThreads) {
+  int base = 0;                                     // kept points so far (the same value in every thread)
+  for (int start = 0, r = 0; start < HW; start += kPcThreads, r ^= 1) {
     const int pix = start + tid;
     bool keep = false;
     double x = 0, y = 0, z = 0;
+    float dz = 0.f;
     if (pix < HW) {
       const int i = pix / p.W, j = pix - i * p.W;
-      const float dz = dep[pix];
+      dz = dep[pix];
       z = static_cast<double>(dz);
       // ((float(j) - 0.5*W) / focal) * depth : float32 grid, float64 from the division on (VisionUtils.py:60-71)
       x = __dmul_rn(__ddiv_rn(static_cast<double>(static_cast<float>(j) - half_w), p.focal), z);
@@ -62,66 +88,155 @@ __global__ void __launch_bounds__(kPcThreads) pointcloud_from_depth_kernel(const
       if (p.has_max) keep = keep && x < p.mx[0] && y < p.mx[1] && z < p.mx[2];
     }
     const unsigned bal = __ballot_sync(0xffffffffu, keep);
-    if (lane == 0) warp_cnt[warp] = __popc(bal);
+    if (lane == 0) warp_cnt[r][warp] = __popc(bal);
     __syncthreads();
-    int off = s_base;
-    for (int w2 = 0; w2 < warp; ++w2) off += warp_cnt[w2];
+    int off = base, tot = 0;
+#pragma unroll
+    for (int w2 = 0; w2 < kPcThreads / 32; ++w2) {
+      const int c = warp_cnt[r][w2];
+      if (w2 < warp) off += c;
+      tot += c;
+    }
+    base += tot;
     if (keep) {
-      double* q = pts + static_cast<long long>(off + __popc(bal & ((1u << lane) - 1u))) * 6;
+      const int at = off + __popc(bal & ((1u << lane) - 1u));
+      const uint32_t c0 = col[pix * 3 + 0], c1 = col[pix * 3 + 1], c2 = col[pix * 3 + 2];
+      double* q = pts + static_cast<long long>(at) * 6;
       q[0] = x; q[1] = y; q[2] = z;
-      q[3] = static_cast<double>(__fdiv_rn(static_cast<float>(col[pix * 3 + 0]), 255.0f));
-      q[4] = static_cast<double>(__fdiv_rn(static_cast<float>(col[pix * 3 + 1]), 255.0f));
-      q[5] = static_cast<double>(__fdiv_rn(static_cast<float>(col[pix * 3 + 2]), 255.0f));
+      q[3] = static_cast<double>(__fdiv_rn(static_cast<float>(c0), 255.0f));
+      q[4] = static_cast<double>(__fdiv_rn(static_cast<float>(c1), 255.0f));
+      q[5] = static_cast<double>(__fdiv_rn(static_cast<float>(c2), 255.0f));
+      if (at < kPcCap) {
+        s_xy[at] = make_double2(x, y);
+        s_z[at] = dz;
+        s_rgb[at] = c0 | (c1 << 8) | (c2 << 16);
+      }
     }
-    __syncthreads();
-    if (tid == 0) {
-      int tot = 0;
-      for (int w2 = 0; w2 < kPcThreads / 32; ++w2) tot += warp_cnt[w2];
-      s_base += tot;
-    }
-    __syncthreads();
   }
-  const int N = s_base;
+  const int N = base;
   if (tid == 0 && count != nullptr) count[b] = N;
   int* idx_out = indices + static_cast<long long>(b) * p.K;
-  // ---- farthest point sampling on the 6-D points (the reference passes xyz and rgb columns)
-  for (int i = tid; i < N; i += kPcThreads) mind[i] = INFINITY;
   for (int k = tid; k < p.K; k += kPcThreads) idx_out[k] = (k == 0 && N > 0) ? 0 : -1;
-  if (tid == 0) s_sel = 0;
-  __syncthreads();
   const int kmax = p.K < N ? p.K : N;
-  for (int k = 1; k < kmax; ++k) {
-    if (tid < 6) sel_pt[tid] = pts[static_cast<long long>(s_sel) * 6 + tid];
-    __syncthreads();
-    double best = -1.0; int best_i = 0x7fffffff;
-    for (int i = tid; i < N; i += kPcThreads) {
-      const double* q = pts + static_cast<long long>(i) * 6;
-      double d2 = 0.0;
+  __syncthreads();
+  // ---- farthest point sampling on the 6-D points (the reference passes xyz and rgb columns)
+  if (N <= kPcCap) {
+    // Points past N never win: their running minimum starts at -inf and fmin keeps it there whatever the (stale)
+    // shared-memory contents are, so the sweep needs no per-point branch and the chains of different points interleave.
+    double mind[kPcPpt];
+    float cr[kPcPpt], cg[kPcPpt], cb[kPcPpt];
+    const int jmax = (N + kPcThreads - 1) / kPcThreads;
 #pragma unroll
-      for (int d = 0; d < 6; ++d) {
-        const double df = __dsub_rn(q[d], sel_pt[d]);
-        d2 = __dadd_rn(d2, __dmul_rn(df, df));
+    for (int j = 0; j < kPcPpt; ++j) {
+      const int i = j * kPcThreads + tid;
+      mind[j] = (i < N) ? INFINITY : -INFINITY;
+      cr[j] = cg[j] = cb[j] = 0.f;
+      if (i < N) {
+        const uint32_t u = s_rgb[i];
+        cr[j] = s_lut[u & 255u]; cg[j] = s_lut[(u >> 8) & 255u]; cb[j] = s_lut[(u >> 16) & 255u];
+      } else {
+        s_xy[i] = make_double2(0.0, 0.0);
+        s_z[i] = 0.f;
       }
-      const double m = fmin(mind[i], d2);
-      mind[i] = m;
-      if (m > best) { best = m; best_i = i; }              // ascending i per thread: strict > keeps the first
     }
+    __syncthreads();
+    int sel = 0, par = 0;
+    for (int k = 1; k < kmax; ++k, par ^= 1) {
+      const double2 sxy = s_xy[sel];
+      const double sz = static_cast<double>(s_z[sel]);
+      const uint32_t su = s_rgb[sel];
+      const double sr = static_cast<double>(s_lut[su & 255u]), sg = static_cast<double>(s_lut[(su >> 8) & 255u]),
+                   sb = static_cast<double>(s_lut[(su >> 16) & 255u]);
+      // two (value, index) accumulators (even / odd j), each over ascending indices with a strict >, merged with the
+      // full rule (larger value, then smaller index) = the first maximum of the thread's points
+      double best = -1.0, best1 = -1.0; int best_i = 0x7fffffff, best1_i = 0x7fffffff;
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      const double ov = __shfl_xor_sync(0xffffffffu, best, o);
-      const int oi = __shfl_xor_sync(0xffffffffu, best_i, o);
-      if (ov > best || (ov == best && oi < best_i)) { best = ov; best_i = oi; }
+      for (int j = 0; j < kPcPpt; j += kPcGroup) {
+        if (j < jmax) {                                       // block-uniform; a group of points per branch
+          constexpr int kW = kPcGroup;
+          double m2[kW];
+#pragma unroll
+          for (int u = 0; u < kW; ++u) {
+            if (j + u < kPcPpt) {
+              const int i = (j + u) * kPcThreads + tid;
+              const double2 q = s_xy[i];
+              double df = __dsub_rn(q.x, sxy.x);
+              double d2 = __dmul_rn(df, df);                      // 0.0 + v == v for v >= +0
+              df = __dsub_rn(q.y, sxy.y);                          d2 = __dadd_rn(d2, __dmul_rn(df, df));
+              df = __dsub_rn(static_cast<double>(s_z[i]), sz);    d2 = __dadd_rn(d2, __dmul_rn(df, df));
+              df = __dsub_rn(pc_widen(cr[j + u]), sr);             d2 = __dadd_rn(d2, __dmul_rn(df, df));
+              df = __dsub_rn(pc_widen(cg[j + u]), sg);             d2 = __dadd_rn(d2, __dmul_rn(df, df));
+              df = __dsub_rn(pc_widen(cb[j + u]), sb);             d2 = __dadd_rn(d2, __dmul_rn(df, df));
+              m2[u] = fmin(mind[j + u], d2);
+              mind[j + u] = m2[u];
+            }
+          }
+#pragma unroll
+          for (int u = 0; u < kW; u += 2) {
+            if (j + u < kPcPpt) {
+              if (m2[u] > best) { best = m2[u]; best_i = (j + u) * kPcThreads + tid; }
+              if (m2[u + 1] > best1) { best1 = m2[u + 1]; best1_i = (j + u + 1) * kPcThreads + tid; }
+            }
+          }
+        }
+      }
+      if (best1 > best || (best1 == best && best1_i < best_i)) { best = best1; best_i = best1_i; }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        const double ov = __shfl_xor_sync(0xffffffffu, best, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, best_i, o);
+        if (ov > best || (ov == best && oi < best_i)) { best = ov; best_i = oi; }
+      }
+      if (lane == 0) { red_v[par][warp] = best; red_i[par][warp] = best_i; }
+      __syncthreads();
+      best = (lane < kPcThreads / 32) ? red_v[par][lane] : -2.0;
+      best_i = (lane < kPcThreads / 32) ? red_i[par][lane] : 0x7fffffff;
+#pragma unroll
+      for (int o = 8; o > 0; o >>= 1) {
+        const double ov = __shfl_xor_sync(0xffffffffu, best, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, best_i, o);
+        if (ov > best || (ov == best && oi < best_i)) { best = ov; best_i = oi; }
+      }
+      sel = __shfl_sync(0xffffffffu, best_i, 0);
+      if (tid == 0) idx_out[k] = sel;
     }
-    if (lane == 0) { red_v[warp] = best; red_i[warp] = best_i; }
+  } else {
+    for (int i = tid; i < N; i += kPcThreads) mind_g[i] = INFINITY;
+    if (tid == 0) s_sel = 0;
     __syncthreads();
-    if (tid == 0) {
-      double bv = red_v[0]; int bi = red_i[0];
-      for (int w2 = 1; w2 < kPcThreads / 32; ++w2)
-        if (red_v[w2] > bv || (red_v[w2] == bv && red_i[w2] < bi)) { bv = red_v[w2]; bi = red_i[w2]; }
-      s_sel = bi;
-      idx_out[k] = bi;
+    for (int k = 1; k < kmax; ++k) {
+      if (tid < 6) sel_pt[tid] = pts[static_cast<long long>(s_sel) * 6 + tid];
+      __syncthreads();
+      double best = -1.0; int best_i = 0x7fffffff;
+      for (int i = tid; i < N; i += kPcThreads) {
+        const double* q = pts + static_cast<long long>(i) * 6;
+        double d2 = 0.0;
+#pragma unroll
+        for (int d = 0; d < 6; ++d) {
+          const double df = __dsub_rn(q[d], sel_pt[d]);
+          d2 = __dadd_rn(d2, __dmul_rn(df, df));
+        }
+        const double m = fmin(mind_g[i], d2);
+        mind_g[i] = m;
+        if (m > best) { best = m; best_i = i; }              // ascending i per thread: strict > keeps the first
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        const double ov = __shfl_xor_sync(0xffffffffu, best, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, best_i, o);
+        if (ov > best || (ov == best && oi < best_i)) { best = ov; best_i = oi; }
+      }
+      if (lane == 0) { red_v[0][warp] = best; red_i[0][warp] = best_i; }
+      __syncthreads();
+      if (tid == 0) {
+        double bv = red_v[0][0]; int bi = red_i[0][0];
+        for (int w2 = 1; w2 < kPcThreads / 32; ++w2)
+          if (red_v[0][w2] > bv || (red_v[0][w2] == bv && red_i[0][w2] < bi)) { bv = red_v[0][w2]; bi = red_i[0][w2]; }
+        s_sel = bi;
+        idx_out[k] = bi;
+      }
+      __syncthreads();
     }
-    __syncthreads();
   }
   __syncthreads();
   // ---- gather (-1 picks the last point, as numpy indexing does), normalise in fp64, cast to float32
@@ -141,6 +256,28 @@ __global__ void __launch_bounds__(kPcThreads) pointcloud_from_depth_kernel(const
 }
 
 }  // namespace rmb
+
+// one launch path for both entry points; the dynamic shared-memory opt-in is set once per device (it allocates nothing)
+static int pc_launch(const float* d_depth, const uint8_t* d_rgb, const rmb::PcParams& p, double* scratch, float* d_out,
+                     int32_t* d_count, int* idx, int batch, void* stream_) {
+  constexpr int kMaxDevices = 64;
+  static bool attr_set[kMaxDevices] = {};
+  static std::mutex mu;
+  int dev = 0;
+  RMB_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) return fail("rmb_pointcloud_from_depth: device ordinal out of range");
+  {
+    std::lock_guard<std::mutex> lock(mu);
+    if (!attr_set[dev]) {
+      RMB_CUDA(cudaFuncSetAttribute(rmb::pointcloud_from_depth_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, rmb::kPcSmemBytes));
+      attr_set[dev] = true;
+    }
+  }
+  rmb::pointcloud_from_depth_kernel<<<batch, rmb::kPcThreads, rmb::kPcSmemBytes, static_cast<cudaStream_t>(stream_)>>>(
+      d_depth, d_rgb, p, scratch, d_out, d_count, idx);
+  RMB_CUDA(cudaGetLastError());
+  return 0;
+}
 
 extern "C" {
 
@@ -164,9 +301,7 @@ int rmb_pointcloud_from_depth(const float* d_depth, const uint8_t* d_rgb, const 
   for (int i = 0; i < 6; ++i) { p.p0[i] = prm->norm_p0[i]; p.p1[i] = prm->norm_p1[i]; }
   double* scratch = static_cast<double*>(d_scratch);
   int* idx = d_indices ? d_indices : reinterpret_cast<int*>(scratch + static_cast<long long>(batch) * p.H * p.W * 7);
-  rmb::pointcloud_from_depth_kernel<<<batch, rmb::kPcThreads, 0, static_cast<cudaStream_t>(stream_)>>>(d_depth, d_rgb, p, scratch, d_out, d_count, idx);
-  RMB_CUDA(cudaGetLastError());
-  return 0;
+  return pc_launch(d_depth, d_rgb, p, scratch, d_out, d_count, idx, batch, stream_);
 }
 
 
@@ -223,9 +358,7 @@ int rmb_pointcloud_from_depth_static(const float* d_depth, const uint8_t* d_rgb,
   for (int i = 0; i < 6; ++i) { p.p0[i] = prm->norm_p0[i]; p.p1[i] = prm->norm_p1[i]; }
   double* scratch = static_cast<double*>(scratch_v);
   int* idx = d_indices ? d_indices : reinterpret_cast<int*>(scratch + static_cast<long long>(batch) * p.H * p.W * 7);
-  rmb::pointcloud_from_depth_kernel<<<batch, rmb::kPcThreads, 0, static_cast<cudaStream_t>(stream_)>>>(d_depth, d_rgb, p, scratch, d_out, d_count, idx);
-  RMB_CUDA(cudaGetLastError());
-  return 0;
+  return pc_launch(d_depth, d_rgb, p, scratch, d_out, d_count, idx, batch, stream_);
 }
 
 }  // extern "C"

@@ -40,6 +40,27 @@ def test_pointcloud_pipeline_bit_exact(cuda, name, K, norm):
     print(f"[pointcloud {name} K={K} norm={norm}] valid points {cnt.tolist()}, output bit-exact")
 
 
+def test_pointcloud_large_cloud_takes_the_global_memory_sweep(cuda):
+    """More kept points than the resident FPS loop holds on chip (7168): the sweep over the scratch buffer, and a cloud
+    just under the limit beside it in the same launch; both bit-exact against the oracle."""
+    from robomanipbaselines_b200.common.pointcloud import DepthToPointcloud
+
+    K = 48
+    big = dict(H=96, W=128, fovy=50.0, seed=77, min_bound=[-5.0, -5.0, 0.1], max_bound=[5.0, 5.0, 5.0], holes=False)
+    depth, rgb = pointcloud_inputs(big, batch=2)
+    depth[1, 55:] = 0.0                                        # frame 1: 55 x 128 = 7040 valid pixels (resident path)
+    pipe = DepthToPointcloud(2, (big["W"], big["H"]), big["fovy"], K, big["min_bound"], big["max_bound"], None, device=str(cuda))
+    got = pipe(torch.from_numpy(depth).to(cuda), torch.from_numpy(rgb).to(cuda)).cpu().numpy()
+    cnt, idx = pipe.count.cpu().numpy(), pipe.indices.cpu().numpy()
+    assert cnt.tolist() == [96 * 128, 55 * 128]
+    for b in range(2):
+        pc = np.concat(po.convert_depth_image_to_pointcloud(depth[b], big["fovy"], rgb[b]), axis=1)
+        pc = po.crop_pointcloud_bb(pc, big["min_bound"], big["max_bound"])
+        assert np.array_equal(idx[b], po.farthest_point_sampling(pc, K)), b
+        want, _ = po.get_pointcloud(depth[b], rgb[b], big["fovy"], big["min_bound"], big["max_bound"], K, None)
+        assert np.array_equal(got[b], want), b
+
+
 def test_pointcloud_matches_reference_golden_directly(cuda):
     """The first frame of each case is the very input the reference functions were run on: device output rows must be
     rows of the stored reference crop (float64 -> float32)."""
