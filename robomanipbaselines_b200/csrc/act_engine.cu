@@ -188,6 +188,15 @@ struct rmb_act_engine {
   // 256 episodes, same box): one TMEM accumulator serialises the MMAs with the first epilogue phase and the epilogue is
   // memory-latency bound (ncu: profiles/r02_gemm_ln_out_proj_ncu_full_summary.txt), so it is opt-in.
   int fuse_ln = 0;              // 0 never, 1 auto, 2 always
+  // Residual operand of the encoder's two residual GEMMs: the 16-bit copy of the LayerNorm output (the very tensor the
+  // next GEMMs read as their A operand) instead of a separate fp32 copy. The LayerNorm kernels then write no fp32 output
+  // (6 -> 4 / 5 -> 3 KB per token) and the out-projection reads 1 KB less per token; the pre-norm sums stay fp32. Default
+  // in the fp16 build (one more 2^-11 rounding per sublayer); the bf16 build keeps the fp32 copy. RMB_RES_F32=1 / 0 overrides.
+#ifdef RMB_ACT_BF16
+  bool res16 = false;
+#else
+  bool res16 = true;
+#endif
   bool fuse_stem_pool = true;   // RMB_NO_STEM_POOL=1: stem and max-pool as two kernels through a [img, H/2, W/2, 64] buffer
   struct BatchPlans {
     HaloPlan stem;
@@ -327,6 +336,7 @@ int rmb_act_engine_create(const rmb_act_config_t* cfg, rmb_act_engine_t** out) {
   e->num_sms = prop.multiProcessorCount;
   { const char* ev = getenv("RMB_NO_STEM_POOL"); e->fuse_stem_pool = !(ev != nullptr && ev[0] == '1'); }
   { const char* ev = getenv("RMB_LN_FUSE"); e->fuse_ln = (ev == nullptr) ? 0 : (ev[0] == 'n' ? 0 : (ev[0] == 'a' && ev[1] == 'l') ? 2 : 1); }
+  { const char* ev = getenv("RMB_RES_F32"); if (ev != nullptr && (ev[0] == '0' || ev[0] == '1')) e->res16 = (ev[0] == '0'); }
   e->Hf = cfg->img_h / 32; e->Wf = cfg->img_w / 32;
   e->n_prefix = 2 + (cfg->task_token ? 1 : 0);
   e->L = e->n_prefix + e->Hf * e->Wf * cfg->num_cams;
@@ -632,9 +642,11 @@ static int build_plans(rmb_act_engine* e, int nb, rmb_act_engine::BatchPlans** o
     if (!plan_linear(&pl.qk, e->tok_pb, BL, D, D, w.w_qk, 2 * D, w.b_qk, nullptr, 0, false, e->qk, 2 * D, false, false, &err)) return fail(err);
     if (!plan_linear(&pl.v, e->tok_b, BL, D, D, w.w_v, D, w.b_v, nullptr, 0, false, e->v, D, false, false, &err)) return fail(err);
     if (!plan_attention(&pl.attn, e->qk, 2 * D, 0, false, e->qk, 2 * D, D, e->v, D, 0, e->ao, D, nb, c.nheads, L, L, &err)) return fail(err);
-    if (!plan_linear(&pl.o, e->ao, BL, D, D, w.w_o, D, w.b_o, e->tok_f32, D, true, e->y_f32, D, true, false, &err)) return fail(err);
+    const bool r16 = e->res16 && !bp->ln_fused;
+    // r16: residual = the 16-bit LayerNorm output, pre-norm sum y written in 16 bits into the same (fp32-sized) buffer
+    if (!plan_linear(&pl.o, e->ao, BL, D, D, w.w_o, D, w.b_o, r16 ? (const void*)e->tok_b : (const void*)e->tok_f32, D, !r16, e->y_f32, D, !r16, false, &err)) return fail(err);
     if (!plan_linear(&pl.ff1, e->x1_b, BL, D, D, w.w_1, FF, w.b_1, nullptr, 0, false, e->hh, FF, false, true, &err)) return fail(err);
-    if (!plan_linear(&pl.ff2, e->hh, BL, FF, FF, w.w_2, D, w.b_2, e->x1_f32, D, true, e->y_f32, D, true, false, &err)) return fail(err);
+    if (!plan_linear(&pl.ff2, e->hh, BL, FF, FF, w.w_2, D, w.b_2, r16 ? (const void*)e->x1_b : (const void*)e->x1_f32, D, !r16, e->y_f32, D, !r16, false, &err)) return fail(err);
   }
   auto& d = e->dec;
   if (!plan_linear(&bp->dk, e->tok_pb, BL, D, D, d.w_k, D, d.b_k, nullptr, 0, false, e->kd, D, false, false, &err)) return fail(err);
@@ -932,14 +944,18 @@ static int forward_impl(rmb_act_engine_t* e, const void* d_images, int image_for
     }
     snprintf(nm, sizeof(nm), "enc%d out proj +res", l); RMB_RUN(run_gemm(nm, pl.o, tokb));   // y = ao Wo^T + bo + x
     snprintf(nm, sizeof(nm), "enc%d norm1", l);
-    begin(nm, "layernorm512_kernel", 0, (double)BL * 512 * (4 + 4 + 2));
-    RMB_CUDA(launch_pdl(layernorm512_kernel, dim3(ln_grid), dim3(256), 0, s, e->y_f32, w.g1, w.be1, nullptr, L, e->x1_f32, e->x1_b, nullptr, BL, 1, 1e-5f));
+    begin(nm, "layernorm512_kernel", 0, (double)BL * 512 * (e->res16 ? 2 + 2 : 4 + 4 + 2));
+    if (e->res16) RMB_CUDA(launch_pdl(layernorm512_kernel_t<act_t>, dim3(ln_grid), dim3(256), 0, s, (const act_t*)e->y_f32, w.g1, w.be1, nullptr, L, (float*)nullptr, e->x1_b, nullptr, BL, 1, 1e-5f));
+    else RMB_CUDA(launch_pdl(layernorm512_kernel, dim3(ln_grid), dim3(256), 0, s, e->y_f32, w.g1, w.be1, nullptr, L, e->x1_f32, e->x1_b, nullptr, BL, 1, 1e-5f));
     end();
     snprintf(nm, sizeof(nm), "enc%d linear1+relu", l); RMB_RUN(run_gemm(nm, pl.ff1, tokb));
     snprintf(nm, sizeof(nm), "enc%d linear2 +res", l); RMB_RUN(run_gemm(nm, pl.ff2, (double)BL * FF * 2));   // y = relu(.) W2^T + b2 + x1
     snprintf(nm, sizeof(nm), "enc%d norm2", l);
-    begin(nm, "layernorm512_kernel", 0, (double)BL * 512 * (4 + 4 + 2 + 2));
-    RMB_CUDA(launch_pdl(layernorm512_kernel, dim3(ln_grid), dim3(256), 0, s, e->y_f32, w.g2, w.be2, e->pos, L, e->tok_f32, e->tok_b, e->tok_pb, BL, 1, 1e-5f));
+    // the last layer's fp32 output is the encoder memory read by rmb_act_debug_read
+    const bool f32_out = !e->res16 || l == c.enc_layers - 1;
+    begin(nm, "layernorm512_kernel", 0, (double)BL * 512 * ((e->res16 ? 2 : 4) + (f32_out ? 4 : 0) + 2 + 2));
+    if (e->res16) RMB_CUDA(launch_pdl(layernorm512_kernel_t<act_t>, dim3(ln_grid), dim3(256), 0, s, (const act_t*)e->y_f32, w.g2, w.be2, e->pos, L, f32_out ? e->tok_f32 : (float*)nullptr, e->tok_b, e->tok_pb, BL, 1, 1e-5f));
+    else RMB_CUDA(launch_pdl(layernorm512_kernel, dim3(ln_grid), dim3(256), 0, s, e->y_f32, w.g2, w.be2, e->pos, L, e->tok_f32, e->tok_b, e->tok_pb, BL, 1, 1e-5f));
     end();
   }
   RMB_RUN(run_gemm("dec0 K proj", bp->dk, tokb));

@@ -131,7 +131,8 @@ __global__ void maxpool3x3s2_kernel(const act_t* __restrict__ in, act_t* __restr
 //   outputs (each optional): y_f32 (residual stream), y_act (GEMM A operand), ypos_act = act_t(y + pos[row % L])
 //   do_norm = 0 turns it into the plain cast(+pos) pass used once on the assembled input tokens.
 constexpr int kD = 512;
-__global__ void layernorm512_kernel(const float* __restrict__ x_in, const float* __restrict__ gamma,
+template <typename TIn>
+__global__ void layernorm512_kernel_t(const TIn* __restrict__ x_in, const float* __restrict__ gamma,
                                     const float* __restrict__ beta, const float* __restrict__ pos, int L,
                                     float* __restrict__ y_f32, act_t* __restrict__ y_act,
                                     act_t* __restrict__ ypos_act, long long rows, int do_norm, float eps) {
@@ -141,12 +142,22 @@ __global__ void layernorm512_kernel(const float* __restrict__ x_in, const float*
   const long long warp_global = (blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x) >> 5;
   const long long warps_total = (static_cast<long long>(gridDim.x) * blockDim.x) >> 5;
   for (long long row = warp_global; row < rows; row += warps_total) {
-    const float4* xp = reinterpret_cast<const float4*>(x_in + row * kD);
     float v[16];
+    if constexpr (sizeof(TIn) == 4) {
+      const float4* xp = reinterpret_cast<const float4*>(x_in + row * kD);
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const float4 t = __ldg(xp + i * 32 + lane);
-      v[4 * i] = t.x; v[4 * i + 1] = t.y; v[4 * i + 2] = t.z; v[4 * i + 3] = t.w;
+      for (int i = 0; i < 4; ++i) {
+        const float4 t = __ldg(xp + i * 32 + lane);
+        v[4 * i] = t.x; v[4 * i + 1] = t.y; v[4 * i + 2] = t.z; v[4 * i + 3] = t.w;
+      }
+    } else {                                          // 16-bit pre-norm sums (same element -> lane mapping)
+      const uint2* xp = reinterpret_cast<const uint2*>(x_in + row * kD);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const uint2 t = __ldg(xp + i * 32 + lane);
+        const float2 a = unpack_act2(t.x), b = unpack_act2(t.y);
+        v[4 * i] = a.x; v[4 * i + 1] = a.y; v[4 * i + 2] = b.x; v[4 * i + 3] = b.y;
+      }
     }
     if (do_norm) {
       float s = 0.f;
@@ -195,6 +206,8 @@ __global__ void layernorm512_kernel(const float* __restrict__ x_in, const float*
     }
   }
 }
+// the two instances in use: fp32 pre-norm rows (C ABI, decoder, bf16 build) and 16-bit pre-norm rows (encoder, fp16 build)
+#define layernorm512_kernel layernorm512_kernel_t<float>
 
 // ---------------------------------------------------------------------------------------------------------------------
 // Tokens 0 (latent) and 1 (proprio) of every episode (detr_vae.py:124-125,138; transformer.py:62-63), fp32 [B, L, 512].
