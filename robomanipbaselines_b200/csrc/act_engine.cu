@@ -1179,6 +1179,18 @@ int rmb_attention(const void* d_Q, int ldq, int q_col0, int q_shared, const void
   return 0;
 }
 
+#ifdef RMB_ATTN_TRACE
+// debug builds only (scripts/attn_trace.py): copies the (event, clock) pairs logged by attention_v3_kernel and resets the log
+extern "C" int rmb_attention_trace_dump(long long* h_words, int max_words) {
+  RMB_CUDA(cudaDeviceSynchronize());
+  const int n = max_words < 2 * 16384 ? max_words : 2 * 16384;
+  RMB_CUDA(cudaMemcpyFromSymbol(h_words, rmb::g_attn_trace, sizeof(long long) * n));
+  static long long zeros[2 * 16384] = {};
+  RMB_CUDA(cudaMemcpyToSymbol(rmb::g_attn_trace, zeros, sizeof(zeros)));
+  return n;
+}
+#endif
+
 int rmb_set_attention_variant(int variant) {
   if (variant == 0) return g_attn_variant;
   if (variant < 1 || variant > 3) return fail("rmb_set_attention_variant: variant must be 1, 2 or 3 (0 = query)");

@@ -104,6 +104,41 @@ __device__ __forceinline__ void tma_load_3d_a(uint32_t smem_dst, const void* tma
       ::"r"(smem_dst), "l"(reinterpret_cast<uint64_t>(tmap)), "r"(bar_addr), "r"(c0), "r"(c1), "r"(c2)
       : "memory");
 }
+// Part of the exponentials runs on the FMA pipe instead of the MUFU unit (16 ex2 per clock per SM is what bounds the
+// kernel: one exponential per score against 256 tensor flops at head dim 64). 2^t for t <= ~8: n = round(t) by the
+// magic-number add, f = t - n in [-0.5, 0.5], degree-3 minimax polynomial (max relative error 7.5e-5, below the 16-bit
+// rounding of P), n added into the exponent field. Of every 16 score pairs of a chunk, RMB_ATTN_POLY_NUM * 4 of the
+// odd ones take this path. Measured on B200 at 256 episodes x 602 keys: 0.3645 ms without, 0.3674 / 0.3752 / 0.3802 ms
+// with 25 / 37.5 / 50 % of the scores on the polynomial (an FFMA2 occupies the FMA pipe for as long as two EX2 occupy
+// the MUFU unit, and the kernel was latency- not MUFU-bound), so the default is 0 (off).
+#ifndef RMB_ATTN_PINGPONG
+#define RMB_ATTN_PINGPONG 1
+#endif
+#ifndef RMB_ATTN_STAGGER
+#define RMB_ATTN_STAGGER 0
+#endif
+#ifndef RMB_ATTN_MAX_CHAINS
+#define RMB_ATTN_MAX_CHAINS 4
+#endif
+#ifndef RMB_ATTN_POLY_NUM
+#define RMB_ATTN_POLY_NUM 0
+#endif
+__device__ __forceinline__ float2 poly_exp2_x2(float2 t) {
+  t.x = fmaxf(t.x, -125.0f); t.y = fmaxf(t.y, -125.0f);
+  const float2 magic = make_float2(12582912.0f, 12582912.0f), nmagic = make_float2(-12582912.0f, -12582912.0f);
+  const float2 none = make_float2(-1.0f, -1.0f);
+  float2 j, r, f, q;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(reinterpret_cast<uint64_t&>(j)) : "l"(reinterpret_cast<uint64_t&>(t)), "l"(reinterpret_cast<const uint64_t&>(magic)));
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(reinterpret_cast<uint64_t&>(r)) : "l"(reinterpret_cast<uint64_t&>(j)), "l"(reinterpret_cast<const uint64_t&>(nmagic)));
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(reinterpret_cast<uint64_t&>(f)) : "l"(reinterpret_cast<uint64_t&>(r)), "l"(reinterpret_cast<const uint64_t&>(none)), "l"(reinterpret_cast<uint64_t&>(t)));
+  const float2 c3 = make_float2(0.0551716685295105f, 0.0551716685295105f), c2 = make_float2(0.2426111251115799f, 0.2426111251115799f);
+  const float2 c1 = make_float2(0.6932609677314758f, 0.6932609677314758f), c0 = make_float2(0.9999280571937561f, 0.9999280571937561f);
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(reinterpret_cast<uint64_t&>(q)) : "l"(reinterpret_cast<uint64_t&>(f)), "l"(reinterpret_cast<const uint64_t&>(c3)), "l"(reinterpret_cast<const uint64_t&>(c2)));
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(reinterpret_cast<uint64_t&>(q)) : "l"(reinterpret_cast<uint64_t&>(q)), "l"(reinterpret_cast<uint64_t&>(f)), "l"(reinterpret_cast<const uint64_t&>(c1)));
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(reinterpret_cast<uint64_t&>(q)) : "l"(reinterpret_cast<uint64_t&>(q)), "l"(reinterpret_cast<uint64_t&>(f)), "l"(reinterpret_cast<const uint64_t&>(c0)));
+  return make_float2(__uint_as_float(__float_as_uint(q.x) + (__float_as_uint(j.x) << 23)),
+                     __uint_as_float(__float_as_uint(q.y) + (__float_as_uint(j.y) << 23)));
+}
 __device__ __forceinline__ float2 fadd2(float2 a, float2 b) {
   float2 d;
   asm("add.rn.f32x2 %0, %1, %2;"
@@ -111,6 +146,22 @@ __device__ __forceinline__ float2 fadd2(float2 a, float2 b) {
       : "l"(reinterpret_cast<uint64_t&>(a)), "l"(reinterpret_cast<uint64_t&>(b)));
   return d;
 }
+
+// RMB_ATTN_TRACE (scripts/attn_trace.py builds a separate library with it): CTA 0 / stream 0 logs (event, clock64) pairs
+// of its first softmax warp and of its issuer thread; never compiled into the product libraries.
+#ifdef RMB_ATTN_TRACE
+__device__ long long g_attn_trace[2 * 16384];     // [0, 16384): softmax warp, [16384, 32768): issuer; (id << 48) | clock
+__device__ int g_attn_trace_n;
+#define ATRACE(cond, id)                                                                                   \
+  do {                                                                                                     \
+    if (blockIdx.x == 0 && stream == 0 && lane == 0 && (cond) && trace_k < 16384) {                        \
+      g_attn_trace[((id) >= 100 ? 16384 : 0) + trace_k] = (static_cast<long long>(id) << 48) | (clock64() & 0xffffffffffffll); \
+      ++trace_k;                                                                                           \
+    }                                                                                                      \
+  } while (0)
+#else
+#define ATRACE(cond, id)
+#endif
 
 __global__ void __launch_bounds__(kAttn3Threads, 1)
 attention_v3_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_k,
@@ -123,6 +174,9 @@ attention_v3_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int stream = (warp < 8) ? (warp >> 2) : (warp & 1);
+#ifdef RMB_ATTN_TRACE
+  int trace_k = 0;
+#endif
   const uint32_t sbase = opaque(smem_u32(smem) + stream * kAttn3StreamBytes);   // 32-bit shared-window addresses from here on
   const uint32_t sQ = sbase;              // 2 buffers
   const uint32_t sK = sbase + 2 * 16384;  // 3 stages
@@ -142,8 +196,12 @@ attention_v3_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
       for (int j = 0; j < 9; ++j) mbar_init(b + j, 1);
       mbar_init(b + 9, 4);
       mbar_init(b + 10, 4);
+      for (int j = 11; j < 15; ++j) mbar_init(b + j, 1);   // exponential-section tokens, one per softmax warp
     }
     fence_mbar_init();
+#if RMB_ATTN_PINGPONG
+    for (int j = 11; j < 15; ++j) mbar_arrive(bars_all + j);   // stream 0 goes first: its round-0 grants
+#endif
   }
   if (warp == 8 && lane == 0) { prefetch_tmap(&tmap_q); prefetch_tmap(&tmap_k); prefetch_tmap(&tmap_v); }
   if (warp == 0) { tmem_alloc(tmem_ptr_smem, 512); tmem_relinquish(); }
@@ -230,16 +288,20 @@ attention_v3_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
         if (g1 == nkt) { g1 = 0; it1 = it + 1; }
         if (ks1 == 3) { ks1 = 0; kpar1 ^= 1; }
         mbar_wait_lite(sc_bar, n & 1);                    // S(n) is in registers: the S buffer and K stage ks are free
+        ATRACE(warp == 8, 101);
         if (n + 1 < total) {                         // S(n+1): on the tensor pipe during the whole of block n's softmax
           if (g1 == 0) mbar_wait_lite(q_bar + (it1 & 1) * 8, (it1 >> 1) & 1);
           mbar_wait_lite(k_bar + ks1 * 8, kpar1);
           tc_fence_after();
           issue_s(it1 & 1, ks1, g1 == nkt - 1);
         }
+        ATRACE(warp == 8, 102);
         if (kl < total) load_k();                    // K(n+3) -> stage ks
         if (g == nkt - 1 && it + 2 < my_items) load_q();   // last S of the item is complete: its Q buffer is free
         mbar_wait_lite(pr_bar, n & 1);                    // P(n) is in TMEM; its writers had waited for P V (n - 1)
+        ATRACE(warp == 8, 103);
         mbar_wait_lite(v_bar + (n & 1) * 8, (n >> 1) & 1);
+        ATRACE(warp == 8, 104);
         tc_fence_after();
         {
           const uint64_t dv = dv0 + static_cast<uint64_t>((n & 1) * 1024);
@@ -252,6 +314,7 @@ attention_v3_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
           }
           umma_commit_u32(o_bar);
         }
+        ATRACE(warp == 8, 105);
         if (n >= 1 && vl < total) load_v();          // V(n+1) -> the stage P V (n - 1) has finished with
         g = g1; it = it1; ks = ks1; kpar = kpar1;
       }
@@ -264,6 +327,18 @@ attention_v3_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
     const uint32_t tmem_row = opaque(tmem_S + (static_cast<uint32_t>(wq * 32) << 16));   // this warp's 32 lanes of S
     const float scale = p.scale_log2e;
     const float2 scale2 = make_float2(scale, scale);
+#if RMB_ATTN_PINGPONG
+    // The two softmax warps of a scheduler (same wq, one per stream) take turns at the exponential section of a block.
+    // Free-running they fall into lock-step (scripts/attn_trace.py): both in the section at once, each getting half
+    // of the MUFU unit, then both outside it with the unit idle. With a token that alternates between them one warp
+    // has the unit to itself while the other loads S, takes its maximum and writes O. Round r of a warp = its r-th key
+    // block; a stream with fewer blocks (or none) keeps passing the token until the longer one is done.
+    const uint32_t tok_mine = bars + (11 + wq) * 8;
+    const uint32_t tok_other = opaque(smem_u32(bars_all) + (1 - stream) * kAttn3BarsPerStream * 8) + (11 + wq) * 8;
+    const int first_o = 2 * blockIdx.x + (1 - stream);
+    const int items_o = (first_o < n_items) ? (n_items - first_o + n_streams - 1) / n_streams : 0;
+    const int rounds_total = (my_items > items_o ? my_items : items_o) * nkt;
+#endif
     uint32_t n = 0;                                   // key blocks of this stream seen so far (= S / P V phase counter)
     // The output of an item is written one block late: its last P V is still on the tensor pipe when the item's
     // softmax ends, so the warp goes on to block 0 of its next item and reads O just before it lets that block's P V
@@ -290,6 +365,12 @@ attention_v3_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
       pend = false;
     };
     float m = 0.f, row_sum = 0.f;                          // reference maximum (raw logits), sum of P of the current item
+#if RMB_ATTN_STAGGER > 0
+    if (stream == 1) {                                // start the second stream half a block late (see RMB_ATTN_STAGGER)
+      const long long t_start = clock64();
+      while (clock64() - t_start < RMB_ATTN_STAGGER) {}
+    }
+#endif
     // One key block of a live warp. The common case (all 128 keys valid) runs straight through: the ragged last block
     // of an item takes ONE side branch that masks its dead keys and skips the 32-key chunks without valid keys.
     auto do_block = [&](const int g, const int nvalid) {
@@ -303,6 +384,7 @@ attention_v3_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive_a(sc_bar);             // the issuer may overwrite S: S(g+1) runs under this block's softmax
+      ATRACE(wq == 0, 2);
       // ---- block maximum (keys past Lk: -inf drops out of the maximum and gives P = 0)
       float bm0 = -INFINITY, bm1 = -INFINITY, bm2 = -INFINITY, bm3 = -INFINITY;
       if (nvalid < 128) {
@@ -310,6 +392,21 @@ attention_v3_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
         for (int i = 0; i < 128; ++i)
           if (i >= nvalid) v[i] = 0xff800000u;        // (also the chunks that were not loaded)
       }
+#if RMB_ATTN_MAX_CHAINS == 8
+      float bm4 = -INFINITY, bm5 = -INFINITY, bm6 = -INFINITY, bm7 = -INFINITY;
+#pragma unroll
+      for (int i = 0; i < 128; i += 16) {
+        bm0 = max3(bm0, __uint_as_float(v[i]), __uint_as_float(v[i + 1]));
+        bm1 = max3(bm1, __uint_as_float(v[i + 2]), __uint_as_float(v[i + 3]));
+        bm2 = max3(bm2, __uint_as_float(v[i + 4]), __uint_as_float(v[i + 5]));
+        bm3 = max3(bm3, __uint_as_float(v[i + 6]), __uint_as_float(v[i + 7]));
+        bm4 = max3(bm4, __uint_as_float(v[i + 8]), __uint_as_float(v[i + 9]));
+        bm5 = max3(bm5, __uint_as_float(v[i + 10]), __uint_as_float(v[i + 11]));
+        bm6 = max3(bm6, __uint_as_float(v[i + 12]), __uint_as_float(v[i + 13]));
+        bm7 = max3(bm7, __uint_as_float(v[i + 14]), __uint_as_float(v[i + 15]));
+      }
+      bm0 = max3(bm0, bm4, bm5); bm1 = max3(bm1, bm6, bm7);
+#else
 #pragma unroll
       for (int i = 0; i < 128; i += 8) {
         bm0 = max3(bm0, __uint_as_float(v[i]), __uint_as_float(v[i + 1]));
@@ -317,6 +414,7 @@ attention_v3_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
         bm2 = max3(bm2, __uint_as_float(v[i + 4]), __uint_as_float(v[i + 5]));
         bm3 = max3(bm3, __uint_as_float(v[i + 6]), __uint_as_float(v[i + 7]));
       }
+#endif
       const float bm = fmaxf(fmaxf(bm0, bm1), fmaxf(bm2, bm3));
       bool o_waited = false;
       if (g == 0) {
@@ -344,17 +442,43 @@ attention_v3_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
           tmem_st_wait();
         }
       }
+      ATRACE(wq == 0, 3);
+#if RMB_ATTN_PINGPONG
+      mbar_wait_lite(tok_mine, n & 1);
+      ATRACE(wq == 0, 9);
+#endif
       const float nmsc = -m * scale;
       const float2 nmsc2 = make_float2(nmsc, nmsc);
       float2 acc0 = make_float2(0.f, 0.f), acc1 = make_float2(0.f, 0.f);
+      // One 32-key chunk in three passes over its registers -- scale-and-shift all, exponentiate all, then sum and pack
+      // all -- so that the 32 EX2 go to the MUFU unit back to back. Interleaved per pair (FFMA2, 2 x EX2, FADD2, pack)
+      // a warp issues in order and the FADD2 behind a pair waits out the MUFU latency: the block timeline
+      // (scripts/attn_trace.py) showed ~16 clocks per exponential per warp, twice the unit's 8, with two warps a scheduler.
       auto exp_chunk = [&](auto c_tag, uint32_t (&pk)[16]) {
         constexpr int c = decltype(c_tag)::value;
 #pragma unroll
+        for (int i = 0; i < 32; i += 2) {
+          const float2 t = ffma2(make_float2(__uint_as_float(v[c * 32 + i]), __uint_as_float(v[c * 32 + i + 1])), scale2, nmsc2);
+          v[c * 32 + i] = __float_as_uint(t.x);
+          v[c * 32 + i + 1] = __float_as_uint(t.y);
+        }
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+#if RMB_ATTN_POLY_NUM > 0
+          if ((i & 3) >= 2 && ((i >> 2) & 3) < RMB_ATTN_POLY_NUM) {
+            if (i & 1) continue;
+            const float2 e = poly_exp2_x2(make_float2(__uint_as_float(v[c * 32 + i]), __uint_as_float(v[c * 32 + i + 1])));
+            v[c * 32 + i] = __float_as_uint(e.x);
+            v[c * 32 + i + 1] = __float_as_uint(e.y);
+            continue;
+          }
+#endif
+          v[c * 32 + i] = __float_as_uint(fast_exp2(__uint_as_float(v[c * 32 + i])));
+        }
+#pragma unroll
         for (int i = 0; i < 16; i += 2) {
-          const float2 t0 = ffma2(make_float2(__uint_as_float(v[c * 32 + 2 * i]), __uint_as_float(v[c * 32 + 2 * i + 1])), scale2, nmsc2);
-          const float2 t1 = ffma2(make_float2(__uint_as_float(v[c * 32 + 2 * i + 2]), __uint_as_float(v[c * 32 + 2 * i + 3])), scale2, nmsc2);
-          const float2 e0 = make_float2(fast_exp2(t0.x), fast_exp2(t0.y));
-          const float2 e1 = make_float2(fast_exp2(t1.x), fast_exp2(t1.y));
+          const float2 e0 = make_float2(__uint_as_float(v[c * 32 + 2 * i]), __uint_as_float(v[c * 32 + 2 * i + 1]));
+          const float2 e1 = make_float2(__uint_as_float(v[c * 32 + 2 * i + 2]), __uint_as_float(v[c * 32 + 2 * i + 3]));
           acc0 = fadd2(acc0, e0);
           acc1 = fadd2(acc1, e1);
           pk[i] = pack_act2(e0.x, e0.y);
@@ -367,10 +491,12 @@ attention_v3_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
         uint32_t pk0[16], pk1[16];
         exp_chunk(std::integral_constant<int, 0>{}, pk0);
         if (kFull || nchunks > 1) exp_chunk(std::integral_constant<int, 1>{}, pk1);
+        ATRACE(wq == 0, 4);
         if (n > 0 && !o_waited) {
           mbar_wait_lite(o_bar, (n - 1) & 1);
           tc_fence_after();
         }
+        ATRACE(wq == 0, 5);
         tmem_st_32x32b_x16(tmem_row + 128, pk0);
         if (kFull || nchunks > 1) tmem_st_32x32b_x16(tmem_row + 128 + 16, pk1);
       }
@@ -384,12 +510,19 @@ attention_v3_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
         exp_chunk(std::integral_constant<int, 3>{}, pk);
         tmem_st_32x32b_x16(tmem_row + 128 + 48, pk);
       }
+#if RMB_ATTN_PINGPONG
+      __syncwarp();
+      if (lane == 0) mbar_arrive_a(tok_other);
+#endif
       row_sum += (acc0.x + acc0.y) + (acc1.x + acc1.y);
+      ATRACE(wq == 0, 6);
       if (pend) write_out();                          // g == 0: O of the previous item, complete since the o_bar wait above
+      ATRACE(wq == 0, 8);
       tmem_st_wait();
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive_a(pr_bar);             // 4 arrivals: P V (n) may be issued
+      ATRACE(wq == 0, 7);
     };
     for (int it = 0; it < my_items; ++it) {
       const int item = first + it * n_streams;
@@ -418,6 +551,11 @@ attention_v3_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
           __syncwarp();
           if (lane == 0) mbar_arrive_a(pr_bar);
           __syncwarp();
+#if RMB_ATTN_PINGPONG
+          mbar_wait_lite(tok_mine, n & 1);
+          __syncwarp();
+          if (lane == 0) mbar_arrive_a(tok_other);
+#endif
         }
         continue;
       }
@@ -425,6 +563,7 @@ attention_v3_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
       for (int g = 0; g < nkt; ++g, ++n) {
         mbar_wait_lite(s_bar, n & 1);
         tc_fence_after();
+        ATRACE(wq == 0, 1);
         do_block(g, (g == nkt - 1) ? last_valid : 128);
       }
       const int q = qt * 128 + row;
@@ -437,6 +576,13 @@ attention_v3_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
       tc_fence_after();
       write_out();
     }
+#if RMB_ATTN_PINGPONG
+    for (uint32_t r = n; r < static_cast<uint32_t>(rounds_total); ++r) {   // keep the partner's token moving
+      mbar_wait_lite(tok_mine, r & 1);
+      __syncwarp();
+      if (lane == 0) mbar_arrive_a(tok_other);
+    }
+#endif
   }
   tc_fence_before();
   __syncthreads();
