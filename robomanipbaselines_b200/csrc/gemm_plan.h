@@ -204,6 +204,36 @@ inline bool plan_conv(GemmPlan* g, const void* in, int B, int H, int W, int Cin,
   const uint64_t wdims[2] = {K, (uint64_t)Cout};
   const uint64_t wstr[1] = {K * e};
   g->pair = gemm_use_pair(p);
+  // halo3 (gemm_tc.cuh, GemmParams::halo3): 3x3 stride-1 convs with 128-wide column tiles launched as CTA pairs (the
+  // ResNet layer2 convs). Needs a w x h = 128-pixel box with w % 8 == 0 inside one image that tiles the map at least
+  // as well as the generic box; a stage is the (h + 2)-row input box + three half-tiles of weights, and the launch
+  // uses as many stages as fit in the variant's shared memory (4 of 44 KB for the 16 x 8 box). RMB_GEMM_NO_HALO3=1: off.
+  static const bool halo_off = [] { const char* ev = getenv("RMB_GEMM_NO_HALO3"); return ev != nullptr && ev[0] == '1'; }();
+  if (!halo_off && ksize == 3 && stride == 1 && g->block_n == 128 && g->pair) {
+    const double eff0 = static_cast<double>(OW) * OH * B / (128.0 * p.tiles_w * p.tiles_h * p.tiles_b);
+    int bw = 0, bh = 0;
+    double best = 0.0;
+    for (int w : {8, 16, 32, 64}) {                        // taller boxes first: (h + 2) / h rows are fetched per tile
+      const int h = 128 / w;
+      if (w > OW + 7 || h > OH + 7) continue;
+      const long long tw = (OW + w - 1) / w, th = (OH + h - 1) / h;
+      const double eff = static_cast<double>(OW) * OH / (128.0 * tw * th);
+      if (eff > best + 1e-9) { best = eff; bw = w; bh = h; }
+    }
+    const int a_bytes = (bh + 2) * bw * 128, stage_bytes = a_bytes + 3 * (g->block_n / 2) * 128;
+    const int stages = std::min(8, (8 * (128 * 128 + (g->block_n / 2) * 128)) / std::max(stage_bytes, 1));   // GemmSmem<128, 64, 8, true>
+    if (bw > 0 && best >= eff0 - 0.07 && stages >= 3) {
+      p.box_w = bw; p.box_h = bh; p.box_b = 1;
+      p.tiles_w = (OW + bw - 1) / bw; p.tiles_h = (OH + bh - 1) / bh; p.tiles_b = B;
+      p.halo3 = 1; p.halo_stages = stages; p.halo_a_bytes = a_bytes;
+      const uint64_t dims[5] = {(uint64_t)Cin, (uint64_t)W, 1, (uint64_t)H, (uint64_t)B};
+      const uint64_t strides[4] = {Cin * e, (uint64_t)W * Cin * e, (uint64_t)W * Cin * e, (uint64_t)H * W * Cin * e};
+      const uint32_t box[5] = {64, (uint32_t)bw, 1, (uint32_t)(bh + 2), 1};
+      if (!make_tmap_act(&g->ta, in, 5, dims, strides, box, 128, err)) return false;
+      g->pair = gemm_use_pair(p);
+      if (!g->pair) { if (err) *err = "plan_conv: halo3 box lost the pair launch"; return false; }
+    }
+  }
   const uint32_t wbox[2] = {64, (uint32_t)(g->pair ? g->block_n / 2 : g->block_n)};
   if (!make_tmap_act(&g->tb, Wt, 2, wdims, wstr, wbox, 128, err)) return false;
   g->flops = 2ll * B * OH * OW * Cout * (long long)K;

@@ -29,6 +29,12 @@ struct GemmParams {
   int tap_d1[kMaxTaps];      // added to coordinate 1 (w)
   int tap_d2[kMaxTaps];      // coordinate 2 (h phase for stride-2 views, else 0)
   int tap_d3[kMaxTaps];      // added to coordinate 3 (h)
+  // halo3 (3x3 stride-1 convs, box_w * box_h == 128, box_b == 1, box_w % 8 == 0): a pipeline stage holds, for one filter
+  // COLUMN kw and one 64-channel chunk, the (box_h + 2)-row input box ONCE plus the three weight tiles of kh = 0..2; the
+  // three row taps are MMAs over views of that box shifted by kh * box_w rows (a multiple of the 1024-byte swizzle
+  // period). A is then fetched 3 * (box_h + 2) / box_h times instead of 9 -- what bounded the N = 128 convs was the
+  // L2 -> SM operand stream (96 B/clk per SM wanted at 128-wide tiles, ~61 available).
+  int halo3, halo_stages, halo_a_bytes;
   // epilogue
   const float* bias;         // [N] or nullptr
   const void* residual;      // [rows, ld_res] or nullptr
@@ -173,6 +179,15 @@ __device__ __forceinline__ void gemm_epilogue(const GemmParams& p, uint8_t* smem
       }
     }
     const float* bias_ptr = (p.bias != nullptr) ? p.bias + col0 : nullptr;
+    // 16-bit residual rows are loaded into registers one chunk ahead: chunk 0's before the wait for the accumulator
+    // (the tile is still on the tensor pipe), chunk j + 1's at the top of chunk j -- behind the accumulator they cost a
+    // full L2 round trip per chunk, which set the pace of the N = 128 convs (two chunks per warp and tile)
+    uint2 rvn[8];
+    if (RES == 1) {
+  #pragma unroll
+      for (int it = 0; it < 8; ++it)
+        rvn[it] = (optr[it] != nullptr && col0 < p.n_valid) ? __ldg(reinterpret_cast<const uint2*>(rptr[it])) : make_uint2(0u, 0u);
+    }
     mbar_wait(&tmem_full_bar[acc], acc_phase);
     tc_fence_after();
     const uint32_t t_row = tmem_base + acc * BLOCK_N + half * 32 + (static_cast<uint32_t>(q * 32) << 16);
@@ -180,6 +195,18 @@ __device__ __forceinline__ void gemm_epilogue(const GemmParams& p, uint8_t* smem
     tmem_ld_32x32b_x32(t_row, v);
   #pragma unroll
     for (int j = 0; j < kChunksPerWarp; ++j) {      // this warp's chunk j = columns half*32 + j*64 .. +31 of the tile
+      uint2 rv1[8];
+      if (RES == 1) {
+  #pragma unroll
+        for (int it = 0; it < 8; ++it) rv1[it] = rvn[it];
+        if (j + 1 < kChunksPerWarp) {
+          const bool nok = col0 + (j + 1) * 64 < p.n_valid;
+  #pragma unroll
+          for (int it = 0; it < 8; ++it)
+            rvn[it] = (optr[it] != nullptr && nok) ? __ldg(reinterpret_cast<const uint2*>(rptr[it] + (j + 1) * 64 * kResEsz))
+                                                    : make_uint2(0u, 0u);
+        }
+      }
       tmem_ld_wait();
   #pragma unroll
       for (int g = 0; g < 8; ++g) st_shared_v4(st_addr[g], v[4 * g], v[4 * g + 1], v[4 * g + 2], v[4 * g + 3]);
@@ -215,14 +242,9 @@ __device__ __forceinline__ void gemm_epilogue(const GemmParams& p, uint8_t* smem
   #pragma unroll
         for (int it = 0; it < 8; ++it) { f[it].x += rv[it].x; f[it].y += rv[it].y; f[it].z += rv[it].z; f[it].w += rv[it].w; }
       } else if (RES == 1) {
-        uint2 rv[8];
-  #pragma unroll
-        for (int it = 0; it < 8; ++it)
-          rv[it] = (optr[it] != nullptr && col_ok) ? __ldg(reinterpret_cast<const uint2*>(rptr[it] + j * 64 * kResEsz))
-                                         : make_uint2(0u, 0u);
   #pragma unroll
         for (int it = 0; it < 8; ++it) {
-          const float2 lo = unpack_act2(rv[it].x), hi = unpack_act2(rv[it].y);
+          const float2 lo = unpack_act2(rv1[it].x), hi = unpack_act2(rv1[it].y);
           f[it].x += lo.x; f[it].y += lo.y; f[it].z += hi.x; f[it].w += hi.y;
         }
       }
@@ -412,10 +434,48 @@ __device__ __forceinline__ void gemm_tc_body(const CUtensorMap& tmap_a, const CU
       const int bt = rt / (p.tiles_w * p.tiles_h);
       const int w0 = wt * p.box_w, h0 = ht * p.box_h, b0 = bt * p.box_b;
       const int n0 = ct * BLOCK_N + n_half;
-      int kcol = 0;                                   // column of the weight matrix = kb * BLOCK_K
-      for (int tap = 0; tap < p.num_taps; ++tap) {
-        const int c0 = p.tap_c0[tap], d1 = w0 + p.tap_d1[tap], d2 = p.tap_d2[tap], d3 = h0 + p.tap_d3[tap];
+      if (p.halo3) {
+        const uint32_t a_stride = static_cast<uint32_t>(p.halo_a_bytes), b_stride = 3u * S::kBBytes;
+        const uint32_t bh_base = a_base + p.halo_stages * a_stride;
+        const uint32_t tx = a_stride + b_stride;
+        for (int kw = 0; kw < 3; ++kw) {
+          for (int ch = 0; ch < p.chunks_per_tap; ++ch) {
+            mbar_wait(&empty_bar[stage], phase ^ 1);
+            if (elect_one()) {
+              const uint32_t fb = full_base + stage * 8;
+              if (PAIR) {
+                if (rank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * tx);
+                tma_load_5d_pair(a_base + stage * a_stride, &tmap_a, fb, ch * BLOCK_K, w0 + kw - 1, 0, h0 - 1, b0);
+#pragma unroll
+                for (int kh = 0; kh < 3; ++kh)
+                  tma_load_2d_pair(bh_base + stage * b_stride + kh * S::kBBytes, &tmap_b, fb,
+                                   ((kh * 3 + kw) * p.chunks_per_tap + ch) * BLOCK_K, n0);
+              } else {
+                mbar_arrive_expect_tx_u32(fb, tx);
+                tma_load_5d_u32(a_base + stage * a_stride, &tmap_a, fb, ch * BLOCK_K, w0 + kw - 1, 0, h0 - 1, b0);
+#pragma unroll
+                for (int kh = 0; kh < 3; ++kh)
+                  tma_load_2d_u32(bh_base + stage * b_stride + kh * S::kBBytes, &tmap_b, fb,
+                                  ((kh * 3 + kw) * p.chunks_per_tap + ch) * BLOCK_K, n0);
+              }
+            }
+            __syncwarp();
+            if (++stage == p.halo_stages) { stage = 0; phase ^= 1; }
+          }
+        }
+        continue;
+      }
+      // k-block order. 9-tap (3x3) convs walk (kw, channel chunk, kh) -- the order of the halo3 stages above -- so that
+      // an output element accumulates its products in ONE order whichever path a launch takes (results stay
+      // bit-identical across batch sizes); everything else walks (tap, chunk) = ascending weight column.
+      const bool kw_major = (p.num_taps == 9);
+      const int outer_n = kw_major ? 3 : p.num_taps, inner_n = kw_major ? 3 : 1;
+      for (int outer = 0; outer < outer_n; ++outer) {
         for (int ch = 0; ch < p.chunks_per_tap; ++ch) {
+         for (int inner = 0; inner < inner_n; ++inner) {
+          const int tap = kw_major ? inner * 3 + outer : outer;
+          const int c0 = p.tap_c0[tap], d1 = w0 + p.tap_d1[tap], d2 = p.tap_d2[tap], d3 = h0 + p.tap_d3[tap];
+          const int kcol = (tap * p.chunks_per_tap + ch) * BLOCK_K;   // column of the weight matrix
           mbar_wait(&empty_bar[stage], phase ^ 1);
           if (elect_one()) {
             const uint32_t fb = full_base + stage * 8;
@@ -435,8 +495,8 @@ __device__ __forceinline__ void gemm_tc_body(const CUtensorMap& tmap_a, const CU
             }
           }
           __syncwarp();
-          kcol += BLOCK_K;
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
+         }
         }
       }
     }
@@ -452,6 +512,34 @@ __device__ __forceinline__ void gemm_tc_body(const CUtensorMap& tmap_a, const CU
         mbar_wait(&tmem_empty_bar[acc], acc_phase ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * BLOCK_N;
+        if (p.halo3) {
+          const uint32_t a_stride16 = static_cast<uint32_t>(p.halo_a_bytes) >> 4, b_stride16 = (3u * S::kBBytes) >> 4;
+          const uint64_t bh_desc0 = a_desc0 + static_cast<uint64_t>(p.halo_stages * a_stride16);
+          const uint32_t row_shift16 = static_cast<uint32_t>(p.box_w * BLOCK_K * 2) >> 4;   // one input row of the box
+          const int n_it = 3 * p.chunks_per_tap;
+          for (int it = 0; it < n_it; ++it) {
+            mbar_wait(&full_bar[stage], phase);
+            tc_fence_after();
+            if (elect_one()) {
+              const uint64_t da = a_desc0 + static_cast<uint64_t>(stage * a_stride16);
+              const uint64_t db = bh_desc0 + static_cast<uint64_t>(stage * b_stride16);
+#pragma unroll
+              for (int kh = 0; kh < 3; ++kh) {
+#pragma unroll
+                for (int k = 0; k < BLOCK_K / 16; ++k) {
+                  const uint64_t dak = da + static_cast<uint64_t>(kh * row_shift16 + 2 * k);
+                  const uint64_t dbk = db + static_cast<uint64_t>(kh * (S::kBBytes >> 4) + 2 * k);
+                  if (PAIR) umma_f16_ss_pair(d_tmem, dak, dbk, kIdesc, (it | kh | k) != 0 ? 1u : 0u);
+                  else umma_f16_ss(d_tmem, dak, dbk, kIdesc, (it | kh | k) != 0 ? 1u : 0u);
+                }
+              }
+              if (PAIR) umma_commit_pair_u32(empty_base + stage * 8, 3u);
+              else umma_commit_u32(empty_base + stage * 8);
+            }
+            __syncwarp();
+            if (++stage == p.halo_stages) { stage = 0; phase ^= 1; }
+          }
+        } else
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();

@@ -21,6 +21,8 @@ def kernel_key(name):
     base = re.sub(r"^void\s+", "", name)
     short = re.sub(r"<.*", "", base).replace("rmb::", "").strip()
     short = re.sub(r"\(.*", "", short)
+    if short == "layernorm512_kernel_t":              # the two input-type instances report under bench.py's launch name
+        return "layernorm512_kernel"
     if short == "gemm_tc_pair_kernel" and re.search(r"<\s*\(?int\)?512", base):
         return "gemm_tc_pair_kernel<LN>"
     return short

@@ -101,6 +101,8 @@ def _conv_ref(x_nhwc, w_oihw, bias, res_nhwc, stride, relu):
     (2, 16, 16, 64, 64, 3, 1, 1, 0), (3, 30, 40, 64, 128, 3, 2, 1, 0), (3, 30, 40, 64, 128, 1, 2, 0, 0),
     (2, 15, 20, 512, 512, 3, 1, 1, 1), (5, 15, 20, 512, 512, 1, 1, 0, 0), (2, 60, 80, 128, 128, 3, 1, 1, 1),
     (2, 120, 160, 64, 64, 3, 1, 1, 1), (2, 60, 80, 128, 256, 3, 2, 1, 0), (3, 30, 40, 256, 512, 3, 2, 1, 0),
+    # enough row tiles for CTA pairs: 3x3 stride-1 convs with 128 output channels take the halo3 stages (gemm_tc.cuh)
+    (8, 60, 80, 128, 128, 3, 1, 1, 1), (9, 60, 80, 128, 128, 3, 1, 1, 0), (40, 28, 36, 128, 128, 3, 1, 0, 1),
 ])
 def test_conv(lib, cuda, B, H, W, Cin, Cout, k, stride, relu, use_res):
     g = torch.Generator(device="cpu").manual_seed(B + H + W + Cin + Cout + k + stride)
