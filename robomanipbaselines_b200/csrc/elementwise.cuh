@@ -7,6 +7,7 @@
 //   ensemble_step                  : temporal ensembling + denormalise (policy/act/RolloutAct.py:68-101, DataUtils.py:26-40)
 //   normalize_state                : normalize_data (common/utils/DataUtils.py:9-23) + f64->f32 cast (RolloutBase.py:474-475)
 #pragma once
+#include <type_traits>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -141,20 +142,35 @@ __global__ void layernorm512_kernel_t(const TIn* __restrict__ x_in, const float*
   const int lane = threadIdx.x & 31;
   const long long warp_global = (blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x) >> 5;
   const long long warps_total = (static_cast<long long>(gridDim.x) * blockDim.x) >> 5;
+  // the next row's loads are issued before this row is reduced and written (two rows in flight per warp: a 16-bit
+  // row is only 1 KB, and one row per warp left the kernel at 4.6-5.0 TB/s)
+  using raw_t = typename std::conditional<sizeof(TIn) == 4, float4, uint2>::type;
+  raw_t nxt[4];
+  if (warp_global < rows) {
+    const raw_t* xp = reinterpret_cast<const raw_t*>(x_in + warp_global * kD);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) nxt[i] = __ldg(xp + i * 32 + lane);
+  }
   for (long long row = warp_global; row < rows; row += warps_total) {
+    raw_t cur[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) cur[i] = nxt[i];
+    if (row + warps_total < rows) {
+      const raw_t* xp = reinterpret_cast<const raw_t*>(x_in + (row + warps_total) * kD);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) nxt[i] = __ldg(xp + i * 32 + lane);
+    }
     float v[16];
     if constexpr (sizeof(TIn) == 4) {
-      const float4* xp = reinterpret_cast<const float4*>(x_in + row * kD);
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
-        const float4 t = __ldg(xp + i * 32 + lane);
+        const float4 t = *reinterpret_cast<const float4*>(&cur[i]);
         v[4 * i] = t.x; v[4 * i + 1] = t.y; v[4 * i + 2] = t.z; v[4 * i + 3] = t.w;
       }
     } else {                                          // 16-bit pre-norm sums (same element -> lane mapping)
-      const uint2* xp = reinterpret_cast<const uint2*>(x_in + row * kD);
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
-        const uint2 t = __ldg(xp + i * 32 + lane);
+        const uint2 t = *reinterpret_cast<const uint2*>(&cur[i]);
         const float2 a = unpack_act2(t.x), b = unpack_act2(t.y);
         v[4 * i] = a.x; v[4 * i + 1] = a.y; v[4 * i + 2] = b.x; v[4 * i + 3] = b.y;
       }
