@@ -160,6 +160,8 @@ struct rmb_act_engine {
   ConvW stem;
   ConvW blk[4][2][2];      // [layer][block][conv]
   ConvW down[4];           // layer 1..3 (index = layer), layer 0 unused
+  ConvW c1down[4];         // conv1 of block 0 with the downsample conv as side columns (make_conv1_with_downsample)
+  bool fuse_down = true;   // RMB_NO_DOWN_FUSE=1: the downsample convs as their own launches
   ConvW input_proj;
   struct EncW {
     act_t *w_qk, *w_v, *w_o, *w_1, *w_2;
@@ -265,19 +267,45 @@ bool bn_fold(rmb_act_engine* e, const std::string& bn, int c, std::vector<float>
   return true;
 }
 
-bool make_conv(rmb_act_engine* e, const std::string& conv, const std::string& bn, int cin, int cout, int k, int stride,
-               rmb_act_engine::ConvW* out, std::string* err) {
+// BN-folded conv weights on the host: r [cout][k][k][cin] (tap-major, channel-minor), bias [cout]
+bool fold_conv_host(rmb_act_engine* e, const std::string& conv, const std::string& bn, int cin, int cout, int k,
+                    std::vector<float>* r, std::vector<float>* bias, std::string* err) {
   const auto* w = find_w(e, conv + ".weight", (size_t)cout * cin * k * k, err); if (!w) return false;
-  std::vector<float> scale, bias;
-  if (!bn_fold(e, bn, cout, &scale, &bias, err)) return false;
-  std::vector<float> r((size_t)cout * k * k * cin);
+  std::vector<float> scale;
+  if (!bn_fold(e, bn, cout, &scale, bias, err)) return false;
+  r->assign((size_t)cout * k * k * cin, 0.f);
   for (int co = 0; co < cout; ++co)
     for (int ci = 0; ci < cin; ++ci)
       for (int kh = 0; kh < k; ++kh)
         for (int kw = 0; kw < k; ++kw)
-          r[(((size_t)co * k + kh) * k + kw) * cin + ci] = (*w)[(((size_t)co * cin + ci) * k + kh) * k + kw] * scale[co];
+          (*r)[(((size_t)co * k + kh) * k + kw) * cin + ci] = (*w)[(((size_t)co * cin + ci) * k + kh) * k + kw] * scale[co];
+  return true;
+}
+
+bool make_conv(rmb_act_engine* e, const std::string& conv, const std::string& bn, int cin, int cout, int k, int stride,
+               rmb_act_engine::ConvW* out, std::string* err) {
+  std::vector<float> r, bias;
+  if (!fold_conv_host(e, conv, bn, cin, cout, k, &r, &bias, err)) return false;
   out->cin = cin; out->cout = cout; out->k = k; out->stride = stride;
   return upload_act(e, r, &out->w, err) && upload_f32(e, bias, &out->b, err);
+}
+
+// conv1 (3x3 stride 2) of a down-sampling BasicBlock with the block's 1x1 stride-2 downsample conv as extra output
+// rows: [2 * cout, 9 * cin], the downsample rows non-zero in the centre tap only (backbone.py:86-96 -> torchvision
+// BasicBlock: identity = downsample(x) reads x[2h, 2w], the pixel conv1's centre tap reads); bias [2 * cout].
+bool make_conv1_with_downsample(rmb_act_engine* e, const std::string& blk, int cin, int cout, rmb_act_engine::ConvW* out,
+                                std::string* err) {
+  std::vector<float> r1, b1, rd, bd;
+  if (!fold_conv_host(e, blk + "conv1", blk + "bn1", cin, cout, 3, &r1, &b1, err)) return false;
+  if (!fold_conv_host(e, blk + "downsample.0", blk + "downsample.1", cin, cout, 1, &rd, &bd, err)) return false;
+  std::vector<float> rc((size_t)2 * cout * 9 * cin, 0.f), bc(2 * (size_t)cout);
+  std::copy(r1.begin(), r1.end(), rc.begin());
+  for (int co = 0; co < cout; ++co) {
+    for (int ci = 0; ci < cin; ++ci) rc[(((size_t)(cout + co)) * 9 + 4) * cin + ci] = rd[(size_t)co * cin + ci];
+    bc[co] = b1[co]; bc[cout + co] = bd[co];
+  }
+  out->cin = cin; out->cout = 2 * cout; out->k = 3; out->stride = 2;
+  return upload_act(e, rc, &out->w, err) && upload_f32(e, bc, &out->b, err);
 }
 
 void layernorm_host(const std::vector<double>& x, const std::vector<float>& g, const std::vector<float>& b, std::vector<double>* y) {
@@ -336,6 +364,7 @@ int rmb_act_engine_create(const rmb_act_config_t* cfg, rmb_act_engine_t** out) {
   e->num_sms = prop.multiProcessorCount;
   { const char* ev = getenv("RMB_NO_STEM_POOL"); e->fuse_stem_pool = !(ev != nullptr && ev[0] == '1'); }
   { const char* ev = getenv("RMB_LN_FUSE"); e->fuse_ln = (ev == nullptr) ? 0 : (ev[0] == 'n' ? 0 : (ev[0] == 'a' && ev[1] == 'l') ? 2 : 1); }
+  { const char* ev = getenv("RMB_NO_DOWN_FUSE"); e->fuse_down = !(ev != nullptr && ev[0] == '1'); }
   { const char* ev = getenv("RMB_RES_F32"); if (ev != nullptr && (ev[0] == '0' || ev[0] == '1')) e->res16 = (ev[0] == '0'); }
   e->Hf = cfg->img_h / 32; e->Wf = cfg->img_w / 32;
   e->n_prefix = 2 + (cfg->task_token ? 1 : 0);
@@ -392,8 +421,10 @@ int rmb_act_finalize(rmb_act_engine_t* e) {
       const int stride = (bi == 0 && li > 0) ? 2 : 1;
       if (!make_conv(e, p + "conv1", p + "bn1", cin, chans[li], 3, stride, &e->blk[li][bi][0], &err)) return fail(err);
       if (!make_conv(e, p + "conv2", p + "bn2", chans[li], chans[li], 3, 1, &e->blk[li][bi][1], &err)) return fail(err);
-      if (bi == 0 && li > 0)
+      if (bi == 0 && li > 0) {
         if (!make_conv(e, p + "downsample.0", p + "downsample.1", cin, chans[li], 1, 2, &e->down[li], &err)) return fail(err);
+        if (!make_conv1_with_downsample(e, p, cin, chans[li], &e->c1down[li], &err)) return fail(err);
+      }
     }
   {
     // input_proj: Conv2d 1x1 512 -> hidden with bias, no BN (detr_vae.py:67,135)
@@ -600,7 +631,7 @@ static int build_plans(rmb_act_engine* e, int nb, rmb_act_engine::BatchPlans** o
     const int cin = (li == 0) ? 64 : chans[li - 1];
     const void* identity = x_in;
     if (li > 0) {
-      if (!plan_conv(&bp->down[li], x_in, NI, hin, win, cin, 1, 2, e->down[li].w, chans[li], e->down[li].b, nullptr, false, z, chans[li], false, false, &err)) return fail(err);
+      if (!e->fuse_down && !plan_conv(&bp->down[li], x_in, NI, hin, win, cin, 1, 2, e->down[li].w, chans[li], e->down[li].b, nullptr, false, z, chans[li], false, false, &err)) return fail(err);
       identity = z;
     }
     if (li == 0) {
@@ -610,6 +641,10 @@ static int build_plans(rmb_act_engine* e, int nb, rmb_act_engine::BatchPlans** o
       if (!plan_conv3x3_halo(&bp->conv_l1[1][1], t, NI, h, w, e->blk[0][1][1].w, e->blk[0][1][1].b, y, z, true, &err)) return fail(err);
       continue;
     }
+    if (li > 0 && e->fuse_down) {   // conv1 + the downsample conv (-> z, no ReLU) in one launch
+      if (!plan_conv(&bp->conv[li][0][0], x_in, NI, hin, win, cin, 3, 2, e->c1down[li].w, chans[li], e->c1down[li].b, nullptr, false, t, chans[li], false, true, &err,
+                     chans[li], z, chans[li], false)) return fail(err);
+    } else
     if (!plan_conv(&bp->conv[li][0][0], x_in, NI, hin, win, cin, 3, (li == 0) ? 1 : 2, e->blk[li][0][0].w, chans[li], e->blk[li][0][0].b, nullptr, false, t, chans[li], false, true, &err)) return fail(err);
     if (!plan_conv(&bp->conv[li][0][1], t, NI, h, w, chans[li], 3, 1, e->blk[li][0][1].w, chans[li], e->blk[li][0][1].b, identity, false, y, chans[li], false, true, &err)) return fail(err);
     if (!plan_conv(&bp->conv[li][1][0], y, NI, h, w, chans[li], 3, 1, e->blk[li][1][0].w, chans[li], e->blk[li][1][0].b, nullptr, false, t, chans[li], false, true, &err)) return fail(err);
@@ -664,7 +699,7 @@ int rmb_act_forward_num_launches(const rmb_act_engine_t* e) {
   if (!e) return -1;
   // preprocess, stem, maxpool, 16 convs + 3 downsamples, input_proj, extra tokens, cast(+pos), 8 per encoder layer,
   // decoder: K, V, attention, out, LN, FF1, FF2, head
-  return (e->fuse_stem_pool ? 2 : 3) + 19 + 3 + 8 * e->cfg.enc_layers + 8;
+  return (e->fuse_stem_pool ? 2 : 3) + (e->fuse_down ? 16 : 19) + 3 + 8 * e->cfg.enc_layers + 8;
 }
 
 double rmb_act_forward_flops(const rmb_act_engine_t* e, int batch) {
@@ -858,6 +893,7 @@ static int forward_impl(rmb_act_engine_t* e, const void* d_images, int image_for
     RMB_CUDA(launch_gemm(g, sms, s));
     end();
     if (!g.p.out_f32 && g.p.remap_ncam == 0) scan(g.p.out, (long long)g.p.W * g.p.H * g.p.B * g.p.ld_out);
+    if (g.p.n_main_ct > 0) scan(g.p.out2, (long long)g.p.W * g.p.H * g.p.B * g.p.ld_out2);
     return 0;
   };
 #define RMB_RUN(x) do { if (int _r = (x)) return _r; } while (0)
@@ -895,7 +931,7 @@ static int forward_impl(rmb_act_engine_t* e, const void* d_images, int image_for
     const double px = (double)NI * (H >> (2 + li)) * (W >> (2 + li));
     const double cin = li == 0 ? 64 : chans[li - 1];
     const double in_b = (li == 0 ? px : px * 4) * cin * 2, mid_b = px * chans[li] * 2;
-    if (li > 0) { snprintf(nm, sizeof(nm), "layer%d.0.downsample 1x1/2", li + 1); RMB_RUN(run_gemm(nm, bp->down[li], in_b)); }
+    if (li > 0 && !e->fuse_down) { snprintf(nm, sizeof(nm), "layer%d.0.downsample 1x1/2", li + 1); RMB_RUN(run_gemm(nm, bp->down[li], in_b)); }
     if (li == 0) {
       RMB_RUN(run_halo("layer1.0.conv1 3x3", bp->conv_l1[0][0], in_b));
       RMB_RUN(run_halo("layer1.0.conv2 3x3", bp->conv_l1[0][1], mid_b));
@@ -903,7 +939,8 @@ static int forward_impl(rmb_act_engine_t* e, const void* d_images, int image_for
       RMB_RUN(run_halo("layer1.1.conv2 3x3", bp->conv_l1[1][1], mid_b));
       continue;
     }
-    snprintf(nm, sizeof(nm), "layer%d.0.conv1 3x3", li + 1); RMB_RUN(run_gemm(nm, bp->conv[li][0][0], in_b));
+    snprintf(nm, sizeof(nm), (li > 0 && e->fuse_down) ? "layer%d.0.conv1 3x3 + downsample" : "layer%d.0.conv1 3x3", li + 1);
+    RMB_RUN(run_gemm(nm, bp->conv[li][0][0], in_b));
     snprintf(nm, sizeof(nm), "layer%d.0.conv2 3x3", li + 1); RMB_RUN(run_gemm(nm, bp->conv[li][0][1], mid_b));
     snprintf(nm, sizeof(nm), "layer%d.1.conv1 3x3", li + 1); RMB_RUN(run_gemm(nm, bp->conv[li][1][0], mid_b));
     snprintf(nm, sizeof(nm), "layer%d.1.conv2 3x3", li + 1); RMB_RUN(run_gemm(nm, bp->conv[li][1][1], mid_b));

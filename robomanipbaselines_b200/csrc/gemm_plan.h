@@ -156,9 +156,13 @@ inline bool plan_linear_ln(GemmPlan* g, const void* A, long long M, int K, int l
 
 // NHWC 16-bit conv, k x k (k = 1 or 3), stride 1 or 2, pad = k/2, as an implicit GEMM.
 //   in [B, H, W, Cin], Wt [Cout, k*k*Cin] (tap-major, channel-minor), out rows = B*OH*OW, ld = Cout (or ld_out)
+// side_cout > 0 (3x3 stride-2 convs only): Wt is [Cout + side_cout, 9*Cin] whose rows >= Cout are a 1x1 stride-2 conv on
+// the same input (non-zero in the centre tap's columns only), bias is [Cout + side_cout]; those columns go to out2
+// (GemmParams::n_main_ct).
 inline bool plan_conv(GemmPlan* g, const void* in, int B, int H, int W, int Cin, int ksize, int stride, const void* Wt,
                       int Cout, const float* bias, const void* residual, bool res_f32, void* out, int ld_out,
-                      bool out_f32, bool relu, std::string* err) {
+                      bool out_f32, bool relu, std::string* err, int side_cout = 0, void* out2 = nullptr, int ld_out2 = 0,
+                      bool relu2 = false) {
   *g = GemmPlan();
   g->block_k = 64;
   if (Cout % 64 != 0 || Cin % 64 != 0) { if (err) *err = "plan_conv: Cout and Cin must be multiples of 64"; return false; }
@@ -172,6 +176,15 @@ inline bool plan_conv(GemmPlan* g, const void* in, int B, int H, int W, int Cin,
   p.tiles_w = (OW + p.box_w - 1) / p.box_w; p.tiles_h = (OH + p.box_h - 1) / p.box_h; p.tiles_b = (B + p.box_b - 1) / p.box_b;
   g->block_n = pick_block_n(Cout, 1ll * p.tiles_w * p.tiles_h * p.tiles_b);
   p.n_col_tiles = Cout / g->block_n;
+  if (side_cout > 0) {
+    if (ksize != 3 || stride != 2 || residual != nullptr || out_f32 || out2 == nullptr || side_cout % g->block_n != 0) {
+      if (err) *err = "plan_conv: side columns need a 3x3 stride-2 conv without residual, a 16-bit output and side_cout % block_n == 0";
+      return false;
+    }
+    p.n_main_ct = p.n_col_tiles;
+    p.n_col_tiles += side_cout / g->block_n;
+    p.out2 = out2; p.ld_out2 = ld_out2; p.relu2 = relu2 ? 1 : 0;
+  }
   p.num_taps = ksize * ksize; p.chunks_per_tap = Cin / 64;
   for (int t = 0; t < kMaxTaps; ++t) { p.tap_c0[t] = p.tap_d1[t] = p.tap_d2[t] = p.tap_d3[t] = 0; }
   for (int kh = 0; kh < ksize; ++kh)
@@ -201,7 +214,7 @@ inline bool plan_conv(GemmPlan* g, const void* in, int B, int H, int W, int Cin,
     if (!make_tmap_act(&g->ta, in, 5, dims, strides, box, 128, err)) return false;
   }
   const uint64_t K = (uint64_t)ksize * ksize * Cin;
-  const uint64_t wdims[2] = {K, (uint64_t)Cout};
+  const uint64_t wdims[2] = {K, (uint64_t)(Cout + side_cout)};
   const uint64_t wstr[1] = {K * e};
   g->pair = gemm_use_pair(p);
   // halo3 (gemm_tc.cuh, GemmParams::halo3): 3x3 stride-1 convs with 128-wide column tiles launched as CTA pairs (the
@@ -236,7 +249,7 @@ inline bool plan_conv(GemmPlan* g, const void* in, int B, int H, int W, int Cin,
   }
   const uint32_t wbox[2] = {64, (uint32_t)(g->pair ? g->block_n / 2 : g->block_n)};
   if (!make_tmap_act(&g->tb, Wt, 2, wdims, wstr, wbox, 128, err)) return false;
-  g->flops = 2ll * B * OH * OW * Cout * (long long)K;
+  g->flops = 2ll * B * OH * OW * Cout * (long long)K + 2ll * B * OH * OW * side_cout * (long long)Cin;
   return true;
 }
 

@@ -35,6 +35,13 @@ struct GemmParams {
   // period). A is then fetched 3 * (box_h + 2) / box_h times instead of 9 -- what bounded the N = 128 convs was the
   // L2 -> SM operand stream (96 B/clk per SM wanted at 128-wide tiles, ~61 available).
   int halo3, halo_stages, halo_a_bytes;
+  // side column tiles (n_main_ct > 0): column tiles ct >= n_main_ct belong to a SECOND, 1x1 conv on the same input pixels
+  // -- the stride-2 downsample of a ResNet block riding in the launch of the block's 3x3 stride-2 conv1, whose centre
+  // tap reads exactly the pixels the 1x1 conv reads. Their weight rows (>= n_main_ct * BLOCK_N of the same matrix) are
+  // zero outside the centre tap, so the k-loop of a side tile is the centre tap's k-blocks only; they are stored to
+  // out2 (columns counted from 0) with their own ReLU switch; bias rows continue the main conv's.
+  int n_main_ct, ld_out2, relu2;
+  void* out2;
   // epilogue
   const float* bias;         // [N] or nullptr
   const void* residual;      // [rows, ld_res] or nullptr
@@ -154,6 +161,11 @@ __device__ __forceinline__ void gemm_epilogue(const GemmParams& p, uint8_t* smem
         my_orow = (b / p.remap_ncam) * p.remap_L + p.remap_off + h * (p.W * p.remap_ncam) + (b % p.remap_ncam) * p.W + w;
     }
     const int col0 = ct * BLOCK_N + col_in_tile;
+    const bool side = p.n_main_ct > 0 && ct >= p.n_main_ct;          // (RES == 0 launches only: plan_conv)
+    char* const out_base = static_cast<char*>(side ? p.out2 : p.out);
+    const int out_ld = side ? p.ld_out2 : p.ld_out;
+    const int out_col0 = side ? col0 - p.n_main_ct * BLOCK_N : col0;
+    const float relu_floor_t = side ? (p.relu2 ? 0.0f : -INFINITY) : relu_floor;
     if (RES != 0 && my_grow >= 0) {
       // this row's residual segments of the tile go to L2 now, while the accumulator is still being built: the loads
       // in pass 2 then see L2 latency instead of HBM latency (no registers to hold them across the chunk loop)
@@ -170,7 +182,7 @@ __device__ __forceinline__ void gemm_epilogue(const GemmParams& p, uint8_t* smem
     for (int it = 0; it < 8; ++it) {
       fptr[it] = FILM ? p.film + __shfl_sync(0xffffffffu, my_film, it * 4 + rsel) + col0 : nullptr;
       const int orow = __shfl_sync(0xffffffffu, my_orow, it * 4 + rsel);
-      optr[it] = (orow >= 0) ? static_cast<char*>(p.out) + (static_cast<long long>(orow) * p.ld_out + col0) * kOutEsz : nullptr;
+      optr[it] = (orow >= 0) ? out_base + (static_cast<long long>(orow) * out_ld + out_col0) * kOutEsz : nullptr;
       if (RES != 0) {
         const int grow = __shfl_sync(0xffffffffu, my_grow, it * 4 + rsel);
         rptr[it] = static_cast<const char*>(p.residual) + (static_cast<long long>(grow < 0 ? 0 : grow) * p.ld_res + col0) * kResEsz;
@@ -250,8 +262,8 @@ __device__ __forceinline__ void gemm_epilogue(const GemmParams& p, uint8_t* smem
       }
   #pragma unroll
       for (int it = 0; it < 8; ++it) {
-        const float ox = fmaxf(f[it].x + bv.x, relu_floor), oy = fmaxf(f[it].y + bv.y, relu_floor);
-        const float oz = fmaxf(f[it].z + bv.z, relu_floor), ow = fmaxf(f[it].w + bv.w, relu_floor);
+        const float ox = fmaxf(f[it].x + bv.x, relu_floor_t), oy = fmaxf(f[it].y + bv.y, relu_floor_t);
+        const float oz = fmaxf(f[it].z + bv.z, relu_floor_t), ow = fmaxf(f[it].w + bv.w, relu_floor_t);
         if (optr[it] != nullptr && col_ok) {
           if (OUT_F32) *reinterpret_cast<float4*>(optr[it] + j * 64 * kOutEsz) = make_float4(ox, oy, oz, ow);
           else *reinterpret_cast<uint2*>(optr[it] + j * 64 * kOutEsz) = make_uint2(pack_act2(ox, oy), pack_act2(oz, ow));
@@ -469,11 +481,13 @@ __device__ __forceinline__ void gemm_tc_body(const CUtensorMap& tmap_a, const CU
       // an output element accumulates its products in ONE order whichever path a launch takes (results stay
       // bit-identical across batch sizes); everything else walks (tap, chunk) = ascending weight column.
       const bool kw_major = (p.num_taps == 9);
+      const bool side_tile = p.n_main_ct > 0 && ct >= p.n_main_ct;
       const int outer_n = kw_major ? 3 : p.num_taps, inner_n = kw_major ? 3 : 1;
       for (int outer = 0; outer < outer_n; ++outer) {
         for (int ch = 0; ch < p.chunks_per_tap; ++ch) {
          for (int inner = 0; inner < inner_n; ++inner) {
           const int tap = kw_major ? inner * 3 + outer : outer;
+          if (side_tile && tap != 4) continue;
           const int c0 = p.tap_c0[tap], d1 = w0 + p.tap_d1[tap], d2 = p.tap_d2[tap], d3 = h0 + p.tap_d3[tap];
           const int kcol = (tap * p.chunks_per_tap + ch) * BLOCK_K;   // column of the weight matrix
           mbar_wait(&empty_bar[stage], phase ^ 1);
@@ -512,6 +526,7 @@ __device__ __forceinline__ void gemm_tc_body(const CUtensorMap& tmap_a, const CU
         mbar_wait(&tmem_empty_bar[acc], acc_phase ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * BLOCK_N;
+        const int tile_kb = (p.n_main_ct > 0 && ts.tile(ti) % p.n_col_tiles >= p.n_main_ct) ? p.chunks_per_tap : num_kb;
         if (p.halo3) {
           const uint32_t a_stride16 = static_cast<uint32_t>(p.halo_a_bytes) >> 4, b_stride16 = (3u * S::kBBytes) >> 4;
           const uint64_t bh_desc0 = a_desc0 + static_cast<uint64_t>(p.halo_stages * a_stride16);
@@ -540,7 +555,7 @@ __device__ __forceinline__ void gemm_tc_body(const CUtensorMap& tmap_a, const CU
             if (++stage == p.halo_stages) { stage = 0; phase ^= 1; }
           }
         } else
-        for (int kb = 0; kb < num_kb; ++kb) {
+        for (int kb = 0; kb < tile_kb; ++kb) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
           if (elect_one()) {
