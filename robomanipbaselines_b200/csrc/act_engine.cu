@@ -161,7 +161,11 @@ struct rmb_act_engine {
   ConvW blk[4][2][2];      // [layer][block][conv]
   ConvW down[4];           // layer 1..3 (index = layer), layer 0 unused
   ConvW c1down[4];         // conv1 of block 0 with the downsample conv as side columns (make_conv1_with_downsample)
-  bool fuse_down = true;   // RMB_NO_DOWN_FUSE=1: the downsample convs as their own launches
+  // RMB_DOWN_FUSE=1: the downsample convs as side column tiles of conv1's launch. Correct and bit-identical, but measured
+  // SLOWER on B200 (layer2.0: 0.95 ms against 0.25 + 0.45 ms; step 19.8 against 19.1 ms): a side tile is one k-block of
+  // MMA work and a full epilogue, and the plain epilogue (~1 us per 128 x 128 tile) then runs twice per nine k-blocks,
+  // so the launch becomes epilogue-bound; in their own launches the two epilogues overlap different MMAs. Opt-in.
+  bool fuse_down = false;
   ConvW input_proj;
   struct EncW {
     act_t *w_qk, *w_v, *w_o, *w_1, *w_2;
@@ -364,7 +368,7 @@ int rmb_act_engine_create(const rmb_act_config_t* cfg, rmb_act_engine_t** out) {
   e->num_sms = prop.multiProcessorCount;
   { const char* ev = getenv("RMB_NO_STEM_POOL"); e->fuse_stem_pool = !(ev != nullptr && ev[0] == '1'); }
   { const char* ev = getenv("RMB_LN_FUSE"); e->fuse_ln = (ev == nullptr) ? 0 : (ev[0] == 'n' ? 0 : (ev[0] == 'a' && ev[1] == 'l') ? 2 : 1); }
-  { const char* ev = getenv("RMB_NO_DOWN_FUSE"); e->fuse_down = !(ev != nullptr && ev[0] == '1'); }
+  { const char* ev = getenv("RMB_DOWN_FUSE"); e->fuse_down = (ev != nullptr && ev[0] == '1'); }
   { const char* ev = getenv("RMB_RES_F32"); if (ev != nullptr && (ev[0] == '0' || ev[0] == '1')) e->res16 = (ev[0] == '0'); }
   e->Hf = cfg->img_h / 32; e->Wf = cfg->img_w / 32;
   e->n_prefix = 2 + (cfg->task_token ? 1 : 0);
@@ -423,7 +427,7 @@ int rmb_act_finalize(rmb_act_engine_t* e) {
       if (!make_conv(e, p + "conv2", p + "bn2", chans[li], chans[li], 3, 1, &e->blk[li][bi][1], &err)) return fail(err);
       if (bi == 0 && li > 0) {
         if (!make_conv(e, p + "downsample.0", p + "downsample.1", cin, chans[li], 1, 2, &e->down[li], &err)) return fail(err);
-        if (!make_conv1_with_downsample(e, p, cin, chans[li], &e->c1down[li], &err)) return fail(err);
+        if (e->fuse_down && !make_conv1_with_downsample(e, p, cin, chans[li], &e->c1down[li], &err)) return fail(err);
       }
     }
   {

@@ -249,6 +249,21 @@ inline bool plan_conv(GemmPlan* g, const void* in, int B, int H, int W, int Cin,
   }
   const uint32_t wbox[2] = {64, (uint32_t)(g->pair ? g->block_n / 2 : g->block_n)};
   if (!make_tmap_act(&g->tb, Wt, 2, wdims, wstr, wbox, 128, err)) return false;
+  // 1x1 convs with a 16-bit NHWC output and no residual (the stride-2 downsample convs: one or a few k-blocks per tile,
+  // bound by the epilogue): the TMA-store epilogue (EPI 3) over a rank-5 output map. Measured at 256 episodes: 0.252 /
+  // 0.134 / 0.080 -> 0.213 / 0.106 / 0.066 ms; on the 3x3 stride-2 conv1 launches the same epilogue measured SLOWER
+  // (layer2.0.conv1 0.46 -> 0.53 ms: boxes of two images, 2 KB runs), so they keep the staged-transpose epilogue.
+  // RMB_GEMM_NO_TMA_OUT=1 keeps the plain epilogue everywhere.
+  static const bool no_tma_out = [] { const char* ev = getenv("RMB_GEMM_NO_TMA_OUT"); return ev != nullptr && ev[0] == '1'; }();
+  if (!no_tma_out && ksize == 1 && !out_f32 && residual == nullptr && side_cout == 0 && ld_out == Cout &&
+      p.box_w * p.box_h * p.box_b <= 128 && (reinterpret_cast<uintptr_t>(out) & 15) == 0) {
+    const uint64_t odims[5] = {(uint64_t)Cout, (uint64_t)OW, 1, (uint64_t)OH, (uint64_t)B};
+    const uint64_t ostr[4] = {Cout * e, (uint64_t)OW * Cout * e, (uint64_t)OW * Cout * e, (uint64_t)OH * OW * Cout * e};
+    const uint32_t obox[5] = {64, (uint32_t)p.box_w, 1, (uint32_t)p.box_h, (uint32_t)p.box_b};
+    if (!make_tmap_act(&g->tout, out, 5, odims, ostr, obox, 128, err)) return false;
+    g->tma_out = true;
+    p.out_5d = 1;
+  }
   g->flops = 2ll * B * OH * OW * Cout * (long long)K + 2ll * B * OH * OW * side_cout * (long long)Cin;
   return true;
 }

@@ -42,6 +42,9 @@ struct GemmParams {
   // out2 (columns counted from 0) with their own ReLU switch; bias rows continue the main conv's.
   int n_main_ct, ld_out2, relu2;
   void* out2;
+  // EPI 3 on a conv: tmap_out is the rank-5 NHWC output map (channels, W, 1, H, B) and a slab is stored as one
+  // (64, box_w, 1, box_h, box_b) box at the tile's pixel origin instead of a 128-row box of a plain matrix
+  int out_5d;
   // epilogue
   const float* bias;         // [N] or nullptr
   const void* residual;      // [rows, ld_res] or nullptr
@@ -334,7 +337,13 @@ __device__ __forceinline__ void gemm_epilogue_tma(const CUtensorMap* tmap_out, c
       }
       fence_proxy_async_smem();                        // generic-proxy writes -> visible to the TMA store
       named_bar_sync(1 + grp, 128);
-      if (issuer && col_ok && row0 < p.W) {
+      if (p.out_5d) {
+        const int wt = rt % p.tiles_w, ht = (rt / p.tiles_w) % p.tiles_h, bt = rt / (p.tiles_w * p.tiles_h);
+        if (issuer && col_ok && bt < p.tiles_b) {      // (a pair's odd last row tile is all padding)
+          tma_store_5d(tmap_out, stage, col0, wt * p.box_w, 0, ht * p.box_h, bt * p.box_b);
+          bulk_commit_group();
+        }
+      } else if (issuer && col_ok && row0 < p.W) {
         tma_store_2d(tmap_out, stage, col0, row0);
         bulk_commit_group();
       }
