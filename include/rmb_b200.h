@@ -179,6 +179,10 @@ int rmb_set_attention_variant(int variant);
 /* LayerNorm over 512 columns: x fp32 [rows,512]; outputs optional (NULL): y fp32, y act, act(y + pos[row % L]) */
 int rmb_layernorm512(const float* d_x, const float* d_gamma, const float* d_beta, const float* d_pos, int L,
                      float* d_y_f32, void* d_y_act, void* d_ypos_act, int64_t rows, int do_norm, void* stream);
+/* The same LayerNorm over 16-bit rows: x act [rows,512] (the pre-norm sums x + sublayer(x) that the residual GEMMs of
+ * the fp16 build write in 16 bits; transformer.py:166-179 norm1 / norm2); statistics and arithmetic in fp32. */
+int rmb_layernorm512_act(const void* d_x_act, const float* d_gamma, const float* d_beta, const float* d_pos, int L,
+                         float* d_y_f32, void* d_y_act, void* d_ypos_act, int64_t rows, int do_norm, void* stream);
 
 /* =====================================================================================================================
  * Diffusion Policy / DP3 denoising path.

@@ -147,6 +147,8 @@ SIGNATURES = {
     "rmb_set_attention_variant": (c_int, [c_int]),
     "rmb_layernorm512": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p,
                                  c_int64, c_int, c_void_p]),
+    "rmb_layernorm512_act": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p,
+                                 c_int64, c_int, c_void_p]),
     "rmb_scheduler_step": (c_int, [c_void_p, c_void_p, c_void_p, POINTER(SchedStep), c_void_p, c_int64, c_void_p]),
     "rmb_unet_engine_create": (c_int, [POINTER(UnetConfig), POINTER(c_void_p)]),
     "rmb_unet_engine_destroy": (None, [c_void_p]),

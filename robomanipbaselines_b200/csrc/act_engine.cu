@@ -1251,6 +1251,18 @@ int rmb_layernorm512(const float* d_x, const float* d_gamma, const float* d_beta
   return 0;
 }
 
+int rmb_layernorm512_act(const void* d_x_act, const float* d_gamma, const float* d_beta, const float* d_pos, int L,
+                         float* d_y_f32, void* d_y_act, void* d_ypos_act, int64_t rows, int do_norm, void* stream_) {
+  if (!d_x_act) return fail("rmb_layernorm512_act: null argument");
+  if (do_norm && (!d_gamma || !d_beta)) return fail("rmb_layernorm512_act: gamma/beta required");
+  if (d_ypos_act && (!d_pos || L < 1)) return fail("rmb_layernorm512_act: pos table required");
+  layernorm512_kernel_t<act_t><<<grid_for(rows * 32, 256, 148), 256, 0, static_cast<cudaStream_t>(stream_)>>>(
+      static_cast<const act_t*>(d_x_act), d_gamma, d_beta, d_pos, L < 1 ? 1 : L, d_y_f32, static_cast<act_t*>(d_y_act),
+      static_cast<act_t*>(d_ypos_act), rows, do_norm, 1e-5f);
+  RMB_CUDA(cudaGetLastError());
+  return 0;
+}
+
 }  // extern "C"
 
 #include "diffusion_engine.cuh"

@@ -278,6 +278,31 @@ def test_layernorm(lib, cuda):
     assert (ypb.float() - (x + pos.repeat(2, 1))).abs().max().item() <= 8e-2
 
 
+def test_layernorm_16bit_rows(lib, cuda):
+    """layernorm512_kernel_t<act_t> (the encoder's LayerNorms in the fp16 build read 16-bit pre-norm sums): against
+    F.layer_norm of the SAME 16-bit values in fp32, so only the arithmetic is compared (<= 1e-4 on the fp32 output)."""
+    rows, L = 2411, 602           # odd row count: the two-rows-in-flight loop ends on a single row in some warps
+    x16 = (torch.randn(rows, 512) * 3 + 1).to(cuda).to(_act_dtype())
+    gamma, beta = torch.randn(512).to(cuda), torch.randn(512).to(cuda)
+    pos = torch.randn(L, 512).to(cuda)
+    y = torch.empty(rows, 512, device=cuda)
+    yb = torch.empty(rows, 512, device=cuda, dtype=_act_dtype())
+    ypb = torch.empty(rows, 512, device=cuda, dtype=_act_dtype())
+    check(lib.rmb_layernorm512_act(ptr(x16), ptr(gamma), ptr(beta), ptr(pos), L, ptr(y), ptr(yb), ptr(ypb), rows, 1,
+                                   cur_stream()), "layernorm_act")
+    torch.cuda.synchronize()
+    ref = F.layer_norm(x16.float(), (512,), gamma, beta, 1e-5)
+    posr = pos.repeat((rows + L - 1) // L, 1)[:rows]
+    assert (y - ref).abs().max().item() <= 1e-4
+    assert (yb.float() - ref).abs().max().item() <= 4e-2
+    assert (ypb.float() - (ref + posr)).abs().max().item() <= 6e-2
+    y2 = torch.empty_like(y)
+    check(lib.rmb_layernorm512(ptr(x16.float().contiguous()), ptr(gamma), ptr(beta), ptr(pos), L, ptr(y2), None, None, rows, 1,
+                               cur_stream()), "layernorm")
+    torch.cuda.synchronize()
+    assert torch.equal(y, y2)     # same arithmetic as the fp32-row instance on the same values
+
+
 @pytest.mark.parametrize("norm", ["gaussian", "limits"])
 def test_ensemble_bit_exact(lib, cuda, norm):
     """Ring positions, step counters and float64 actions must equal the numpy oracle exactly (C=7, wraps 3 times)."""
