@@ -173,7 +173,8 @@ int rmb_attention(const void* d_Q, int ldq, int q_col0, int q_shared, const void
                        const void* d_V, int ldv, int v_col0, void* d_out, int ld_out, int B, int n_heads, int Lq, int Lk,
                        void* stream);
 /* Which attention kernel rmb_attention and the ACT engine launch (csrc/act_engine.cu: 1 two-sweep, 2 one-sweep with P in
- * shared memory, 3 one-sweep with P in TMEM). variant 0 = query. Returns the variant now in force, or -1.
+ * shared memory, 3 one-sweep with P in TMEM and two query streams per CTA, 4 = 3 with three streams and 64-key blocks,
+ * the default). variant 0 = query. Returns the variant now in force, or -1.
  * Captured CUDA graphs keep the kernel they were captured with. */
 int rmb_set_attention_variant(int variant);
 /* LayerNorm over 512 columns: x fp32 [rows,512]; outputs optional (NULL): y fp32, y act, act(y + pos[row % L]) */

@@ -8,7 +8,7 @@ CSRC = os.path.join(PKG_DIR, "csrc")
 LIB_PATH = os.path.join(PKG_DIR, "librmb_b200.so")             # product default: IEEE fp16 operands
 LIB_PATH_BF16 = os.path.join(PKG_DIR, "librmb_b200_bf16.so")   # same sources with -DRMB_ACT_BF16 (RMB_LIB_DTYPE=bf16)
 SOURCES = ["act_engine.cu"]
-HEADERS = ["ptx.cuh", "gemm_tc.cuh", "gemm_plan.h", "tma_host.h", "attention_tc.cuh", "elementwise.cuh", "conv_halo.cuh", "diffusion_kernels.cuh", "diffusion_engine.cuh", "imgenc_engine.cuh", "gemm_gn.cuh", "pointcloud.cuh", "resize.cuh", "rollout_glue.cuh", "launch.h", "stem_pool.cuh", "gemm_ln.cuh", "attention_v2.cuh", "attention_v3.cuh", "ik.cuh"]
+HEADERS = ["ptx.cuh", "gemm_tc.cuh", "gemm_plan.h", "tma_host.h", "attention_tc.cuh", "elementwise.cuh", "conv_halo.cuh", "diffusion_kernels.cuh", "diffusion_engine.cuh", "imgenc_engine.cuh", "gemm_gn.cuh", "pointcloud.cuh", "resize.cuh", "rollout_glue.cuh", "launch.h", "stem_pool.cuh", "gemm_ln.cuh", "attention_v2.cuh", "attention_v3.cuh", "attention_v4.cuh", "ik.cuh"]
 
 
 def _nvcc():

@@ -21,6 +21,7 @@
 #include "attention_tc.cuh"
 #include "attention_v2.cuh"
 #include "attention_v3.cuh"
+#include "attention_v4.cuh"
 #include "elementwise.cuh"
 #include "gemm_plan.h"
 
@@ -38,6 +39,7 @@ namespace {
 
 struct AttnPlan {
   CUtensorMap tq, tk, tv;
+  CUtensorMap tk64, tv64;   // 64-key boxes of K / V (attention_v4_kernel)
   AttnParams p;
   int grid = 0;
 };
@@ -60,6 +62,14 @@ bool plan_attention(AttnPlan* a, const void* Q, int ldq, int q_col0, bool q_shar
     const uint64_t dims[3] = {(uint64_t)ldv, (uint64_t)Lk, (uint64_t)B};
     const uint64_t str[2] = {(uint64_t)ldv * 2, (uint64_t)ldv * 2 * Lk};
     if (!make_tmap_act(&a->tv, V, 3, dims, str, box, 128, err)) return false;
+    const uint32_t box64[3] = {64, 64, 1};
+    if (!make_tmap_act(&a->tv64, V, 3, dims, str, box64, 128, err)) return false;
+  }
+  {
+    const uint64_t dims[3] = {(uint64_t)ldk, (uint64_t)Lk, (uint64_t)B};
+    const uint64_t str[2] = {(uint64_t)ldk * 2, (uint64_t)ldk * 2 * Lk};
+    const uint32_t box64[3] = {64, 64, 1};
+    if (!make_tmap_act(&a->tk64, K, 3, dims, str, box64, 128, err)) return false;
   }
   AttnParams& p = a->p;
   p.Lq = Lq; p.Lk = Lk; p.n_q_tiles = (Lq + 127) / 128; p.n_heads = n_heads;
@@ -75,21 +85,22 @@ bool plan_attention(AttnPlan* a, const void* Q, int ldq, int q_col0, bool q_shar
 //   2 attention_v2_kernel  persistent, two streams per CTA, one sweep, P through shared memory (round 2, not faster)
 //   3 attention_v3_kernel  v2's structure with P in TMEM as the A operand of P V, S released before the arithmetic,
 //                          packed fp32x2 softmax arithmetic
-// RMB_ATTN=1|2|3 (or RMB_ATTN_V2=1) picks one at start-up; rmb_set_attention_variant() switches at run time.
+//   4 attention_v4_kernel  v3 with three streams per CTA and 64-key blocks (three softmax warps per scheduler); default
+// RMB_ATTN=1|2|3|4 (or RMB_ATTN_V2=1) picks one at start-up; rmb_set_attention_variant() switches at run time.
 #ifndef RMB_ATTN_DEFAULT
-#define RMB_ATTN_DEFAULT 3
+#define RMB_ATTN_DEFAULT 4
 #endif
 cudaError_t launch_attention_v1(const AttnPlan& a, cudaStream_t stream);
 static int g_attn_variant = [] {
   const char* e = getenv("RMB_ATTN");
-  if (e != nullptr && e[0] >= '1' && e[0] <= '3') return e[0] - '0';
+  if (e != nullptr && e[0] >= '1' && e[0] <= '4') return e[0] - '0';
   const char* e2 = getenv("RMB_ATTN_V2");
   if (e2 != nullptr && e2[0] == '1') return 2;
   return RMB_ATTN_DEFAULT;
 }();
 int attention_variant() { return g_attn_variant; }
 const char* attention_kernel_name() {
-  return g_attn_variant == 3 ? "attention_v3_kernel" : g_attn_variant == 2 ? "attention_v2_kernel" : "attention_tc_kernel";
+  return g_attn_variant == 4 ? "attention_v4_kernel" : g_attn_variant == 3 ? "attention_v3_kernel" : g_attn_variant == 2 ? "attention_v2_kernel" : "attention_tc_kernel";
 }
 cudaError_t launch_attention(const AttnPlan& a, cudaStream_t stream) {
   if (g_attn_variant == 1) return launch_attention_v1(a, stream);
@@ -100,11 +111,16 @@ cudaError_t launch_attention(const AttnPlan& a, cudaStream_t stream) {
     if (e != cudaSuccess) return e;
     e = cudaFuncSetAttribute(attention_v3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttn3SmemBytes);
     if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(attention_v4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttn4SmemBytes);
+    if (e != cudaSuccess) return e;
     int dev = 0;
     if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     attr_set = true;
   }
   const int n_items = a.grid;                       // (episode, head, query tile) work items
+  if (g_attn_variant == 4)
+    return launch_pdl(attention_v4_kernel, dim3(std::min(sms, (n_items + kAttn4Streams - 1) / kAttn4Streams)), dim3(kAttn4Threads),
+                      kAttn4SmemBytes, stream, a.tq, a.tk64, a.tv64, a.p, n_items);
   const int grid = std::min(sms, (n_items + 1) / 2);
   if (g_attn_variant == 2)
     return launch_pdl(attention_v2_kernel, dim3(grid), dim3(kAttn2Threads), kAttn2SmemBytes, stream, a.tq, a.tk, a.tv, a.p, n_items);
@@ -1234,7 +1250,7 @@ extern "C" int rmb_attention_trace_dump(long long* h_words, int max_words) {
 
 int rmb_set_attention_variant(int variant) {
   if (variant == 0) return g_attn_variant;
-  if (variant < 1 || variant > 3) return fail("rmb_set_attention_variant: variant must be 1, 2 or 3 (0 = query)");
+  if (variant < 1 || variant > 4) return fail("rmb_set_attention_variant: variant must be 1, 2, 3 or 4 (0 = query)");
   g_attn_variant = variant;
   return variant;
 }

@@ -195,7 +195,7 @@ def test_maxpool(lib, cuda):
     assert torch.equal(out.float(), ref)
 
 
-@pytest.fixture(params=[1, 2, 3], ids=["v1", "v2", "v3"])
+@pytest.fixture(params=[1, 2, 3, 4], ids=["v1", "v2", "v3", "v4"])
 def attn_variant(lib, request):
     """Every attention kernel variant (csrc/act_engine.cu::launch_attention); restores the library default afterwards."""
     default = lib.rmb_set_attention_variant(0)
